@@ -1,0 +1,150 @@
+/*
+ * mkfhe_b200.h -- C ABI of libmkfhe_b200.so: multi-key accumulator bootstrapping (blind rotation) of SKLC-FHE/MKFHE
+ * on NVIDIA B200 (sm_100a).
+ *
+ * This is the drop-in boundary for ONE path of the reference: the body of
+ *     BinFHEContext::EvalBinGate(NAND, ct1, ct2)                 src/binfhe/lib/binfhecontext.cpp:415-426
+ *       -> BinFHEScheme::EvalBinGate (MNTRU / MKLWE)             src/binfhe/lib/binfhe-base-scheme.cpp:380-515
+ *       -> BinFHEScheme::BootstrapGateCore                       src/binfhe/lib/binfhe-base-scheme.cpp:1004-1130
+ *       -> UniEncAccumulator::EvalAcc  (the plug-in surface)     src/binfhe/include/mk-acc.h:54-80
+ *            UniEncAccumulatorXZW::EvalAcc                       src/binfhe/lib/mk-acc-xzw.cpp:89-130
+ *            UniEncAccumulatorXZW_B::EvalAcc                     src/binfhe/lib/mk-acc-xzw_B.cpp:103-133
+ *       -> ModSwitch + KeySwitch2 / KeySwitch                    src/binfhe/lib/mntru-pke.cpp:359-374,763-823
+ *                                                                src/binfhe/lib/mklwe-pke.cpp:160-171,260-290
+ * (all file:line are into the reference tree).  Results are bit-identical to the reference's CPU code for the same
+ * parameters, key bytes and input ciphertexts.
+ *
+ * Conventions
+ *   - plain C: opaque handle, pointers and sizes; no C++ types and no exceptions cross this boundary.
+ *   - every function returns 0 on success, a negative MKFHE_E* code on failure; mkfhe_last_error() gives the text.
+ *     The reference throws OPENFHE_THROW(config_error, ...) (src/core/include/utils/exception.h:101-162); the C++
+ *     accumulator class in integration/unienc_acc_b200.h turns non-zero codes back into those exceptions.
+ *   - all residues are canonical uint32 (the reference's NativeInteger at NATIVE_SIZE=32, README.md:19).
+ *   - polynomials in EVALUATION format use OpenFHE's slot order: in-place Cooley-Tukey output, slot j holds the value at
+ *     psi^(2*bitrev(j)+1) (src/core/include/math/hal/intnat/transformnat-impl.h:299-354,714-727).
+ *   - pointers named *_host_or_dev may be host or device memory (unified addressing decides); `_dev` entry points take
+ *     device pointers only and enqueue on the context's stream without synchronising.
+ *   - one context per GPU; calls on one context are serialised by the caller (as the reference's single-threaded path).
+ *   - there is NO CPU fallback: without a CUDA device mkfhe_ctx_create fails with MKFHE_ENODEV.
+ */
+#ifndef MKFHE_B200_H
+#define MKFHE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MKFHE_OK 0
+#define MKFHE_EINVAL (-1)   /* bad argument / unsupported parameter combination */
+#define MKFHE_ENODEV (-2)   /* no usable CUDA device (there is no CPU fallback)  */
+#define MKFHE_ECUDA (-3)    /* CUDA runtime error; text in mkfhe_last_error       */
+#define MKFHE_ENOKEY (-4)   /* a key this call needs has not been loaded          */
+#define MKFHE_ENOMEM (-5)
+
+/* accumulator variant: which UniEncAccumulator subclass is being replaced (binfhe-base-scheme.h:137-151) */
+#define MKFHE_VARIANT_XZW 0u   /* UniEncAccumulatorXZW   : ternary secret, evk+ and evk- per coefficient (BINFHE_METHOD MKNTRU) */
+#define MKFHE_VARIANT_XZW_B 1u /* UniEncAccumulatorXZW_B : binary secret, one evk per coefficient (MKNTRU_B, MKNTRU_LWE)       */
+/* additive scheme either side of the accumulator */
+#define MKFHE_SCHEME_MNTRU 0u /* matrix-NTRU ciphertexts: [k][n]      (boolean-mkntru) */
+#define MKFHE_SCHEME_MKLWE 1u /* multi-key LWE ciphertexts: [k][n] + b (boolean-mklwe)  */
+
+typedef struct mkfhe_ctx mkfhe_ctx;
+
+/* The fields of UniEncCryptoParams / MNTRUCryptoParams / MKLWECryptoParams the path reads
+ * (mk-cryptoparameters.h:124-181, mntru-cryptoparameters.h:59-83, mklwe-cryptoparameters.h:59-83). */
+typedef struct mkfhe_params {
+    uint32_t k;          /* parties                                                            */
+    uint32_t N;          /* ring dimension (power of two, 8..2048)                             */
+    uint32_t Q;          /* accumulator modulus, prime, Q = 1 mod 2N, Q < 2^30                 */
+    uint32_t psi;        /* GetRootOfUnity(): minimal primitive 2N-th root of unity mod Q      */
+    uint32_t q;          /* ciphertext modulus of the additive scheme                          */
+    uint32_t qKS;        /* key-switching modulus (== q on both MK paths)                      */
+    uint32_t n;          /* lattice dimension of the additive scheme                           */
+    uint32_t baseG_log2; /* log2 of the gadget base                                            */
+    uint32_t digitsG;    /* GetDigitsG() = ceil(log Q / log baseG); digitsG-1 digits are used  */
+    uint32_t baseKS;     /* key-switching base (<= 256)                                        */
+    uint32_t dKS;        /* ceil(log qKS / log baseKS)                                         */
+    uint32_t variant;    /* MKFHE_VARIANT_*                                                    */
+    uint32_t scheme;     /* MKFHE_SCHEME_*                                                     */
+    int32_t device;      /* CUDA device ordinal; -1 = the calling thread's current device      */
+} mkfhe_params;
+
+/* ---- lifetime ---- */
+int mkfhe_ctx_create(const mkfhe_params* p, mkfhe_ctx** out);
+void mkfhe_ctx_destroy(mkfhe_ctx* ctx);
+/* text of the last error on ctx (ctx == NULL: last mkfhe_ctx_create failure on this thread) */
+const char* mkfhe_last_error(const mkfhe_ctx* ctx);
+/* use `cuda_stream` (a cudaStream_t) for all later work of this context; NULL = the context's own stream */
+int mkfhe_ctx_set_stream(mkfhe_ctx* ctx, void* cuda_stream);
+/* block until all work enqueued by this context has finished */
+int mkfhe_ctx_synchronize(mkfhe_ctx* ctx);
+
+/* ---- keys: caller owns the source buffers; each call copies/re-lays-out into HBM and returns ---- */
+
+/* Bootstrapping key, flattened UniEncACCKeyImpl (mk-acckey.h; built at mk-acc-xzw.cpp:38-87 / mk-acc-xzw_B.cpp:38-101):
+ *   [u < k][s < S][i < n][j < digitsG-1][c < 2][N]   then evk* = (*ek)[0][0][n] as [j][c][N]
+ * S = 2 for XZW (s=0: evk+, s=1: evk-), 1 for XZW_B; c = 0: the "d" column, c = 1: the "f" column of UniEncEvalKeyImpl
+ * (mk-evalkey.h); EVALUATION format.  words must equal (k*S*n + 1) * (digitsG-1) * 2 * N. */
+int mkfhe_load_bk(mkfhe_ctx* ctx, const uint32_t* bk_host_or_dev, uint64_t words);
+/* UniEncBTKey::Pkey (binfhe-base-scheme.h:65-83; built at binfhe-base-scheme.cpp:250-269): [u < k][j < digitsG-1][N], EVALUATION */
+int mkfhe_load_pkey(mkfhe_ctx* ctx, const uint32_t* pkey_host_or_dev, uint64_t words);
+/* MNTRUSwitchingKey2Impl digit-1 slice KSK2[u][1][l][.] (mntru-keyswitchkey2.h; KSK2[u][j] = j*KSK2[u][1] mod qKS,
+ * mntru-pke.cpp:743-752): [u < k][l < N*dKS][n] */
+int mkfhe_load_ksk_mntru(mkfhe_ctx* ctx, const uint32_t* ksk_host_or_dev, uint64_t words);
+/* MKLWESwitchingKeyImpl (mklwe-keyswitchkey.h:28-29): A [u < k][i < N][a0 < baseKS][j < dKS][n], B [u][i][a0][j] */
+int mkfhe_load_ksk_mklwe(mkfhe_ctx* ctx, const uint32_t* A_host_or_dev, uint64_t wordsA, const uint32_t* B_host_or_dev,
+                         uint64_t wordsB);
+/* m_ctNAND of BinFHEContext (binfhecontext.h:88; built by ctGateGen, binfhe-base-scheme.cpp:340-376): [u < k][n]; MNTRU only */
+int mkfhe_load_ctnand(mkfhe_ctx* ctx, const uint32_t* ct_host_or_dev, uint64_t words);
+
+/* ---- the hot path ---- */
+
+/* UniEncAccumulator::EvalAcc for `batch` independent accumulators (mk-acc.h:67-71).
+ *   acc_in / acc_out : [batch][k][N] EVALUATION (may alias)
+ *   rot              : [batch][k][n] -- the `ct` argument of EvalAcc: XZW rotates by rot*2N/rot_mod (mk-acc-xzw.cpp:110,125),
+ *                      XZW_B by rot itself (mk-acc-xzw_B.cpp:120,126; rot_mod ignored)
+ * Host pointers; synchronous. */
+int mkfhe_eval_acc(mkfhe_ctx* ctx, const uint32_t* acc_in, const uint32_t* rot, uint32_t rot_mod, uint32_t* acc_out,
+                   uint64_t batch);
+/* same on device pointers, asynchronous on the context's stream */
+int mkfhe_eval_acc_dev(mkfhe_ctx* ctx, const uint32_t* d_acc_in, const uint32_t* d_rot, uint32_t rot_mod, uint32_t* d_acc_out,
+                       uint64_t batch);
+
+/* BinFHEScheme::EvalBinGate(NAND) for `batch` independent gates (binfhe-base-scheme.cpp:380-515): input combine, initial
+ * accumulator, blind rotation, extraction, modulus switch, key switch.
+ *   ct1, ct2, out : [batch][k][n] mod q
+ *   b1, b2, bout  : [batch]       (MKLWE only; pass NULL for MNTRU)
+ * Host pointers; synchronous (H2D, kernels, D2H). */
+int mkfhe_eval_nand(mkfhe_ctx* ctx, const uint32_t* ct1, const uint32_t* b1, const uint32_t* ct2, const uint32_t* b2,
+                    uint32_t* out, uint32_t* bout, uint64_t batch);
+/* same on device pointers, asynchronous on the context's stream */
+int mkfhe_eval_nand_dev(mkfhe_ctx* ctx, const uint32_t* d_ct1, const uint32_t* d_b1, const uint32_t* d_ct2,
+                        const uint32_t* d_b2, uint32_t* d_out, uint32_t* d_bout, uint64_t batch);
+
+/* NativePoly::SetFormat on `batch` polynomials of N coefficients, in place (poly-impl.h:412-430 ->
+ * transformnat-impl.h:299-354 forward, :491-552 inverse).  inverse = 0: COEFFICIENT -> EVALUATION. */
+int mkfhe_ntt(mkfhe_ctx* ctx, uint32_t* polys, uint64_t batch, int inverse);
+int mkfhe_ntt_dev(mkfhe_ctx* ctx, uint32_t* d_polys, uint64_t batch, int inverse);
+
+/* UniEncAccumulator::SignedDigitDecompose on `batch` COEFFICIENT polynomials (mk-acc.cpp:54-80):
+ * in [batch][N] -> out [batch][digitsG-1][N].  Host pointers; exposed for parity tests of that non-linear step. */
+int mkfhe_decompose(mkfhe_ctx* ctx, const uint32_t* polys, uint32_t* out, uint64_t batch);
+
+/* ---- introspection ---- */
+/* number of kernel launches this context has issued since creation (bench.py's gpu_launches claim) */
+uint64_t mkfhe_launch_count(const mkfhe_ctx* ctx);
+/* bytes of HBM held by this context (keys + tables + workspaces) */
+uint64_t mkfhe_device_bytes(const mkfhe_ctx* ctx);
+/* build-time identity: "mkfhe_b200 <version> sm_100a" */
+const char* mkfhe_version(void);
+/* INT32 pipe micro-benchmark (dependent IMAD chains on every SM): returns thread-level IMAD/s in *imad_per_s.
+ * Used by bench.py as the denominator of the integer roofline (SURVEY.md section 8d asks for a measured peak). */
+int mkfhe_measure_int32_peak(mkfhe_ctx* ctx, double* imad_per_s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MKFHE_B200_H */

@@ -1,0 +1,2 @@
+// see mkfhe_ntl_shim.h (test infrastructure; keygen-only stand-in for NTL)
+#include "mkfhe_ntl_shim.h"
