@@ -1,0 +1,282 @@
+"""Host-side mirror of the reference's user API for the multi-key bootstrapping path.
+
+Names, argument meaning and error behaviour follow `BinFHEContext` (src/binfhe/include/binfhecontext.h:94-338 of the
+reference) for the calls on the path: GenerateBinFHEContext(paramset, method) -> parameters; MKBTKeyGen produces keys on the
+host in the reference -- here the caller hands the reference's key bytes to `LoadKeys`; EvalBinGate(NAND, ct1, ct2) runs the
+GPU path.  Everything that computes goes through the C ABI (mkfhe_b200/lib.py); this file holds no arithmetic except the
+derivation of Q and psi (binfhecontext.cpp:157-158), which is host-side parameter logic.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from math import ceil, log
+
+import numpy as np
+
+from . import lib as _lib
+from .lib import MkfheError, Params
+
+# BINFHE_METHOD values on this path (src/binfhe/include/binfhe-constants.h)
+MKNTRU, MKNTRU_B, MKNTRU_LWE = "MKNTRU", "MKNTRU_B", "MKNTRU_LWE"
+NAND = "NAND"
+
+
+class config_error(ValueError):
+    """mirror of lbcrypto::config_error (src/core/include/utils/exception.h:101-162)"""
+
+
+@dataclass(frozen=True)
+class BinFHEContextParams:
+    """One row of the reference's parameter table (binfhecontext.cpp:91-146): the MK rows."""
+    numUser: int
+    numberBits: int
+    cyclOrder: int
+    latticeParam: int
+    mod: int
+    modKS: int
+    stdDev: float
+    baseKS: int
+    gadgetBase: int
+    baseRK: int
+
+
+STD_DEV, STD_NTRU, STD_NTRU2 = 1.9, 0.5, 0.75
+PARAMSETS = {
+    "STD128_MKNTRU": BinFHEContextParams(2, 27, 4096, 765, 45181, 45181, STD_NTRU, 32, 1 << 7, 32),
+    "STD128_MKNTRU_2": BinFHEContextParams(4, 27, 4096, 765, 45181, 45181, STD_NTRU, 32, 1 << 7, 32),
+    "STD128_MKNTRU_3": BinFHEContextParams(8, 27, 4096, 765, 45181, 45181, STD_NTRU, 32, 1 << 6, 32),
+    "STD128_MKNTRU_4": BinFHEContextParams(16, 27, 4096, 765, 45181, 45181, STD_NTRU, 32, 1 << 5, 32),
+    "STD128_MKNTRU_LWE": BinFHEContextParams(2, 27, 4096, 635, 32749, 32749, STD_DEV, 32, 1 << 9, 2),
+    "STD128_MKNTRU_LWE_2": BinFHEContextParams(4, 27, 4096, 635, 32749, 32749, STD_DEV, 32, 1 << 9, 2),
+    "STD128_MKNTRU_LWE_3": BinFHEContextParams(8, 27, 4096, 635, 32749, 32749, STD_DEV, 32, 1 << 9, 2),
+    "STD128_MKNTRU_LWE_4": BinFHEContextParams(16, 27, 4096, 635, 32749, 32749, STD_DEV, 32, 1 << 7, 2),
+    "STD100_MKNTRU": BinFHEContextParams(2, 27, 4096, 560, 45181, 45181, STD_NTRU2, 32, 1 << 9, 32),
+    "STD100_MKNTRU_2": BinFHEContextParams(4, 27, 4096, 560, 45181, 45181, STD_NTRU2, 32, 1 << 9, 32),
+    "STD100_MKNTRU_3": BinFHEContextParams(8, 27, 4096, 560, 45181, 45181, STD_NTRU2, 32, 1 << 9, 32),
+    "STD100_MKNTRU_4": BinFHEContextParams(16, 27, 4096, 560, 45181, 45181, STD_NTRU2, 32, 1 << 9, 32),
+    "STD100_MKNTRU_LWE": BinFHEContextParams(2, 27, 4096, 500, 32749, 32749, STD_DEV, 32, 1 << 9, 2),
+    "STD100_MKNTRU_LWE_2": BinFHEContextParams(4, 27, 4096, 500, 32749, 32749, STD_DEV, 32, 1 << 9, 2),
+    "STD100_MKNTRU_LWE_3": BinFHEContextParams(8, 27, 4096, 500, 32749, 32749, STD_DEV, 32, 1 << 9, 2),
+    "STD100_MKNTRU_LWE_4": BinFHEContextParams(16, 27, 4096, 500, 32749, 32749, STD_DEV, 32, 1 << 9, 2),
+}
+
+
+# ---- parameter derivation (host logic, integers only) ----
+def _is_prime(n: int) -> bool:
+    if n < 2:
+        return False
+    for p in (2, 3, 5, 7, 11, 13, 17, 19, 23, 29, 31, 37):
+        if n % p == 0:
+            return n == p
+    d, s = n - 1, 0
+    while d % 2 == 0:
+        d //= 2
+        s += 1
+    for a in (2, 3, 5, 7, 11, 13):
+        x = pow(a, d, n)
+        if x in (1, n - 1):
+            continue
+        for _ in range(s - 1):
+            x = x * x % n
+            if x == n - 1:
+                break
+        else:
+            return False
+    return True
+
+
+def first_prime(nbits: int, m: int) -> int:
+    """FirstPrime (src/core/include/math/nbtheory-impl.h:334-358)."""
+    q = 1 << nbits
+    r = q % m
+    q2 = q + 1 + ((m - r) if r else 0)
+    while not _is_prime(q2):
+        q2 += m
+    return q2
+
+
+def previous_prime(q: int, m: int) -> int:
+    """PreviousPrime (nbtheory-impl.h:371-379)."""
+    c = q - m
+    while not _is_prime(c):
+        c -= m
+    return c
+
+
+def root_of_unity(m: int, Q: int) -> int:
+    """RootOfUnity (nbtheory-impl.h:183-231): the minimal primitive m-th root (m a power of two)."""
+    g = next(c for c in (pow(x, (Q - 1) // m, Q) for x in range(2, Q)) if pow(c, m // 2, Q) == Q - 1)
+    best, x, g2 = g, g, g * g % Q
+    for _ in range(1, m, 2):
+        best = min(best, x)
+        x = x * g2 % Q
+    return best
+
+
+def derive_params(row: BinFHEContextParams, method: str, device: int = -1) -> Params:
+    if method not in (MKNTRU, MKNTRU_B, MKNTRU_LWE):
+        raise config_error("method is invalid")  # binfhe-base-scheme.h:137-151
+    N = row.cyclOrder // 2
+    Q = previous_prime(first_prime(row.numberBits, row.cyclOrder), row.cyclOrder)  # binfhecontext.cpp:157-158
+    psi = root_of_unity(row.cyclOrder, Q)
+    if row.gadgetBase & (row.gadgetBase - 1):
+        raise config_error("Gadget base should be a power of two.")  # mk-cryptoparameters.h:138-139
+    digitsG = int(ceil(log(float(Q)) / log(float(row.gadgetBase))))  # mk-cryptoparameters.h:141-142
+    dKS = int(ceil(log(float(row.modKS)) / log(float(row.baseKS))))  # mntru-pke.cpp:771
+    return Params(k=row.numUser, N=N, Q=Q, psi=psi, q=row.mod, qKS=row.modKS, n=row.latticeParam,
+                  baseG_log2=row.gadgetBase.bit_length() - 1, digitsG=digitsG, baseKS=row.baseKS, dKS=dKS,
+                  variant=_lib.MKFHE_VARIANT_XZW if method == MKNTRU else _lib.MKFHE_VARIANT_XZW_B,
+                  scheme=_lib.MKFHE_SCHEME_MKLWE if method == MKNTRU_LWE else _lib.MKFHE_SCHEME_MNTRU,
+                  device=device)
+
+
+def _ptr(a):
+    """host numpy array or torch tensor (host or CUDA) -> (void*, words)"""
+    if a is None:
+        return None, 0
+    if isinstance(a, np.ndarray):
+        if a.dtype != np.uint32 or not a.flags["C_CONTIGUOUS"]:
+            raise config_error("expected a C-contiguous uint32 array")
+        return C.c_void_p(a.ctypes.data), a.size
+    # torch tensor: int32/uint32 storage, contiguous
+    if not a.is_contiguous() or a.element_size() != 4:
+        raise config_error("expected a contiguous 32-bit tensor")
+    return C.c_void_p(a.data_ptr()), a.numel()
+
+
+class BinFHEContext:
+    """GPU context for one parameter set on one device (one per GPU; calls are serialised by the caller)."""
+
+    def __init__(self):
+        self._L = None
+        self._h = None
+        self.params: Params | None = None
+
+    # -- BinFHEContext::GenerateBinFHEContext(BINFHE_PARAMSET, BINFHE_METHOD), binfhecontext.cpp:83-194
+    def GenerateBinFHEContext(self, paramset, method: str, device: int = -1):
+        row = PARAMSETS.get(paramset) if isinstance(paramset, str) else paramset
+        if row is None:
+            raise config_error(f"ERROR: Unknown parameter set [{paramset}] for FHEW.")  # binfhecontext.cpp:149-152
+        return self.GenerateFromParams(derive_params(row, method, device))
+
+    def GenerateFromParams(self, p: Params):
+        self.close()
+        self._L = _lib.load()
+        h = C.c_void_p()
+        rc = self._L.mkfhe_ctx_create(C.byref(p), C.byref(h))
+        if rc != 0:
+            raise MkfheError(rc, "mkfhe_ctx_create", self._L.mkfhe_last_error(None).decode())
+        self._h, self.params = h, p
+        return self
+
+    def close(self):
+        if self._h:
+            self._L.mkfhe_ctx_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc, what):
+        if rc != 0:
+            raise MkfheError(rc, what, self._L.mkfhe_last_error(self._h).decode())
+
+    @property
+    def is_lwe(self) -> bool:
+        return self.params.scheme == _lib.MKFHE_SCHEME_MKLWE
+
+    # -- key upload: the flattened bytes of what BinFHEContext::MKBTKeyGen / ctGateGen produce in the reference
+    def LoadKeys(self, bk, pkey, ksk=None, kskA=None, kskB=None, ctnand=None):
+        p, n = _ptr(bk)
+        self._ck(self._L.mkfhe_load_bk(self._h, p, n), "mkfhe_load_bk")
+        p, n = _ptr(pkey)
+        self._ck(self._L.mkfhe_load_pkey(self._h, p, n), "mkfhe_load_pkey")
+        if ksk is not None:
+            p, n = _ptr(ksk)
+            self._ck(self._L.mkfhe_load_ksk_mntru(self._h, p, n), "mkfhe_load_ksk_mntru")
+        if kskA is not None:
+            pa, na = _ptr(kskA)
+            pb, nb = _ptr(kskB)
+            self._ck(self._L.mkfhe_load_ksk_mklwe(self._h, pa, na, pb, nb), "mkfhe_load_ksk_mklwe")
+        if ctnand is not None:
+            p, n = _ptr(ctnand)
+            self._ck(self._L.mkfhe_load_ctnand(self._h, p, n), "mkfhe_load_ctnand")
+
+    # -- BinFHEContext::EvalBinGate(gate, ct1, ct2), binfhecontext.cpp:415-426, batched over the leading axis
+    def EvalBinGate(self, gate, ct1, ct2, b1=None, b2=None):
+        """ct1, ct2: uint32 [B, k, n] (or [k, n]); b1, b2: uint32 [B] for MKNTRU_LWE.  Returns out (and bout)."""
+        if gate != NAND:
+            raise config_error("Support NAND gate Only")  # binfhe-base-scheme.cpp:341-342
+        if ct1 is ct2:
+            raise config_error("Input ciphertexts should be independant")  # binfhe-base-scheme.cpp:382-383,471-472
+        P = self.params
+        c1 = np.ascontiguousarray(ct1, dtype=np.uint32).reshape(-1, P.k, P.n)
+        c2 = np.ascontiguousarray(ct2, dtype=np.uint32).reshape(-1, P.k, P.n)
+        if c1.shape != c2.shape:
+            raise config_error("ciphertext shapes differ")
+        B = c1.shape[0]
+        out = np.empty_like(c1)
+        if self.is_lwe:
+            bb1 = np.ascontiguousarray(b1, dtype=np.uint32).reshape(B)
+            bb2 = np.ascontiguousarray(b2, dtype=np.uint32).reshape(B)
+            bout = np.empty(B, dtype=np.uint32)
+            self._ck(self._L.mkfhe_eval_nand(self._h, _ptr(c1)[0], _ptr(bb1)[0], _ptr(c2)[0], _ptr(bb2)[0], _ptr(out)[0],
+                                             _ptr(bout)[0], B), "mkfhe_eval_nand")
+            return out.reshape(np.shape(ct1)), (bout if np.ndim(b1) else int(bout[0]))
+        self._ck(self._L.mkfhe_eval_nand(self._h, _ptr(c1)[0], None, _ptr(c2)[0], None, _ptr(out)[0], None, B),
+                 "mkfhe_eval_nand")
+        return out.reshape(np.shape(ct1))
+
+    def EvalBinGateDevice(self, ct1, ct2, out, b1=None, b2=None, bout=None):
+        """Same on CUDA tensors (int32 storage, [B, k, n]); asynchronous on the context's stream."""
+        B = ct1.numel() // (self.params.k * self.params.n)
+        g = lambda t: None if t is None else C.c_void_p(t.data_ptr())
+        self._ck(self._L.mkfhe_eval_nand_dev(self._h, g(ct1), g(b1), g(ct2), g(b2), g(out), g(bout), B), "mkfhe_eval_nand_dev")
+
+    # -- UniEncAccumulator::EvalAcc (mk-acc.h:67-71), batched
+    def EvalAcc(self, acc, rot, rot_mod: int):
+        P = self.params
+        a = np.ascontiguousarray(acc, dtype=np.uint32).reshape(-1, P.k, P.N)
+        r = np.ascontiguousarray(rot, dtype=np.uint32).reshape(-1, P.k, P.n)
+        out = np.empty_like(a)
+        self._ck(self._L.mkfhe_eval_acc(self._h, _ptr(a)[0], _ptr(r)[0], int(rot_mod), _ptr(out)[0], a.shape[0]), "mkfhe_eval_acc")
+        return out.reshape(np.shape(acc))
+
+    # -- NativePoly::SetFormat, batched
+    def NTT(self, polys, inverse: bool = False):
+        a = np.ascontiguousarray(polys, dtype=np.uint32).copy()
+        self._ck(self._L.mkfhe_ntt(self._h, _ptr(a)[0], a.size // self.params.N, 1 if inverse else 0), "mkfhe_ntt")
+        return a
+
+    def NTTDevice(self, polys, inverse: bool = False):
+        self._ck(self._L.mkfhe_ntt_dev(self._h, C.c_void_p(polys.data_ptr()), polys.numel() // self.params.N,
+                                       1 if inverse else 0), "mkfhe_ntt_dev")
+
+    def SignedDigitDecompose(self, polys):
+        a = np.ascontiguousarray(polys, dtype=np.uint32).reshape(-1, self.params.N)
+        out = np.empty((a.shape[0], self.params.digitsG - 1, self.params.N), dtype=np.uint32)
+        self._ck(self._L.mkfhe_decompose(self._h, _ptr(a)[0], _ptr(out)[0], a.shape[0]), "mkfhe_decompose")
+        return out
+
+    # -- plumbing
+    def set_stream(self, cuda_stream_handle: int | None):
+        self._ck(self._L.mkfhe_ctx_set_stream(self._h, C.c_void_p(cuda_stream_handle) if cuda_stream_handle else None),
+                 "mkfhe_ctx_set_stream")
+
+    def synchronize(self):
+        self._ck(self._L.mkfhe_ctx_synchronize(self._h), "mkfhe_ctx_synchronize")
+
+    def launch_count(self) -> int:
+        return int(self._L.mkfhe_launch_count(self._h))
+
+    def device_bytes(self) -> int:
+        return int(self._L.mkfhe_device_bytes(self._h))
+
+    def measure_int32_peak(self) -> float:
+        v = C.c_double(0)
+        self._ck(self._L.mkfhe_measure_int32_peak(self._h, C.byref(v)), "mkfhe_measure_int32_peak")
+        return float(v.value)

@@ -1,0 +1,419 @@
+// generic_kernels.cuh -- parameter-generic kernels (any power-of-two N <= 2048, any k, any digit count).
+//
+// One CTA owns one gate.  The accumulator lives in shared memory for the whole blind rotation (k*n sequential steps), in
+// COEFFICIENT form: the reference keeps acc in EVALUATION form and multiplies by NTT(X^c - 1) (mk-acc-xzw.cpp:336-338)
+// only to transform back at the top of HbProd (:240-243); here X^c * a is a negacyclic shift of the coefficient vector,
+// which is the same ring element, so the digits fed to SignedDigitDecompose -- the only non-linear step -- are identical
+// and the result is bit-exact (verified against the oracle, which follows the reference's formulation literally).
+//
+// These kernels are the correctness baseline and the path for parameter sets the specialised N = 2048 kernels do not
+// cover (fast_kernels.cuh).
+#pragma once
+#include <cstdint>
+
+#include "modarith.cuh"
+
+namespace mkfhe {
+
+struct DevCtx {
+    uint32_t k, N, logN, n, ell, gbits, variant, scheme, S;
+    uint32_t q, qKS, baseKS, dKS;
+    Mod mod;
+    uint32_t one_mont;   // R mod Q      (1 in Montgomery form)
+    uint32_t ninv_mont;  // N^-1 * R mod Q
+    const uint32_t* tw;      // [N]  psi^i at index bitrev(i), Montgomery form (transformnat-impl.h:721-727)
+    const uint32_t* twi;     // [N]  psi^-i likewise
+    const uint32_t* psipow;  // [2N] psi^e, Montgomery form: NTT(X^c) at slot j is psi^(c*(2*bitrev(j)+1) mod 2N)
+    const uint32_t* bk;      // bootstrapping key, boundary layout, Montgomery form
+    const uint32_t* pkey;    // [k][ell][N], Montgomery form
+};
+
+// ---- transforms on polynomials resident in shared memory; all threads of the CTA participate ----
+// forward: Cooley-Tukey, natural -> bit-reversed (transformnat-impl.h:299-354).  Entry: data visible (caller synced).
+__device__ __forceinline__ void ntt_fwd_smem(uint32_t* x, uint32_t npoly, const DevCtx& P) {
+    const uint32_t N = P.N, half = N >> 1, total = npoly * half;
+    uint32_t logt = P.logN - 1;
+    for (uint32_t m = 1; m < N; m <<= 1, --logt) {
+        const uint32_t t = 1u << logt;
+        for (uint32_t idx = threadIdx.x; idx < total; idx += blockDim.x) {
+            const uint32_t poly = idx >> (P.logN - 1), b = idx & (half - 1);
+            const uint32_t i = b >> logt, j = ((i << logt) << 1) + (b & (t - 1));
+            uint32_t* y = x + poly * N;
+            const uint32_t w = __ldg(P.tw + m + i);
+            const uint32_t lo = y[j], of = montmul(y[j + t], w, P.mod);
+            y[j] = addmod(lo, of, P.mod.Q);
+            y[j + t] = submod(lo, of, P.mod.Q);
+        }
+        __syncthreads();
+    }
+}
+// inverse: Gentleman-Sande, bit-reversed -> natural (transformnat-impl.h:491-552), WITHOUT the N^-1 scaling (the consumer
+// multiplies by ninv_mont; the reference folds it into its first stage -- same value mod Q).
+__device__ __forceinline__ void ntt_inv_smem(uint32_t* x, uint32_t npoly, const DevCtx& P) {
+    const uint32_t N = P.N, half = N >> 1, total = npoly * half;
+    uint32_t logt = 0;
+    for (uint32_t m = half; m >= 1; m >>= 1, ++logt) {
+        const uint32_t t = 1u << logt;
+        for (uint32_t idx = threadIdx.x; idx < total; idx += blockDim.x) {
+            const uint32_t poly = idx >> (P.logN - 1), b = idx & (half - 1);
+            const uint32_t i = b >> logt, j = ((i << logt) << 1) + (b & (t - 1));
+            uint32_t* y = x + poly * N;
+            const uint32_t w = __ldg(P.twi + m + i);
+            const uint32_t lo = y[j], hi = y[j + t];
+            y[j] = addmod(lo, hi, P.mod.Q);
+            y[j + t] = montmul(submod(lo, hi, P.mod.Q), w, P.mod);
+        }
+        __syncthreads();
+    }
+}
+
+// coefficient e of (X^c - 1) * a, canonical; c in [0, 2N)
+__device__ __forceinline__ uint32_t rot_sub(const uint32_t* a, uint32_t c, uint32_t e, uint32_t N, uint32_t Q) {
+    const uint32_t cm = c & (N - 1);
+    const bool neg0 = c >= N;
+    const bool wrap = e < cm;
+    const uint32_t src = wrap ? e + N - cm : e - cm;
+    const uint32_t v = a[src];
+    const uint32_t rv = (neg0 != wrap) ? (v == 0 ? 0u : Q - v) : v;
+    return submod(rv, a[e], Q);
+}
+
+// The (d | f) column of the evaluation key used by HbProd at slot e, Montgomery form, assembled on the fly:
+//   XZW   step > 0 : ev1 - ev2*(X^-c - 1) - ev2 = ev1 - ev2*X^-c                         (mk-acc-xzw.cpp:322-325)
+//   XZW   step 0   : evs + ev1*(X^c - 1) + ev2*(X^-c - 1)                                (mk-acc-xzw.cpp:370-377)
+//   XZW_B step > 0 : ev1                                                                 (mk-acc-xzw_B.cpp:306-309)
+//   XZW_B step 0   : evs + ev1*(X^c - 1)                                                 (mk-acc-xzw_B.cpp:366-369)
+struct KeyView {
+    const uint32_t *ev1, *ev2, *evs;
+    uint32_t xpos, xneg;  // X^c and X^-c evaluated at this slot (Montgomery form)
+    bool first;
+};
+__device__ __forceinline__ uint32_t key_elem(const KeyView& kv, uint32_t off, const DevCtx& P) {
+    const uint32_t Q = P.mod.Q;
+    const uint32_t e1 = __ldg(kv.ev1 + off);
+    if (P.variant == 0) {
+        const uint32_t e2 = __ldg(kv.ev2 + off);
+        if (!kv.first) return submod(e1, montmul(e2, kv.xneg, P.mod), Q);
+        uint32_t r = __ldg(kv.evs + off);
+        r = addmod(r, montmul(e1, submod(kv.xpos, P.one_mont, Q), P.mod), Q);
+        return addmod(r, montmul(e2, submod(kv.xneg, P.one_mont, Q), P.mod), Q);
+    }
+    if (!kv.first) return e1;
+    return addmod(__ldg(kv.evs + off), montmul(e1, submod(kv.xpos, P.one_mont, Q), P.mod), Q);
+}
+
+struct GateIO {
+    // EvalAcc surface
+    const uint32_t* acc_in;   // [B][k][N] EVALUATION
+    const uint32_t* rot;      // [B][k][n]
+    uint32_t rot_mod;
+    uint32_t* acc_out;        // [B][k][N] EVALUATION
+    // EvalBinGate surface
+    const uint32_t *ct1, *ct2, *b1, *b2, *ctnand;
+    uint32_t* ms_out;         // [B][k][N] mod qKS  (extracted + modulus-switched)
+};
+
+// Shared memory: a[k][N] | D[ell][N] | V[N] | X[N] | crot[k*n] (u16)
+template <bool GATE>
+__global__ void blind_rotate_generic(const DevCtx P, const GateIO io) {
+    extern __shared__ uint32_t sm[];
+    const uint32_t N = P.N, Q = P.mod.Q, k = P.k, n = P.n, ell = P.ell, M = 2 * N;
+    uint32_t* a = sm;
+    uint32_t* D = a + k * N;
+    uint32_t* V = D + ell * N;
+    uint32_t* X = V + N;
+    uint16_t* crot = reinterpret_cast<uint16_t*>(X + N);
+    const uint32_t g = blockIdx.x, tid = threadIdx.x, T = blockDim.x;
+
+    // ---------------- prologue ----------------
+    if (GATE) {
+        const uint32_t* c1 = io.ct1 + size_t(g) * k * n;
+        const uint32_t* c2 = io.ct2 + size_t(g) * k * n;
+        uint32_t b_hat = 0;
+        if (P.scheme == 0) {
+            // ct_temp = ctNAND - (ct1 + ct2) mod q (binfhe-base-scheme.cpp:485-490); c = ct*2N/q (mk-acc-xzw.cpp:110)
+            for (uint32_t s = tid; s < k * n; s += T) {
+                const uint32_t r = submod(__ldg(io.ctnand + s), addmod(c1[s], c2[s], P.q), P.q);
+                crot[s] = static_cast<uint16_t>((r * M) / P.q);
+            }
+        } else {
+            // ct_temp = (0, 5q/8) - (ct1 + ct2); ModSwitch to 2N; GetAneg (binfhe-base-scheme.cpp:393-406, mklwe-ciphertext.h:86-96)
+            for (uint32_t s = tid; s < k * n; s += T) {
+                const uint32_t av = submod(0u, addmod(c1[s], c2[s], P.q), P.q);
+                const uint32_t ams = round_qQ(av, M, P.q);
+                crot[s] = static_cast<uint16_t>((M - ams) & (M - 1));
+            }
+            const uint32_t bt = submod((5u * P.q / 8u) % P.q, addmod(io.b1[g], io.b2[g], P.q), P.q);
+            b_hat = round_qQ(bt, M, P.q);  // b*2N/q with q == 2N (binfhe-base-scheme.cpp:1027)
+        }
+        // initial accumulator in COEFFICIENT form (binfhe-base-scheme.cpp:1018-1055 MKLWE, :1086-1110 MNTRU)
+        const uint32_t Q2p = Q / 8 + 1, Q2pNeg = Q - Q2p;
+        for (uint32_t e = tid; e < k * N; e += T) {
+            uint32_t v = 0;
+            if (e < N) {
+                if (P.scheme == 0) {
+                    v = e < N / 2 ? Q2pNeg : Q2p;
+                } else {
+                    const uint32_t j = (e + M - b_hat) & (N - 1);
+                    const uint32_t Rx = j < N / 2 ? Q2p : Q2pNeg;
+                    const uint32_t index = b_hat + j;
+                    v = (index >= N && index < M) ? Q - Rx : Rx;
+                }
+            }
+            a[e] = v;
+        }
+        __syncthreads();
+    } else {
+        const uint32_t* r = io.rot + size_t(g) * k * n;
+        for (uint32_t s = tid; s < k * n; s += T) {
+            const uint32_t v = r[s];
+            crot[s] = static_cast<uint16_t>(P.variant == 0 ? ((v * M) / io.rot_mod) % M : v % M);
+        }
+        const uint32_t* ai = io.acc_in + size_t(g) * k * N;
+        for (uint32_t e = tid; e < k * N; e += T) a[e] = ai[e];
+        __syncthreads();
+        ntt_inv_smem(a, k, P);
+        for (uint32_t e = tid; e < k * N; e += T) a[e] = montmul(a[e], P.ninv_mont, P.mod);
+        __syncthreads();
+    }
+
+    // ---------------- k*n sequential steps (mk-acc-xzw.cpp:106-129) ----------------
+    const size_t per = size_t(ell) * 2 * N;
+    const uint32_t* evs = P.bk + size_t(k) * P.S * n * per;
+    for (uint32_t s = 0; s < k * n; ++s) {
+        const uint32_t c = crot[s];
+        if (s > 0 && c == 0) continue;  // X^0 - 1 = 0: HbProd(0) = 0, the step leaves acc unchanged
+        const uint32_t uidx = s / n, i = s - uidx * n;
+        const uint32_t cneg = (M - c) & (M - 1);
+        KeyView kv;
+        kv.ev1 = P.bk + (size_t(uidx * P.S + 0) * n + i) * per;
+        kv.ev2 = P.S == 2 ? P.bk + (size_t(uidx * P.S + 1) * n + i) * per : nullptr;
+        kv.evs = evs;
+        kv.first = (s == 0);
+
+        for (uint32_t pp = 0; pp < k; ++pp) {
+            // parties other than the key owner first; the owner last (its f-term needs the complete sumV)
+            const uint32_t p = (pp + 1 < k) ? (pp < uidx ? pp : pp + 1) : uidx;
+            const uint32_t* ap = a + p * N;
+            for (uint32_t e = tid; e < N; e += T) {
+                const uint32_t t = (s == 0) ? ap[e] : rot_sub(ap, c, e, N, Q);
+                Decomposer dec(t, Q, P.gbits);
+                for (uint32_t j = 0; j < ell; ++j) {
+                    const int32_t r = dec.next();
+                    D[j * N + e] = r < 0 ? static_cast<uint32_t>(r + static_cast<int32_t>(Q)) : static_cast<uint32_t>(r);
+                }
+            }
+            __syncthreads();
+            ntt_fwd_smem(D, ell, P);
+            for (uint32_t e = tid; e < N; e += T) {
+                const uint32_t ex = 2 * (__brev(e) >> (32 - P.logN)) + 1;
+                kv.xpos = __ldg(P.psipow + ((c * ex) & (M - 1)));
+                kv.xneg = __ldg(P.psipow + ((cneg * ex) & (M - 1)));
+                uint64_t accn = 0, vv = 0;
+                for (uint32_t j = 0; j < ell; ++j) {
+                    const uint32_t dj = key_elem(kv, (j * 2 + 0) * N + e, P);
+                    const uint32_t x = D[j * N + e];
+                    accn += static_cast<uint64_t>(x) * dj;
+                    vv += static_cast<uint64_t>(x) * __ldg(P.pkey + (size_t(p) * ell + j) * N + e);
+                }
+                const uint32_t vr = montredc(vv, P.mod);
+                V[e] = pp == 0 ? vr : addmod(V[e], vr, Q);
+                X[e] = montredc(accn, P.mod);
+            }
+            __syncthreads();
+            if (pp + 1 < k) {
+                ntt_inv_smem(X, 1, P);
+                uint32_t* aw = a + p * N;
+                for (uint32_t e = tid; e < N; e += T) {
+                    const uint32_t val = montmul(X[e], P.ninv_mont, P.mod);
+                    aw[e] = (s == 0) ? val : addmod(aw[e], val, Q);
+                }
+                // no barrier needed here: the next writers of D/X are behind the barrier that follows phase 1 of the next party
+            }
+        }
+        // sumV -> coefficients -> digits -> <g^-1(v), f>  (mk-acc-xzw.cpp:273-289)
+        ntt_inv_smem(V, 1, P);
+        for (uint32_t e = tid; e < N; e += T) {
+            const uint32_t t = montmul(V[e], P.ninv_mont, P.mod);
+            Decomposer dec(t, Q, P.gbits);
+            for (uint32_t j = 0; j < ell; ++j) {
+                const int32_t r = dec.next();
+                D[j * N + e] = r < 0 ? static_cast<uint32_t>(r + static_cast<int32_t>(Q)) : static_cast<uint32_t>(r);
+            }
+        }
+        __syncthreads();
+        ntt_fwd_smem(D, ell, P);
+        for (uint32_t e = tid; e < N; e += T) {
+            const uint32_t ex = 2 * (__brev(e) >> (32 - P.logN)) + 1;
+            kv.xpos = __ldg(P.psipow + ((c * ex) & (M - 1)));
+            kv.xneg = __ldg(P.psipow + ((cneg * ex) & (M - 1)));
+            uint64_t w = 0;
+            for (uint32_t j = 0; j < ell; ++j) w += static_cast<uint64_t>(D[j * N + e]) * key_elem(kv, (j * 2 + 1) * N + e, P);
+            X[e] = addmod(X[e], montredc(w, P.mod), Q);
+        }
+        __syncthreads();
+        ntt_inv_smem(X, 1, P);
+        {
+            uint32_t* aw = a + uidx * N;
+            for (uint32_t e = tid; e < N; e += T) {
+                const uint32_t val = montmul(X[e], P.ninv_mont, P.mod);
+                aw[e] = (s == 0) ? val : addmod(aw[e], val, Q);
+            }
+        }
+        __syncthreads();
+    }
+
+    // ---------------- epilogue ----------------
+    if (GATE) {
+        // Transpose + INTT = [a0, -a_{N-1}, ..., -a_1] (poly-impl.h:349-356); then RoundqQ to qKS (mntru-pke.cpp:359-374)
+        uint32_t* out = io.ms_out + size_t(g) * k * N;
+        for (uint32_t x = tid; x < k * N; x += T) {
+            const uint32_t u = x >> P.logN, e = x & (N - 1);
+            const uint32_t v = e == 0 ? a[u * N] : a[u * N + N - e];
+            const uint32_t ext = (e == 0 || v == 0) ? v : Q - v;
+            out[x] = round_qQ(ext, P.qKS, Q);
+        }
+    } else {
+        ntt_fwd_smem(a, k, P);
+        uint32_t* out = io.acc_out + size_t(g) * k * N;
+        for (uint32_t e = tid; e < k * N; e += T) out[e] = a[e];
+    }
+}
+
+// ---- standalone batched NTT: one CTA per polynomial (config 5 and the mkfhe_ntt entry point) ----
+__global__ void ntt_batch_generic(const DevCtx P, uint32_t* polys, int inverse) {
+    extern __shared__ uint32_t sm[];
+    uint32_t* x = polys + size_t(blockIdx.x) * P.N;
+    for (uint32_t e = threadIdx.x; e < P.N; e += blockDim.x) sm[e] = x[e];
+    __syncthreads();
+    if (!inverse) {
+        ntt_fwd_smem(sm, 1, P);
+        for (uint32_t e = threadIdx.x; e < P.N; e += blockDim.x) x[e] = sm[e];
+    } else {
+        ntt_inv_smem(sm, 1, P);
+        for (uint32_t e = threadIdx.x; e < P.N; e += blockDim.x) x[e] = montmul(sm[e], P.ninv_mont, P.mod);
+    }
+}
+
+// ---- SignedDigitDecompose, elementwise (mk-acc.cpp:54-80) ----
+__global__ void decompose_generic(const DevCtx P, const uint32_t* in, uint32_t* out, uint64_t total) {
+    const uint64_t x = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;
+    if (x >= total) return;
+    const uint64_t b = x >> P.logN, e = x & (P.N - 1);
+    Decomposer dec(in[x], P.mod.Q, P.gbits);
+    for (uint32_t j = 0; j < P.ell; ++j) {
+        const int32_t r = dec.next();
+        out[(b * P.ell + j) * P.N + e] = r < 0 ? static_cast<uint32_t>(r + static_cast<int32_t>(P.mod.Q)) : static_cast<uint32_t>(r);
+    }
+}
+
+// ---- plain residues -> Montgomery form (key upload) ----
+__global__ void to_montgomery(uint32_t* dst, const uint32_t* src, uint64_t words, Mod mod, uint32_t r2) {
+    for (uint64_t x = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x; x < words; x += uint64_t(gridDim.x) * blockDim.x)
+        dst[x] = montmul(src[x], r2, mod);
+}
+
+// ---- MNTRU key switch: out[g][u][x] = sum_l digit_l(ms[g][u]) * KSK[u][l][x] mod qKS  (mntru-pke.cpp:763-823) ----
+// Integer GEMM, [gates x N*dKS] x [N*dKS x n] per party.  64 x 64 output tile per CTA, 4 x 4 per thread, K-chunks of 32.
+__global__ void __launch_bounds__(256) keyswitch_mntru_generic(const DevCtx P, const uint32_t* __restrict__ ms,
+                                                               const uint32_t* __restrict__ ksk, uint32_t* __restrict__ out,
+                                                               uint32_t B) {
+    __shared__ uint32_t Ds[32][64 + 1];  // [l][gate]
+    __shared__ uint32_t Ks[32][64];      // [l][col]
+    const uint32_t u = blockIdx.z, g0 = blockIdx.y * 64, x0 = blockIdx.x * 64;
+    const uint32_t tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    const uint32_t L = P.N * P.dKS, n = P.n;
+    unsigned long long acc[4][4] = {};
+    for (uint32_t l0 = 0; l0 < L; l0 += 32) {
+        for (uint32_t t = threadIdx.x; t < 32 * 64; t += 256) {
+            const uint32_t gl = t >> 5, ll = t & 31, g = g0 + gl, l = l0 + ll;
+            uint32_t dig = 0;
+            if (g < B && l < L) {
+                uint32_t v = ms[(size_t(g) * P.k + u) * P.N + l / P.dKS];
+                for (uint32_t j = l % P.dKS; j > 0; --j) v /= P.baseKS;
+                dig = v % P.baseKS;
+            }
+            Ds[ll][gl] = dig;
+        }
+        for (uint32_t t = threadIdx.x; t < 32 * 64; t += 256) {
+            const uint32_t ll = t >> 6, xl = t & 63, l = l0 + ll, x = x0 + xl;
+            Ks[ll][xl] = (l < L && x < n) ? ksk[(size_t(u) * L + l) * n + x] : 0u;
+        }
+        __syncthreads();
+#pragma unroll 8
+        for (uint32_t ll = 0; ll < 32; ++ll) {
+            uint32_t dv[4], kvv[4];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) dv[r] = Ds[ll][ty * 4 + r];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) kvv[c] = Ks[ll][tx * 4 + c];
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) acc[r][c] += static_cast<unsigned long long>(dv[r]) * kvv[c];
+        }
+        __syncthreads();
+    }
+    for (int r = 0; r < 4; ++r)
+        for (int c = 0; c < 4; ++c) {
+            const uint32_t g = g0 + ty * 4 + r, x = x0 + tx * 4 + c;
+            if (g < B && x < n) out[(size_t(g) * P.k + u) * n + x] = static_cast<uint32_t>(acc[r][c] % P.qKS);
+        }
+}
+
+// ---- MKLWE key switch (mklwe-pke.cpp:260-290): gather-accumulate; partial sums over i-chunks combined with atomics ----
+// raw[g][u][x] += sum_{i in chunk, j} A[u][i][digit_j(ms[g][u][i])][j][x] ; braw[g] += sum B[...]
+__global__ void keyswitch_mklwe_generic(const DevCtx P, const uint32_t* __restrict__ ms, const uint32_t* __restrict__ A,
+                                        const uint32_t* __restrict__ Bk, uint32_t* raw, uint32_t* braw, uint32_t ichunk) {
+    const uint32_t g = blockIdx.x, u = blockIdx.y, i0 = blockIdx.z * ichunk;
+    const uint32_t i1 = min(P.N, i0 + ichunk), n = P.n;
+    const uint32_t* msr = ms + (size_t(g) * P.k + u) * P.N;
+    uint32_t bacc = 0;
+    for (uint32_t x0 = 0; x0 < n; x0 += blockDim.x) {
+        const uint32_t x = x0 + threadIdx.x;
+        uint32_t acc = 0;
+        for (uint32_t i = i0; i < i1; ++i) {
+            uint32_t v = msr[i];
+            for (uint32_t j = 0; j < P.dKS; ++j) {
+                const uint32_t a0 = v % P.baseKS;
+                v /= P.baseKS;
+                const size_t row = ((size_t(u) * P.N + i) * P.baseKS + a0) * P.dKS + j;
+                if (x < n) acc += __ldg(A + row * n + x);
+                if (x0 == 0 && threadIdx.x == 0) bacc += __ldg(Bk + row);
+            }
+        }
+        if (x < n) atomicAdd(raw + (size_t(g) * P.k + u) * n + x, acc % P.qKS);
+    }
+    if (threadIdx.x == 0) atomicAdd(braw + g, bacc % P.qKS);
+}
+// out = 0 - raw mod qKS ; bout = RoundqQ(Q/8+1) - braw mod qKS (binfhe-base-scheme.cpp:450-458)
+__global__ void keyswitch_mklwe_finish(const DevCtx P, const uint32_t* raw, const uint32_t* braw, uint32_t* out, uint32_t* bout,
+                                       uint64_t total, uint32_t B) {
+    const uint64_t x = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;
+    if (x < total) {
+        const uint32_t r = raw[x] % P.qKS;
+        out[x] = r == 0 ? 0u : P.qKS - r;
+    }
+    if (x < B) {
+        const uint32_t b0 = round_qQ((P.mod.Q >> 3) + 1, P.qKS, P.mod.Q);
+        bout[x] = submod(b0, braw[x] % P.qKS, P.qKS);
+    }
+}
+
+// ---- INT32 pipe micro-benchmark: 8 independent dependent-IMAD chains per thread ----
+__global__ void int32_peak_kernel(uint32_t* sink, uint32_t iters, uint32_t seed) {
+    uint32_t a0 = seed + threadIdx.x, a1 = a0 ^ 0x9e3779b9u, a2 = a0 * 3u, a3 = a0 + 17u;
+    uint32_t a4 = a0 ^ 0x85ebca6bu, a5 = a0 * 5u, a6 = a0 + 101u, a7 = a0 ^ 0xc2b2ae35u;
+    const uint32_t m = seed | 1u, c = blockIdx.x + 12345u;
+    for (uint32_t i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+            a0 = a0 * m + c; a1 = a1 * m + c; a2 = a2 * m + c; a3 = a3 * m + c;
+            a4 = a4 * m + c; a5 = a5 * m + c; a6 = a6 * m + c; a7 = a7 * m + c;
+        }
+    }
+    const uint32_t r = a0 ^ a1 ^ a2 ^ a3 ^ a4 ^ a5 ^ a6 ^ a7;
+    if (r == 0x12345678u) sink[0] = r;  // never true in practice; keeps the chains alive
+}
+
+}  // namespace mkfhe

@@ -1,0 +1,516 @@
+// mkfhe_b200.cu -- context, key upload and the C ABI of include/mkfhe_b200.h.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -shared -Xcompiler -fPIC (see mkfhe_b200/build.py).
+//
+// There is no CPU fallback in this library: every entry point that computes launches CUDA kernels.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/mkfhe_b200.h"
+#include "fast_kernels.cuh"
+#include "generic_kernels.cuh"
+
+using namespace mkfhe;
+
+#define MKFHE_VERSION_STR "mkfhe_b200 0.1.0 sm_100a"
+
+struct mkfhe_ctx {
+    mkfhe_params p{};
+    DevCtx d{};
+    int device{0};
+    cudaStream_t stream{nullptr};
+    cudaStream_t own_stream{nullptr};
+    std::string err;
+    uint64_t launches{0};
+    uint64_t dev_bytes{0};
+    // tables
+    uint32_t *tw{nullptr}, *twi{nullptr}, *psipow{nullptr};
+    // keys
+    uint32_t *bk{nullptr}, *pkey{nullptr}, *ksk_mntru{nullptr}, *kskA{nullptr}, *kskB{nullptr}, *ctnand{nullptr};
+    // workspaces (grown on demand)
+    uint32_t* ws_ms{nullptr};
+    size_t ws_ms_words{0};
+    uint32_t* ws_raw{nullptr};
+    size_t ws_raw_words{0};
+    uint32_t* ws_io{nullptr};
+    size_t ws_io_words{0};
+    uint32_t r2{0};  // 2^64 mod Q
+    FastState fast{};
+    bool use_fast{false};
+};
+
+static thread_local std::string g_create_error;
+
+static int fail(mkfhe_ctx* c, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (c)
+        c->err = buf;
+    else
+        g_create_error = buf;
+    return code;
+}
+
+#define CU(call)                                                                                         \
+    do {                                                                                                 \
+        cudaError_t e_ = (call);                                                                         \
+        if (e_ != cudaSuccess)                                                                           \
+            return fail(ctx, MKFHE_ECUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+
+// ---- host number theory (table construction only) ----
+static uint32_t h_mulmod(uint32_t a, uint32_t b, uint32_t m) { return uint32_t((uint64_t(a) * b) % m); }
+static uint32_t h_powmod(uint32_t a, uint64_t e, uint32_t m) {
+    uint64_t r = 1, b = a % m;
+    while (e) {
+        if (e & 1) r = (r * b) % m;
+        b = (b * b) % m;
+        e >>= 1;
+    }
+    return uint32_t(r);
+}
+static uint32_t h_bitrev(uint32_t x, uint32_t bits) {
+    uint32_t r = 0;
+    for (uint32_t i = 0; i < bits; ++i) r |= ((x >> i) & 1u) << (bits - 1 - i);
+    return r;
+}
+static bool h_is_prime(uint32_t n) {
+    if (n < 2) return false;
+    for (uint64_t d = 2; d * d <= n; ++d)
+        if (n % d == 0) return false;
+    return true;
+}
+
+template <class T>
+static int dev_alloc(mkfhe_ctx* ctx, T** p, size_t count) {
+    CU(cudaMalloc(reinterpret_cast<void**>(p), count * sizeof(T)));
+    ctx->dev_bytes += count * sizeof(T);
+    return MKFHE_OK;
+}
+static int grow(mkfhe_ctx* ctx, uint32_t** p, size_t* have, size_t want) {
+    if (*have >= want) return MKFHE_OK;
+    if (*p) {
+        CU(cudaStreamSynchronize(ctx->stream));
+        CU(cudaFree(*p));
+        ctx->dev_bytes -= *have * sizeof(uint32_t);
+        *p = nullptr;
+        *have = 0;
+    }
+    CU(cudaMalloc(reinterpret_cast<void**>(p), want * sizeof(uint32_t)));
+    ctx->dev_bytes += want * sizeof(uint32_t);
+    *have = want;
+    return MKFHE_OK;
+}
+
+static size_t bk_words(const mkfhe_params& p) {
+    const size_t S = p.variant == MKFHE_VARIANT_XZW ? 2 : 1;
+    return (size_t(p.k) * S * p.n + 1) * (p.digitsG - 1) * 2 * p.N;
+}
+
+// upload `words` residues (host or device source) into *dst, converting to Montgomery form mod Q when mont != 0
+static int upload(mkfhe_ctx* ctx, uint32_t** dst, const uint32_t* src, uint64_t words, bool mont) {
+    if (*dst == nullptr) {
+        int rc = dev_alloc(ctx, dst, words);
+        if (rc) return rc;
+    }
+    CU(cudaMemcpyAsync(*dst, src, words * sizeof(uint32_t), cudaMemcpyDefault, ctx->stream));
+    if (mont) {
+        const unsigned blocks = unsigned(std::min<uint64_t>((words + 255) / 256, 148 * 16));
+        to_montgomery<<<blocks, 256, 0, ctx->stream>>>(*dst, *dst, words, ctx->d.mod, ctx->r2);
+        ctx->launches++;
+        CU(cudaGetLastError());
+    }
+    CU(cudaStreamSynchronize(ctx->stream));
+    return MKFHE_OK;
+}
+
+extern "C" {
+
+const char* mkfhe_version(void) { return MKFHE_VERSION_STR; }
+
+const char* mkfhe_last_error(const mkfhe_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int mkfhe_ctx_create(const mkfhe_params* p, mkfhe_ctx** out) {
+    mkfhe_ctx* ctx = nullptr;  // CU() reports into g_create_error while ctx == nullptr
+    if (!p || !out) return fail(nullptr, MKFHE_EINVAL, "null argument");
+    *out = nullptr;
+    if (p->N < 8 || p->N > 2048 || (p->N & (p->N - 1))) return fail(nullptr, MKFHE_EINVAL, "N must be a power of two in [8, 2048]");
+    if (p->k == 0 || p->k > 64 || p->n == 0) return fail(nullptr, MKFHE_EINVAL, "bad k or n");
+    if (p->Q >= (1u << 30) || !h_is_prime(p->Q) || (p->Q - 1) % (2 * p->N) != 0)
+        return fail(nullptr, MKFHE_EINVAL, "Q must be a prime < 2^30 with Q = 1 mod 2N");
+    if (p->digitsG < 2 || p->digitsG > 9 || p->baseG_log2 == 0 || p->baseG_log2 > 16)
+        return fail(nullptr, MKFHE_EINVAL, "unsupported gadget (digitsG in [2,9], baseG_log2 in [1,16])");
+    if (p->variant > 1 || p->scheme > 1) return fail(nullptr, MKFHE_EINVAL, "bad variant/scheme");
+    if (p->q < 2 || p->qKS < 2 || p->baseKS < 2 || p->baseKS > 256 || p->dKS == 0 || p->dKS > 16)
+        return fail(nullptr, MKFHE_EINVAL, "bad q/qKS/baseKS/dKS");
+    if (uint64_t(p->q) * 2 * p->N >= (1ull << 32) || p->qKS >= (1u << 24))
+        return fail(nullptr, MKFHE_EINVAL, "q*2N must fit 32 bits (mk-acc-xzw.cpp:110 uses 32-bit NativeInteger) and qKS < 2^24");
+    if (h_powmod(p->psi, p->N, p->Q) != p->Q - 1) return fail(nullptr, MKFHE_EINVAL, "psi is not a primitive 2N-th root of unity mod Q");
+
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(nullptr, MKFHE_ENODEV, "no CUDA device: libmkfhe_b200 has no CPU fallback");
+    int dev = p->device;
+    if (dev < 0) CU(cudaGetDevice(&dev));
+    if (dev >= ndev) return fail(nullptr, MKFHE_EINVAL, "device ordinal out of range");
+    CU(cudaSetDevice(dev));
+
+    ctx = new mkfhe_ctx();
+    ctx->p = *p;
+    ctx->device = dev;
+    auto bail = [&](int rc) {
+        g_create_error = ctx->err;
+        mkfhe_ctx_destroy(ctx);
+        return rc;
+    };
+    if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess)
+        return bail(fail(ctx, MKFHE_ECUDA, "cudaStreamCreate failed"));
+    ctx->stream = ctx->own_stream;
+
+    const uint32_t N = p->N, Q = p->Q;
+    uint32_t logN = 0;
+    while ((1u << logN) < N) ++logN;
+    // Montgomery constants
+    uint32_t inv = 1;  // Q^-1 mod 2^32 by Newton iteration
+    for (int i = 0; i < 5; ++i) inv *= 2u - Q * inv;
+    const uint32_t R = uint32_t((1ull << 32) % Q);
+    ctx->r2 = h_mulmod(R, R, Q);
+    auto to_m = [&](uint32_t x) { return h_mulmod(x, R, Q); };
+
+    DevCtx& d = ctx->d;
+    d.k = p->k; d.N = N; d.logN = logN; d.n = p->n; d.ell = p->digitsG - 1; d.gbits = p->baseG_log2;
+    d.variant = p->variant; d.scheme = p->scheme; d.S = p->variant == MKFHE_VARIANT_XZW ? 2 : 1;
+    d.q = p->q; d.qKS = p->qKS; d.baseKS = p->baseKS; d.dKS = p->dKS;
+    d.mod.Q = Q; d.mod.qinv_neg = 0u - inv;
+    d.one_mont = R;
+    d.ninv_mont = to_m(h_powmod(N % Q, uint64_t(Q) - 2, Q));
+
+    std::vector<uint32_t> tw(N), twi(N), pp(2 * N);
+    const uint32_t psi_inv = h_powmod(p->psi, uint64_t(Q) - 2, Q);
+    uint32_t x = 1, xi = 1;
+    for (uint32_t i = 0; i < N; ++i) {
+        const uint32_t r = h_bitrev(i, logN);
+        tw[r] = to_m(x);
+        twi[r] = to_m(xi);
+        x = h_mulmod(x, p->psi, Q);
+        xi = h_mulmod(xi, psi_inv, Q);
+    }
+    x = 1;
+    for (uint32_t e = 0; e < 2 * N; ++e) {
+        pp[e] = to_m(x);
+        x = h_mulmod(x, p->psi, Q);
+    }
+    int rc;
+    if ((rc = upload(ctx, &ctx->tw, tw.data(), N, false))) return bail(rc);
+    if ((rc = upload(ctx, &ctx->twi, twi.data(), N, false))) return bail(rc);
+    if ((rc = upload(ctx, &ctx->psipow, pp.data(), 2 * N, false))) return bail(rc);
+    d.tw = ctx->tw; d.twi = ctx->twi; d.psipow = ctx->psipow;
+
+    // specialised N = 2048 path (fast_kernels.cuh)
+    ctx->use_fast = fast_supported(d);
+    if (ctx->use_fast && (rc = fast_init(ctx->fast, d, p->psi, ctx->stream, &ctx->dev_bytes))) {
+        return bail(fail(ctx, MKFHE_ECUDA, "fast path initialisation failed: %s", cudaGetErrorString(cudaGetLastError())));
+    }
+    if (getenv("MKFHE_FORCE_GENERIC")) ctx->use_fast = false;
+    *out = ctx;
+    return MKFHE_OK;
+}
+
+void mkfhe_ctx_destroy(mkfhe_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->own_stream) cudaStreamSynchronize(ctx->own_stream);
+    fast_destroy(ctx->fast);
+    for (uint32_t* p : {ctx->tw, ctx->twi, ctx->psipow, ctx->bk, ctx->pkey, ctx->ksk_mntru, ctx->kskA, ctx->kskB, ctx->ctnand,
+                        ctx->ws_ms, ctx->ws_raw, ctx->ws_io})
+        if (p) cudaFree(p);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+    delete ctx;
+}
+
+int mkfhe_ctx_set_stream(mkfhe_ctx* ctx, void* s) {
+    if (!ctx) return MKFHE_EINVAL;
+    ctx->stream = s ? static_cast<cudaStream_t>(s) : ctx->own_stream;
+    return MKFHE_OK;
+}
+int mkfhe_ctx_synchronize(mkfhe_ctx* ctx) {
+    if (!ctx) return MKFHE_EINVAL;
+    CU(cudaStreamSynchronize(ctx->stream));
+    return MKFHE_OK;
+}
+uint64_t mkfhe_launch_count(const mkfhe_ctx* ctx) { return ctx ? ctx->launches : 0; }
+uint64_t mkfhe_device_bytes(const mkfhe_ctx* ctx) { return ctx ? ctx->dev_bytes : 0; }
+
+// ---- keys ----
+int mkfhe_load_bk(mkfhe_ctx* ctx, const uint32_t* bk, uint64_t words) {
+    if (!ctx || !bk) return MKFHE_EINVAL;
+    if (words != bk_words(ctx->p)) return fail(ctx, MKFHE_EINVAL, "mkfhe_load_bk: expected %zu words, got %llu", bk_words(ctx->p), (unsigned long long)words);
+    CU(cudaSetDevice(ctx->device));
+    int rc = upload(ctx, &ctx->bk, bk, words, true);
+    ctx->d.bk = ctx->bk;
+    if (!rc && ctx->use_fast) {
+        cudaError_t e = fast_load_bk(ctx->fast, ctx->d, ctx->stream, &ctx->dev_bytes, &ctx->launches);
+        if (e != cudaSuccess) return fail(ctx, MKFHE_ECUDA, "fast_load_bk: %s", cudaGetErrorString(e));
+    }
+    return rc;
+}
+int mkfhe_load_pkey(mkfhe_ctx* ctx, const uint32_t* pk, uint64_t words) {
+    if (!ctx || !pk) return MKFHE_EINVAL;
+    if (words != uint64_t(ctx->p.k) * (ctx->p.digitsG - 1) * ctx->p.N) return fail(ctx, MKFHE_EINVAL, "mkfhe_load_pkey: wrong size");
+    CU(cudaSetDevice(ctx->device));
+    int rc = upload(ctx, &ctx->pkey, pk, words, true);
+    ctx->d.pkey = ctx->pkey;
+    if (!rc && ctx->use_fast) {
+        cudaError_t e = fast_load_pkey(ctx->fast, ctx->d, ctx->stream, &ctx->dev_bytes, &ctx->launches);
+        if (e != cudaSuccess) return fail(ctx, MKFHE_ECUDA, "fast_load_pkey: %s", cudaGetErrorString(e));
+    }
+    return rc;
+}
+int mkfhe_load_ksk_mntru(mkfhe_ctx* ctx, const uint32_t* ksk, uint64_t words) {
+    if (!ctx || !ksk) return MKFHE_EINVAL;
+    if (ctx->p.scheme != MKFHE_SCHEME_MNTRU) return fail(ctx, MKFHE_EINVAL, "context is not MNTRU");
+    if (words != uint64_t(ctx->p.k) * ctx->p.N * ctx->p.dKS * ctx->p.n) return fail(ctx, MKFHE_EINVAL, "mkfhe_load_ksk_mntru: wrong size");
+    CU(cudaSetDevice(ctx->device));
+    return upload(ctx, &ctx->ksk_mntru, ksk, words, false);
+}
+int mkfhe_load_ksk_mklwe(mkfhe_ctx* ctx, const uint32_t* A, uint64_t wordsA, const uint32_t* B, uint64_t wordsB) {
+    if (!ctx || !A || !B) return MKFHE_EINVAL;
+    if (ctx->p.scheme != MKFHE_SCHEME_MKLWE) return fail(ctx, MKFHE_EINVAL, "context is not MKLWE");
+    const uint64_t rows = uint64_t(ctx->p.k) * ctx->p.N * ctx->p.baseKS * ctx->p.dKS;
+    if (wordsB != rows || wordsA != rows * ctx->p.n) return fail(ctx, MKFHE_EINVAL, "mkfhe_load_ksk_mklwe: wrong size");
+    CU(cudaSetDevice(ctx->device));
+    int rc = upload(ctx, &ctx->kskA, A, wordsA, false);
+    if (rc) return rc;
+    return upload(ctx, &ctx->kskB, B, wordsB, false);
+}
+int mkfhe_load_ctnand(mkfhe_ctx* ctx, const uint32_t* ct, uint64_t words) {
+    if (!ctx || !ct) return MKFHE_EINVAL;
+    if (ctx->p.scheme != MKFHE_SCHEME_MNTRU) return fail(ctx, MKFHE_EINVAL, "ctNAND exists only on the MNTRU path");
+    if (words != uint64_t(ctx->p.k) * ctx->p.n) return fail(ctx, MKFHE_EINVAL, "mkfhe_load_ctnand: wrong size");
+    CU(cudaSetDevice(ctx->device));
+    return upload(ctx, &ctx->ctnand, ct, words, false);
+}
+
+// ---- launch helpers ----
+static int generic_rotate_config(mkfhe_ctx* ctx, size_t* smem, unsigned* threads) {
+    const DevCtx& d = ctx->d;
+    size_t bytes = size_t(d.k + d.ell + 2) * d.N * 4 + ((size_t(d.k) * d.n * 2 + 15) & ~size_t(15));
+    if (bytes > 227 * 1024) return fail(ctx, MKFHE_EINVAL, "parameter set needs %zu bytes of shared memory per gate (> 227 KB)", bytes);
+    unsigned ctas = unsigned(std::max<size_t>(1, std::min<size_t>(8, (227 * 1024) / bytes)));
+    unsigned t = 2048 / ctas / 2, p2 = 32;
+    while (p2 * 2 <= t) p2 *= 2;
+    p2 = std::min(p2, std::min(1024u, std::max(32u, d.N / 2)));
+    *smem = bytes;
+    *threads = std::max(32u, p2);
+    return MKFHE_OK;
+}
+
+static int launch_rotate(mkfhe_ctx* ctx, bool gate, const GateIO& io, uint64_t batch) {
+    if (!ctx->bk || !ctx->pkey) return fail(ctx, MKFHE_ENOKEY, "bootstrapping key / Pkey not loaded");
+    if (batch == 0) return MKFHE_OK;
+    if (batch > 0x7fffffffull) return fail(ctx, MKFHE_EINVAL, "batch too large");
+    if (ctx->use_fast) {
+        cudaError_t e = fast_blind_rotate(ctx->fast, ctx->d, gate, io, uint32_t(batch), ctx->stream, &ctx->launches);
+        if (e != cudaSuccess) return fail(ctx, MKFHE_ECUDA, "fast_blind_rotate: %s", cudaGetErrorString(e));
+        return MKFHE_OK;
+    }
+    size_t smem;
+    unsigned threads;
+    int rc = generic_rotate_config(ctx, &smem, &threads);
+    if (rc) return rc;
+    if (gate) {
+        CU(cudaFuncSetAttribute(blind_rotate_generic<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+        blind_rotate_generic<true><<<unsigned(batch), threads, smem, ctx->stream>>>(ctx->d, io);
+    } else {
+        CU(cudaFuncSetAttribute(blind_rotate_generic<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+        blind_rotate_generic<false><<<unsigned(batch), threads, smem, ctx->stream>>>(ctx->d, io);
+    }
+    ctx->launches++;
+    CU(cudaGetLastError());
+    return MKFHE_OK;
+}
+
+int mkfhe_eval_acc_dev(mkfhe_ctx* ctx, const uint32_t* d_acc_in, const uint32_t* d_rot, uint32_t rot_mod, uint32_t* d_acc_out,
+                       uint64_t batch) {
+    if (!ctx || !d_acc_in || !d_rot || !d_acc_out) return MKFHE_EINVAL;
+    if (ctx->p.variant == MKFHE_VARIANT_XZW && rot_mod == 0) return fail(ctx, MKFHE_EINVAL, "rot_mod must be non-zero for XZW");
+    CU(cudaSetDevice(ctx->device));
+    GateIO io{};
+    io.acc_in = d_acc_in; io.rot = d_rot; io.rot_mod = rot_mod ? rot_mod : 1; io.acc_out = d_acc_out;
+    return launch_rotate(ctx, false, io, batch);
+}
+
+int mkfhe_eval_acc(mkfhe_ctx* ctx, const uint32_t* acc_in, const uint32_t* rot, uint32_t rot_mod, uint32_t* acc_out, uint64_t batch) {
+    if (!ctx || !acc_in || !rot || !acc_out) return MKFHE_EINVAL;
+    CU(cudaSetDevice(ctx->device));
+    const size_t aw = size_t(batch) * ctx->p.k * ctx->p.N, rw = size_t(batch) * ctx->p.k * ctx->p.n;
+    int rc = grow(ctx, &ctx->ws_io, &ctx->ws_io_words, aw + rw);
+    if (rc) return rc;
+    uint32_t* d_acc = ctx->ws_io;
+    uint32_t* d_rot = ctx->ws_io + aw;
+    CU(cudaMemcpyAsync(d_acc, acc_in, aw * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(d_rot, rot, rw * 4, cudaMemcpyHostToDevice, ctx->stream));
+    rc = mkfhe_eval_acc_dev(ctx, d_acc, d_rot, rot_mod, d_acc, batch);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(acc_out, d_acc, aw * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return MKFHE_OK;
+}
+
+int mkfhe_eval_nand_dev(mkfhe_ctx* ctx, const uint32_t* d_ct1, const uint32_t* d_b1, const uint32_t* d_ct2, const uint32_t* d_b2,
+                        uint32_t* d_out, uint32_t* d_bout, uint64_t batch) {
+    if (!ctx || !d_ct1 || !d_ct2 || !d_out) return MKFHE_EINVAL;
+    const mkfhe_params& p = ctx->p;
+    const bool lwe = p.scheme == MKFHE_SCHEME_MKLWE;
+    if (lwe && (!d_b1 || !d_b2 || !d_bout)) return fail(ctx, MKFHE_EINVAL, "MKLWE gates need b1, b2 and bout");
+    if (lwe ? (!ctx->kskA || !ctx->kskB) : (!ctx->ksk_mntru || !ctx->ctnand))
+        return fail(ctx, MKFHE_ENOKEY, lwe ? "MKLWE key-switch key not loaded" : "MNTRU key-switch key / ctNAND not loaded");
+    if (batch == 0) return MKFHE_OK;
+    CU(cudaSetDevice(ctx->device));
+    int rc = grow(ctx, &ctx->ws_ms, &ctx->ws_ms_words, size_t(batch) * p.k * p.N);
+    if (rc) return rc;
+    GateIO io{};
+    io.ct1 = d_ct1; io.ct2 = d_ct2; io.b1 = d_b1; io.b2 = d_b2; io.ctnand = ctx->ctnand; io.ms_out = ctx->ws_ms;
+    rc = launch_rotate(ctx, true, io, batch);
+    if (rc) return rc;
+    const uint32_t B = uint32_t(batch);
+    if (!lwe) {
+        dim3 grid((p.n + 63) / 64, (B + 63) / 64, p.k);
+        keyswitch_mntru_generic<<<grid, 256, 0, ctx->stream>>>(ctx->d, ctx->ws_ms, ctx->ksk_mntru, d_out, B);
+        ctx->launches++;
+        CU(cudaGetLastError());
+    } else {
+        const size_t rw = size_t(batch) * p.k * p.n + batch;
+        rc = grow(ctx, &ctx->ws_raw, &ctx->ws_raw_words, rw);
+        if (rc) return rc;
+        CU(cudaMemsetAsync(ctx->ws_raw, 0, rw * 4, ctx->stream));
+        uint32_t* braw = ctx->ws_raw + size_t(batch) * p.k * p.n;
+        const uint32_t ichunk = std::min(p.N, 256u);
+        dim3 grid(B, p.k, (p.N + ichunk - 1) / ichunk);
+        keyswitch_mklwe_generic<<<grid, 256, 0, ctx->stream>>>(ctx->d, ctx->ws_ms, ctx->kskA, ctx->kskB, ctx->ws_raw, braw, ichunk);
+        ctx->launches++;
+        CU(cudaGetLastError());
+        const uint64_t total = uint64_t(batch) * p.k * p.n;
+        keyswitch_mklwe_finish<<<unsigned((std::max<uint64_t>(total, batch) + 255) / 256), 256, 0, ctx->stream>>>(
+            ctx->d, ctx->ws_raw, braw, d_out, d_bout, total, B);
+        ctx->launches++;
+        CU(cudaGetLastError());
+    }
+    return MKFHE_OK;
+}
+
+int mkfhe_eval_nand(mkfhe_ctx* ctx, const uint32_t* ct1, const uint32_t* b1, const uint32_t* ct2, const uint32_t* b2, uint32_t* out,
+                    uint32_t* bout, uint64_t batch) {
+    if (!ctx || !ct1 || !ct2 || !out) return MKFHE_EINVAL;
+    const mkfhe_params& p = ctx->p;
+    const bool lwe = p.scheme == MKFHE_SCHEME_MKLWE;
+    if (lwe && (!b1 || !b2 || !bout)) return fail(ctx, MKFHE_EINVAL, "MKLWE gates need b1, b2 and bout");
+    if (batch == 0) return MKFHE_OK;
+    CU(cudaSetDevice(ctx->device));
+    const size_t cw = size_t(batch) * p.k * p.n;
+    int rc = grow(ctx, &ctx->ws_io, &ctx->ws_io_words, 3 * cw + 3 * batch);
+    if (rc) return rc;
+    uint32_t *d1 = ctx->ws_io, *d2 = d1 + cw, *dout = d2 + cw, *db1 = dout + cw, *db2 = db1 + batch, *dbo = db2 + batch;
+    CU(cudaMemcpyAsync(d1, ct1, cw * 4, cudaMemcpyHostToDevice, ctx->stream));
+    CU(cudaMemcpyAsync(d2, ct2, cw * 4, cudaMemcpyHostToDevice, ctx->stream));
+    if (lwe) {
+        CU(cudaMemcpyAsync(db1, b1, batch * 4, cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaMemcpyAsync(db2, b2, batch * 4, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    rc = mkfhe_eval_nand_dev(ctx, d1, lwe ? db1 : nullptr, d2, lwe ? db2 : nullptr, dout, lwe ? dbo : nullptr, batch);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(out, dout, cw * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (lwe) CU(cudaMemcpyAsync(bout, dbo, batch * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return MKFHE_OK;
+}
+
+int mkfhe_ntt_dev(mkfhe_ctx* ctx, uint32_t* d_polys, uint64_t batch, int inverse) {
+    if (!ctx || !d_polys) return MKFHE_EINVAL;
+    if (batch == 0) return MKFHE_OK;
+    if (batch > 0x7fffffffull) return fail(ctx, MKFHE_EINVAL, "batch too large");
+    CU(cudaSetDevice(ctx->device));
+    if (ctx->use_fast) {
+        cudaError_t e = fast_ntt(ctx->fast, ctx->d, d_polys, batch, inverse, ctx->stream, &ctx->launches);
+        if (e != cudaSuccess) return fail(ctx, MKFHE_ECUDA, "fast_ntt: %s", cudaGetErrorString(e));
+        return MKFHE_OK;
+    }
+    const unsigned threads = std::max(32u, std::min(1024u, ctx->p.N / 2));
+    ntt_batch_generic<<<unsigned(batch), threads, ctx->p.N * 4, ctx->stream>>>(ctx->d, d_polys, inverse);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    return MKFHE_OK;
+}
+int mkfhe_ntt(mkfhe_ctx* ctx, uint32_t* polys, uint64_t batch, int inverse) {
+    if (!ctx || !polys) return MKFHE_EINVAL;
+    if (batch == 0) return MKFHE_OK;
+    CU(cudaSetDevice(ctx->device));
+    const size_t w = size_t(batch) * ctx->p.N;
+    int rc = grow(ctx, &ctx->ws_io, &ctx->ws_io_words, w);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(ctx->ws_io, polys, w * 4, cudaMemcpyHostToDevice, ctx->stream));
+    rc = mkfhe_ntt_dev(ctx, ctx->ws_io, batch, inverse);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(polys, ctx->ws_io, w * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return MKFHE_OK;
+}
+
+int mkfhe_decompose(mkfhe_ctx* ctx, const uint32_t* polys, uint32_t* out, uint64_t batch) {
+    if (!ctx || !polys || !out) return MKFHE_EINVAL;
+    if (batch == 0) return MKFHE_OK;
+    CU(cudaSetDevice(ctx->device));
+    const size_t w = size_t(batch) * ctx->p.N, ell = ctx->p.digitsG - 1;
+    int rc = grow(ctx, &ctx->ws_io, &ctx->ws_io_words, w * (1 + ell));
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(ctx->ws_io, polys, w * 4, cudaMemcpyHostToDevice, ctx->stream));
+    decompose_generic<<<unsigned((w + 255) / 256), 256, 0, ctx->stream>>>(ctx->d, ctx->ws_io, ctx->ws_io + w, w);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(out, ctx->ws_io + w, w * ell * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return MKFHE_OK;
+}
+
+int mkfhe_measure_int32_peak(mkfhe_ctx* ctx, double* imad_per_s) {
+    if (!ctx || !imad_per_s) return MKFHE_EINVAL;
+    CU(cudaSetDevice(ctx->device));
+    int sms = 0;
+    CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device));
+    uint32_t* sink = nullptr;
+    CU(cudaMalloc(&sink, 4));
+    const uint32_t iters = 4096, blocks = sms * 8, threads = 256;
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0));
+    CU(cudaEventCreate(&e1));
+    int32_peak_kernel<<<blocks, threads, 0, ctx->stream>>>(sink, 64, 7u);  // warm-up
+    float best = 1e30f;
+    for (int rep = 0; rep < 5; ++rep) {
+        CU(cudaEventRecord(e0, ctx->stream));
+        int32_peak_kernel<<<blocks, threads, 0, ctx->stream>>>(sink, iters, 7u + rep);
+        CU(cudaEventRecord(e1, ctx->stream));
+        CU(cudaEventSynchronize(e1));
+        float ms = 0;
+        CU(cudaEventElapsedTime(&ms, e0, e1));
+        best = std::min(best, ms);
+        ctx->launches++;
+    }
+    CU(cudaGetLastError());
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(sink);
+    *imad_per_s = double(blocks) * threads * double(iters) * 16 * 8 / (best * 1e-3);
+    return MKFHE_OK;
+}
+
+}  // extern "C"

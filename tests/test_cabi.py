@@ -1,0 +1,52 @@
+"""CPU: the C-ABI library loads and exports exactly the symbols include/mkfhe_b200.h declares; without a GPU it refuses to
+create a context (no CPU fallback); host-side parameter derivation matches the reference's constants."""
+import ctypes
+import os
+import re
+
+import pytest
+
+import mkfhe_b200 as mk
+from mkfhe_b200 import lib as mklib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    text = open(os.path.join(ROOT, "include", "mkfhe_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(mkfhe_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_symbols_exported():
+    declared = _declared()
+    assert declared == sorted(mklib.SYMBOLS)
+    L = ctypes.CDLL(mklib.LIB_PATH)
+    for s in declared:
+        assert hasattr(L, s), s
+    assert b"sm_100a" in mklib.load().mkfhe_version()
+
+
+def test_no_cpu_fallback():
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(mk.MkfheError) as e:
+        mk.BinFHEContext().GenerateBinFHEContext("STD100_MKNTRU", mk.MKNTRU)
+    assert e.value.code == -2  # MKFHE_ENODEV
+
+
+def test_parameter_derivation_matches_reference_constants():
+    # SURVEY section 8 (probe-verified against the reference): Q(27,4096)=134176769, psi=100530; Q(27,2048)=134215681, psi=282116
+    p = mk.derive_params(mk.PARAMSETS["STD100_MKNTRU"], mk.MKNTRU)
+    assert (p.Q, p.psi, p.digitsG, p.dKS, p.N, p.n, p.k) == (134176769, 100530, 3, 4, 2048, 560, 2)
+    p = mk.derive_params(mk.PARAMSETS["STD100_MKNTRU_LWE"], mk.MKNTRU_LWE)
+    assert (p.Q, p.psi, p.digitsG, p.dKS, p.variant, p.scheme) == (134176769, 100530, 3, 3, 1, 1)
+    from mkfhe_b200.context import first_prime, previous_prime, root_of_unity
+
+    Q = previous_prime(first_prime(27, 2048), 2048)
+    assert (Q, root_of_unity(2048, Q)) == (134215681, 282116)
+    assert mk.derive_params(mk.PARAMSETS["STD128_MKNTRU_4"], mk.MKNTRU).digitsG == 6
+    with pytest.raises(mk.config_error):
+        mk.derive_params(mk.PARAMSETS["STD100_MKNTRU"], "GINX")
