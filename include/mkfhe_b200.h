@@ -136,6 +136,9 @@ int mkfhe_decompose(mkfhe_ctx* ctx, const uint32_t* polys, uint32_t* out, uint64
 /* ---- introspection ---- */
 /* number of kernel launches this context has issued since creation (bench.py's gpu_launches claim) */
 uint64_t mkfhe_launch_count(const mkfhe_ctx* ctx);
+/* device time (CUDA events on the context's stream) of the last mkfhe_eval_nand[_dev] batch, split into the blind-rotation
+ * kernel and the key-switch kernels; waits for that batch to finish.  bench.py's roofline numerators come from here. */
+int mkfhe_last_gate_timing(mkfhe_ctx* ctx, float* rotate_ms, float* keyswitch_ms);
 /* bytes of HBM held by this context (keys + tables + workspaces) */
 uint64_t mkfhe_device_bytes(const mkfhe_ctx* ctx);
 /* build-time identity: "mkfhe_b200 <version> sm_100a" */

@@ -270,6 +270,12 @@ class BinFHEContext:
     def synchronize(self):
         self._ck(self._L.mkfhe_ctx_synchronize(self._h), "mkfhe_ctx_synchronize")
 
+    def last_gate_timing(self):
+        """(blind_rotation_ms, key_switch_ms) of the last gate batch, from CUDA events on the context's stream"""
+        a, b = C.c_float(0), C.c_float(0)
+        self._ck(self._L.mkfhe_last_gate_timing(self._h, C.byref(a), C.byref(b)), "mkfhe_last_gate_timing")
+        return float(a.value), float(b.value)
+
     def launch_count(self) -> int:
         return int(self._L.mkfhe_launch_count(self._h))
 

@@ -44,6 +44,8 @@ struct mkfhe_ctx {
     uint32_t r2{0};  // 2^64 mod Q
     FastState fast{};
     bool use_fast{false};
+    cudaEvent_t ev[3]{nullptr, nullptr, nullptr};  // before blind rotation | after it | after key switch (last gate batch)
+    bool ev_valid{false};
 };
 
 static thread_local std::string g_create_error;
@@ -176,6 +178,8 @@ int mkfhe_ctx_create(const mkfhe_params* p, mkfhe_ctx** out) {
     if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess)
         return bail(fail(ctx, MKFHE_ECUDA, "cudaStreamCreate failed"));
     ctx->stream = ctx->own_stream;
+    for (auto& e : ctx->ev)
+        if (cudaEventCreate(&e) != cudaSuccess) return bail(fail(ctx, MKFHE_ECUDA, "cudaEventCreate failed"));
 
     const uint32_t N = p->N, Q = p->Q;
     uint32_t logN = 0;
@@ -234,6 +238,8 @@ void mkfhe_ctx_destroy(mkfhe_ctx* ctx) {
     for (uint32_t* p : {ctx->tw, ctx->twi, ctx->psipow, ctx->bk, ctx->pkey, ctx->ksk_mntru, ctx->kskA, ctx->kskB, ctx->ctnand,
                         ctx->ws_ms, ctx->ws_raw, ctx->ws_io})
         if (p) cudaFree(p);
+    for (auto& e : ctx->ev)
+        if (e) cudaEventDestroy(e);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     delete ctx;
 }
@@ -381,8 +387,10 @@ int mkfhe_eval_nand_dev(mkfhe_ctx* ctx, const uint32_t* d_ct1, const uint32_t* d
     if (rc) return rc;
     GateIO io{};
     io.ct1 = d_ct1; io.ct2 = d_ct2; io.b1 = d_b1; io.b2 = d_b2; io.ctnand = ctx->ctnand; io.ms_out = ctx->ws_ms;
+    CU(cudaEventRecord(ctx->ev[0], ctx->stream));
     rc = launch_rotate(ctx, true, io, batch);
     if (rc) return rc;
+    CU(cudaEventRecord(ctx->ev[1], ctx->stream));
     const uint32_t B = uint32_t(batch);
     if (!lwe) {
         dim3 grid((p.n + 63) / 64, (B + 63) / 64, p.k);
@@ -406,6 +414,17 @@ int mkfhe_eval_nand_dev(mkfhe_ctx* ctx, const uint32_t* d_ct1, const uint32_t* d
         ctx->launches++;
         CU(cudaGetLastError());
     }
+    CU(cudaEventRecord(ctx->ev[2], ctx->stream));
+    ctx->ev_valid = true;
+    return MKFHE_OK;
+}
+
+int mkfhe_last_gate_timing(mkfhe_ctx* ctx, float* rotate_ms, float* keyswitch_ms) {
+    if (!ctx || !rotate_ms || !keyswitch_ms) return MKFHE_EINVAL;
+    if (!ctx->ev_valid) return fail(ctx, MKFHE_EINVAL, "no gate batch has been evaluated yet");
+    CU(cudaEventSynchronize(ctx->ev[2]));
+    CU(cudaEventElapsedTime(rotate_ms, ctx->ev[0], ctx->ev[1]));
+    CU(cudaEventElapsedTime(keyswitch_ms, ctx->ev[1], ctx->ev[2]));
     return MKFHE_OK;
 }
 

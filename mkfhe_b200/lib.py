@@ -22,7 +22,7 @@ SYMBOLS = [
     "mkfhe_ctx_create", "mkfhe_ctx_destroy", "mkfhe_last_error", "mkfhe_ctx_set_stream", "mkfhe_ctx_synchronize",
     "mkfhe_load_bk", "mkfhe_load_pkey", "mkfhe_load_ksk_mntru", "mkfhe_load_ksk_mklwe", "mkfhe_load_ctnand",
     "mkfhe_eval_acc", "mkfhe_eval_acc_dev", "mkfhe_eval_nand", "mkfhe_eval_nand_dev", "mkfhe_ntt", "mkfhe_ntt_dev",
-    "mkfhe_decompose", "mkfhe_launch_count", "mkfhe_device_bytes", "mkfhe_version", "mkfhe_measure_int32_peak",
+    "mkfhe_decompose", "mkfhe_last_gate_timing", "mkfhe_launch_count", "mkfhe_device_bytes", "mkfhe_version", "mkfhe_measure_int32_peak",
 ]
 
 
@@ -67,6 +67,7 @@ def load():
     L.mkfhe_ntt.argtypes = [vp, vp, u64, i32]
     L.mkfhe_ntt_dev.argtypes = [vp, vp, u64, i32]
     L.mkfhe_decompose.argtypes = [vp, vp, vp, u64]
+    L.mkfhe_last_gate_timing.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]
     L.mkfhe_launch_count.argtypes = [vp]
     L.mkfhe_launch_count.restype = u64
     L.mkfhe_device_bytes.argtypes = [vp]
