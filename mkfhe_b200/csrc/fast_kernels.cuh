@@ -1,16 +1,487 @@
-// fast_kernels.cuh -- specialised N = 2048 kernels (placeholder: not enabled yet; the generic kernels serve every set).
+// fast_kernels.cuh -- specialised kernels for the production shape N = 2048, digitsG - 1 = 2 (every STD100_* set and the
+// STD128_*_LWE sets of binfhecontext.cpp:91-146), any party count whose accumulator fits shared memory.
+//
+// One CTA of 128 threads owns one gate.  A size-2048 transform is three register passes of 4 + 4 + 3 radix-2 stages with
+// 16 coefficients per thread; between passes the coefficients are transposed through shared memory (one cross-warp
+// exchange with a block barrier, one exchange that stays inside a warp and needs only __syncwarp).  A single XOR swizzle
+// makes every exchange access bank-conflict free.  Butterflies are lazy: no value is reduced below 2^32 until the end,
+// which Q < 2^32 / 32 allows (forward: +2Q per stage; see the bounds next to each routine).
+//
+// Modular multiplication by a known constant (twiddles) is Shoup's: q = mulhi(y, w'), t = y*w - q*Q in [0, 2Q), with
+// w' = floor(w * 2^32 / Q) -- one IMAD.HI (half rate on sm_100a, measured by tools/pipe_microbench.cu) and two IMAD.LO, one
+// slot fewer on the fma pipe than Montgomery's two IMAD.WIDE.  Key products use Montgomery accumulation in 64 bits, one
+// reduction per output (keys are stored in Montgomery form at upload).
+//
+// What is computed is the reference's HbProd recurrence (mk-acc-xzw.cpp:231-345, mk-acc-xzw_B.cpp:221-331) restated in the
+// coefficient domain, exactly as generic_kernels.cuh does; only the schedule differs:
+//   iteration it = 0..k-1 : party p_it (key owner last): t = (X^c - 1) a_p -> digits -> 2 forward NTTs -> X = <D, d>,
+//                           V += <D, Pkey_p>;  then one inverse NTT: of X (non-owner; a_p += result) or of V (owner)
+//   iteration it = k      : digits of INTT(V) -> 2 forward NTTs -> X_owner += <D, f>; inverse NTT; a_owner += result
+// so every iteration is "2 forward + 1 inverse" and the code holds one instance of each.
 #pragma once
 #include <cuda_runtime.h>
+
 #include <cstdint>
+#include <vector>
+
 #include "generic_kernels.cuh"
 
 namespace mkfhe {
-struct FastState {};
-inline bool fast_supported(const DevCtx&) { return false; }
-inline int fast_init(FastState&, const DevCtx&, uint32_t, cudaStream_t, uint64_t*) { return 0; }
-inline void fast_destroy(FastState&) {}
+
+constexpr uint32_t FN = 2048, FLOGN = 11, FT = 128;  // ring size, threads per gate
+
+struct FastTables {
+    const uint2* tw2;     // [N]  forward twiddles, OpenFHE order: psi^i at bitrev(i), as Shoup pairs (w, floor(w 2^32 / Q))
+    const uint2* itw2;    // [N]  cyclic inverse (DIT) twiddles: itw2[t + m] = omega^(-m N / 2t), m < t, t = 1, 2, .., N/2
+    const uint2* scale2;  // [N]  psi^-i / N  (the twist and the 1/N of the inverse, folded into one Shoup multiply)
+    uint2 twA[16];        // tw2[0..15]: forward pass A twiddles are the same for every thread -> kernel-parameter constants
+    uint2 itwA[16];       // itw2[0..15]
+};
+
+// y * w mod Q in [0, 2Q) for ANY 32-bit y (Harvey's lazy Shoup multiplication)
+__device__ __forceinline__ uint32_t shoup_lazy(uint32_t y, uint2 w, uint32_t Q) {
+    const uint32_t q = __umulhi(y, w.y);
+    return y * w.x - q * Q;
+}
+// [0, 2Q) -> [0, Q)
+__device__ __forceinline__ uint32_t fold1(uint32_t x, uint32_t Q) { return min(x, x - Q); }
+
+// swizzled position of coefficient j (11 bits) in an exchange buffer: bits 2-3 ^= bits 5-6, bits 3-4 ^= bits 7-8.
+// Keeps 16-byte groups intact (bits 0-1 untouched) so 128-bit accesses stay legal.
+__device__ __forceinline__ uint32_t swz(uint32_t j) { return j ^ (((j >> 5) & 3u) << 2) ^ (((j >> 7) & 3u) << 3); }
+
+// ---- forward negacyclic NTT, NP polynomials at once (shared twiddles), Cooley-Tukey, natural -> bit-reversed --------
+// in : x[p][r] = coefficient tid + 128 r          (values < 2Q)
+// out: x[p][i] = slot 16 tid + i (OpenFHE order)   (values < 24Q: +2Q per stage, 11 stages)
+// E: NP * 2048 words of shared memory.  Contains one __syncthreads (after the pass-A writes); the caller guarantees that
+// every thread is done reading E from its previous use before any thread enters (a barrier lies in between).
+template <int NP>
+__device__ __forceinline__ void fwd_ntt_regs(uint32_t (&x)[NP][16], uint32_t* E, const FastTables& T, uint32_t Q, uint32_t tid) {
+    const uint32_t twoQ = 2 * Q;
+    // pass A: t = 1024, 512, 256, 128
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+        const int h = 8 >> s;
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+            if (r & h) continue;
+            const uint2 w = T.twA[(1 << s) + (r >> (4 - s))];
+#pragma unroll
+            for (int p = 0; p < NP; ++p) {
+                const uint32_t t = shoup_lazy(x[p][r + h], w, Q), u = x[p][r];
+                x[p][r] = u + t;
+                x[p][r + h] = u + twoQ - t;
+            }
+        }
+    }
+#pragma unroll
+    for (int p = 0; p < NP; ++p)
+#pragma unroll
+        for (int r = 0; r < 16; ++r) E[p * FN + swz(tid + 128 * r)] = x[p][r];
+    __syncthreads();
+    const uint32_t hi4 = tid >> 3, lo3 = tid & 7;
+#pragma unroll
+    for (int p = 0; p < NP; ++p)
+#pragma unroll
+        for (int r = 0; r < 16; ++r) x[p][r] = E[p * FN + swz(hi4 * 128 + 8 * r + lo3)];
+    // pass B: t = 64, 32, 16, 8
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+        const int h = 8 >> s;
+        const uint2* tws = T.tw2 + (16 << s) + (hi4 << s);
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+            if (r & h) continue;
+            const uint2 w = __ldg(tws + (r >> (4 - s)));
+#pragma unroll
+            for (int p = 0; p < NP; ++p) {
+                const uint32_t t = shoup_lazy(x[p][r + h], w, Q), u = x[p][r];
+                x[p][r] = u + t;
+                x[p][r + h] = u + twoQ - t;
+            }
+        }
+    }
+    // exchange B -> C stays inside the warp: warp w holds coefficients [512 w, 512 w + 512) before and after
+    __syncwarp();
+#pragma unroll
+    for (int p = 0; p < NP; ++p)
+#pragma unroll
+        for (int r = 0; r < 16; ++r) E[p * FN + swz(hi4 * 128 + 8 * r + lo3)] = x[p][r];
+    __syncwarp();
+#pragma unroll
+    for (int p = 0; p < NP; ++p)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const uint4 v = *reinterpret_cast<const uint4*>(E + p * FN + swz(16 * tid + 4 * c));
+            x[p][4 * c + 0] = v.x; x[p][4 * c + 1] = v.y; x[p][4 * c + 2] = v.z; x[p][4 * c + 3] = v.w;
+        }
+    // pass C: t = 4, 2, 1
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+        const int h = 4 >> s;
+        const uint2* tws = T.tw2 + (256 << s) + tid * (2 << s);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            if (i & h) continue;
+            const uint2 w = __ldg(tws + (i >> (3 - s)));
+#pragma unroll
+            for (int p = 0; p < NP; ++p) {
+                const uint32_t t = shoup_lazy(x[p][i + h], w, Q), u = x[p][i];
+                x[p][i] = u + t;
+                x[p][i + h] = u + twoQ - t;
+            }
+        }
+    }
+}
+
+// ---- inverse negacyclic NTT of one polynomial, bit-reversed -> natural -------------------------------------------
+// Written as the cyclic decimation-in-time transform with omega^-1 (Cooley-Tukey butterflies, so growth is additive),
+// followed by one multiplication by psi^-i / N -- the same ring map as the reference's Gentleman-Sande inverse
+// (transformnat-impl.h:491-552), hence the same canonical residues.
+// in : x[i] = slot 16 tid + i, values < 6Q
+// out: x[r] = coefficient tid + 128 r, values in [0, 2Q)
+// bounds: first stage (twiddle 1, no multiplication) < 12Q, then +2Q per stage: < 32Q < 2^32.
+// E: 2048 words.  One __syncthreads inside (after the pass-2 writes); same entry condition as fwd_ntt_regs.
+__device__ __forceinline__ void inv_ntt_regs(uint32_t (&x)[16], uint32_t* E, const FastTables& T, uint32_t Q, uint32_t tid) {
+    const uint32_t twoQ = 2 * Q, sixQ = 6 * Q;
+    // pass 1: t = 1 (trivial twiddle), 2, 4, 8
+#pragma unroll
+    for (int i = 0; i < 16; i += 2) {
+        const uint32_t u = x[i], v = x[i + 1];
+        x[i] = u + v;
+        x[i + 1] = u + sixQ - v;
+    }
+#pragma unroll
+    for (int s = 1; s < 4; ++s) {
+        const int t = 1 << s;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            if (i & t) continue;
+            const uint2 w = T.itwA[t + (i & (t - 1))];
+            const uint32_t v = shoup_lazy(x[i + t], w, Q), u = x[i];
+            x[i] = u + v;
+            x[i + t] = u + twoQ - v;
+        }
+    }
+    __syncwarp();
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+        *reinterpret_cast<uint4*>(E + swz(16 * tid + 4 * c)) = make_uint4(x[4 * c], x[4 * c + 1], x[4 * c + 2], x[4 * c + 3]);
+    __syncwarp();
+    const uint32_t hi3 = tid >> 4, lo4 = tid & 15;
+#pragma unroll
+    for (int r = 0; r < 16; ++r) x[r] = E[swz(hi3 * 256 + 16 * r + lo4)];
+    // pass 2: t = 16, 32, 64, 128   (h = t / 16 in register units)
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+        const int h = 1 << s;
+        const uint2* tws = T.itw2 + 16 * h + lo4;
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+            if (r & h) continue;
+            const uint2 w = __ldg(tws + 16 * (r & (h - 1)));
+            const uint32_t v = shoup_lazy(x[r + h], w, Q), u = x[r];
+            x[r] = u + v;
+            x[r + h] = u + twoQ - v;
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < 16; ++r) E[swz(hi3 * 256 + 16 * r + lo4)] = x[r];
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < 16; ++r) x[r] = E[swz(tid + 128 * r)];
+    // pass 3: t = 256, 512, 1024   (h = t / 128 in register units: 2, 4, 8)
+#pragma unroll
+    for (int s = 1; s < 4; ++s) {
+        const int h = 1 << s;
+        const uint2* tws = T.itw2 + 128 * h + tid;
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+            if (r & h) continue;
+            const uint2 w = __ldg(tws + 128 * (r & (h - 1)));
+            const uint32_t v = shoup_lazy(x[r + h], w, Q), u = x[r];
+            x[r] = u + v;
+            x[r + h] = u + twoQ - v;
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < 16; ++r) x[r] = shoup_lazy(x[r], __ldg(T.scale2 + tid + 128 * r), Q);
+}
+
+// ---- helpers of the specialised step ---------------------------------------------------------------------------------
+
+// SignedDigitDecompose of one canonical coefficient t (mk-acc.cpp:54-80), first digit dropped, two digits kept, each
+// returned as r + Q in (0, 2Q) (same residue as the reference's "r < 0 ? r + Q : r"; the lazy transform takes < 2Q).
+// sext_g(d) = ((d + B/2) mod B) - B/2 and (d - sext_g(d)) >> g = (d + B/2) >> g, so three rounding shifts suffice.
+__device__ __forceinline__ void decompose2(uint32_t t, uint32_t Q, uint32_t g, uint32_t& o0, uint32_t& o1) {
+    const int32_t half = 1 << (g - 1);
+    const int32_t d = static_cast<int32_t>(t < (Q >> 1) ? t : t - Q);
+    const int32_t d1 = (d + half) >> g;   // first digit ignored (approximate gadget decomposition)
+    const int32_t d2 = (d1 + half) >> g;
+    const int32_t d3 = (d2 + half) >> g;
+    o0 = static_cast<uint32_t>(d1 - (d2 << g) + static_cast<int32_t>(Q));
+    o1 = static_cast<uint32_t>(d2 - (d3 << g) + static_cast<int32_t>(Q));
+}
+
+// sum_j a_j * key_j * 2^-32 mod Q, in [0, 3Q): a_j < 24Q (lazy NTT output), key_j < Q in Montgomery form
+__device__ __forceinline__ uint32_t mac2(uint32_t a0, uint32_t k0, uint32_t a1, uint32_t k1, const Mod m) {
+    const uint64_t t = static_cast<uint64_t>(a0) * k0 + static_cast<uint64_t>(a1) * k1;
+    const uint32_t q = static_cast<uint32_t>(t) * m.qinv_neg;
+    return static_cast<uint32_t>((t + static_cast<uint64_t>(q) * m.Q) >> 32);
+}
+
+__device__ __forceinline__ uint4 ldg4(const uint32_t* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+
+// 4 consecutive slots of one key polynomial as HbProd uses it in a step s > 0 (Montgomery form, canonical):
+//   XZW_B: ev1                       (mk-acc-xzw_B.cpp:306-309)
+//   XZW  : ev1 - ev2 * X^-c          (mk-acc-xzw.cpp:322-325: ev1 - ev2*(X^-c - 1) - ev2)
+__device__ __forceinline__ uint4 key4(const uint32_t* ev1, const uint32_t* ev2, const uint32_t (&xneg)[4], bool xzw, const Mod m) {
+    uint4 a = ldg4(ev1);
+    if (xzw) {
+        const uint4 b = ldg4(ev2);
+        a.x = submod(a.x, montmul(b.x, xneg[0], m), m.Q);
+        a.y = submod(a.y, montmul(b.y, xneg[1], m), m.Q);
+        a.z = submod(a.z, montmul(b.z, xneg[2], m), m.Q);
+        a.w = submod(a.w, montmul(b.w, xneg[3], m), m.Q);
+    }
+    return a;
+}
+
+// Shared memory of one gate: a[k][N] | E1[2][N] | E2[N] | X[N] | crot[k*n] (u16).
+// E1 / E2 / X double as D / V / X of the generic first step.
+__host__ __device__ inline size_t fast_smem_bytes(uint32_t k, uint32_t n) {
+    return (size_t(k) + 4) * FN * 4 + ((size_t(k) * n * 2 + 15) & ~size_t(15));
+}
+
+template <bool GATE>
+__global__ void __launch_bounds__(FT, 4) blind_rotate_fast(const DevCtx P, const FastTables T, const GateIO io) {
+    extern __shared__ __align__(16) uint32_t sm[];
+    const uint32_t Q = P.mod.Q, k = P.k, n = P.n, tid = threadIdx.x;
+    constexpr uint32_t N = FN, M = 2 * FN;
+    uint32_t* a = sm;
+    uint32_t* E1 = a + k * N;
+    uint32_t* E2 = E1 + 2 * N;
+    uint32_t* Xs = E2 + N;
+    uint16_t* crot = reinterpret_cast<uint16_t*>(Xs + N);
+    const bool xzw = P.variant == 0;
+    const uint32_t g = P.gbits;
+
+    rotate_prologue<GATE>(P, io, blockIdx.x, a, crot);
+    // first step (AddToAccXZW0: KDM key assembled from evk*, acc replaced): once per gate, on the generic routine
+    hbprod_step_generic(P, a, E1, E2, Xs, 0, crot[0]);
+
+    const size_t per = size_t(2) * 2 * N;  // words of one UniEncEvalKey: [j][d|f][N]
+    const uint32_t brv7 = __brev(tid) >> 25;
+    for (uint32_t s = 1; s < k * n; ++s) {
+        const uint32_t c = crot[s];
+        if (c == 0) continue;  // X^0 - 1 = 0: the step leaves acc unchanged
+        const uint32_t u = s / n, i = s - u * n;
+        const uint32_t cneg = (M - c) & (M - 1);
+        const uint32_t* ev1 = P.bk + (size_t(u * P.S) * n + i) * per + 16 * tid;
+        const uint32_t* ev2 = xzw ? ev1 + size_t(n) * per : ev1;
+        const uint32_t e0 = cneg * (2 * brv7 + 1);  // exponent of psi for X^-c at this thread's first slot
+        uint32_t keep[16];                          // V while parties are processed, then X of the key owner
+        uint32_t y[16];
+#pragma unroll 1
+        for (uint32_t it = 0; it <= k; ++it) {
+            uint32_t D[2][16];
+            uint32_t p = u;
+            if (it < k) {
+                p = (it + 1 < k) ? (it < u ? it : it + 1) : u;
+                const uint32_t* ap = a + p * N;
+#pragma unroll
+                for (int r = 0; r < 16; ++r) decompose2(rot_sub(ap, c, tid + 128 * r, N, Q), Q, g, D[0][r], D[1][r]);
+            } else {
+#pragma unroll
+                for (int r = 0; r < 16; ++r) decompose2(fold1(y[r], Q), Q, g, D[0][r], D[1][r]);
+            }
+            fwd_ntt_regs<2>(D, E1, T, Q, tid);
+            const int col = it < k ? 0 : 1;  // "d" column for the parties, "f" column for the sumV term
+            const uint32_t* pk = P.pkey + size_t(p) * 2 * N + 16 * tid;
+#pragma unroll
+            for (int ch = 0; ch < 4; ++ch) {
+                uint32_t xn[4] = {0, 0, 0, 0};
+                if (xzw) {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const uint32_t b4 = __brev(uint32_t(4 * ch + q)) >> 28;
+                        xn[q] = __ldg(P.psipow + ((e0 + 256u * ((cneg * b4) & 15u)) & (M - 1)));
+                    }
+                }
+                const uint4 k0 = key4(ev1 + (0 * 2 + col) * N + 4 * ch, ev2 + (0 * 2 + col) * N + 4 * ch, xn, xzw, P.mod);
+                const uint4 k1 = key4(ev1 + (1 * 2 + col) * N + 4 * ch, ev2 + (1 * 2 + col) * N + 4 * ch, xn, xzw, P.mod);
+                const uint32_t kk0[4] = {k0.x, k0.y, k0.z, k0.w}, kk1[4] = {k1.x, k1.y, k1.z, k1.w};
+                uint32_t pp0[4] = {0, 0, 0, 0}, pp1[4] = {0, 0, 0, 0};
+                if (it < k) {
+                    const uint4 q0 = ldg4(pk + 4 * ch), q1 = ldg4(pk + N + 4 * ch);
+                    pp0[0] = q0.x; pp0[1] = q0.y; pp0[2] = q0.z; pp0[3] = q0.w;
+                    pp1[0] = q1.x; pp1[1] = q1.y; pp1[2] = q1.z; pp1[3] = q1.w;
+                }
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int sl = 4 * ch + q;
+                    const uint32_t x = mac2(D[0][sl], kk0[q], D[1][sl], kk1[q], P.mod);  // < 3Q
+                    if (it < k) {
+                        const uint32_t v = mac2(D[0][sl], pp0[q], D[1][sl], pp1[q], P.mod);
+                        uint32_t vs = (it == 0 ? 0u : keep[sl]) + v;  // < 7Q
+                        vs = min(vs, vs - 4 * Q);                     // < 4Q
+                        if (it + 1 < k) {
+                            keep[sl] = vs;
+                            y[sl] = x;
+                        } else {  // owner: transform V next, hold X
+                            y[sl] = vs;
+                            keep[sl] = x;
+                        }
+                    } else {
+                        y[sl] = keep[sl] + x;  // < 6Q
+                    }
+                }
+            }
+            inv_ntt_regs(y, E2, T, Q, tid);
+            if (it + 1 != k) {  // a_p += result (the owner's V goes on to the next iteration in registers instead)
+                uint32_t* ap = a + p * N;
+#pragma unroll
+                for (int r = 0; r < 16; ++r) {
+                    uint32_t v = ap[tid + 128 * r] + y[r];  // < 3Q
+                    v = min(v, v - 2 * Q);
+                    ap[tid + 128 * r] = min(v, v - Q);
+                }
+            }
+        }
+        __syncthreads();  // a[] complete before the next step's shifted reads
+    }
+    rotate_epilogue<GATE>(P, io, blockIdx.x, a);
+}
+
+// ---- standalone batched transform (config 5, mkfhe_ntt): one polynomial per CTA-iteration, persistent grid -----------
+__global__ void __launch_bounds__(FT, 8) ntt_batch_fast(const FastTables T, const uint32_t Q, const uint2 one2, uint32_t* polys,
+                                                        const uint64_t batch, const int inverse) {
+    __shared__ __align__(16) uint32_t E[FN];
+    const uint32_t tid = threadIdx.x;
+    for (uint64_t b = blockIdx.x; b < batch; b += gridDim.x) {
+        uint32_t* p = polys + b * FN;
+        if (!inverse) {
+            uint32_t x[1][16];
+#pragma unroll
+            for (int r = 0; r < 16; ++r) x[0][r] = p[tid + 128 * r];
+            fwd_ntt_regs<1>(x, E, T, Q, tid);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                uint4 v;
+                v.x = fold1(shoup_lazy(x[0][4 * c + 0], one2, Q), Q);
+                v.y = fold1(shoup_lazy(x[0][4 * c + 1], one2, Q), Q);
+                v.z = fold1(shoup_lazy(x[0][4 * c + 2], one2, Q), Q);
+                v.w = fold1(shoup_lazy(x[0][4 * c + 3], one2, Q), Q);
+                *reinterpret_cast<uint4*>(p + 16 * tid + 4 * c) = v;
+            }
+        } else {
+            uint32_t x[16];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const uint4 v = *reinterpret_cast<const uint4*>(p + 16 * tid + 4 * c);
+                x[4 * c] = v.x; x[4 * c + 1] = v.y; x[4 * c + 2] = v.z; x[4 * c + 3] = v.w;
+            }
+            inv_ntt_regs(x, E, T, Q, tid);
+#pragma unroll
+            for (int r = 0; r < 16; ++r) p[tid + 128 * r] = fold1(x[r], Q);
+        }
+        __syncthreads();  // E is reused by the next polynomial
+    }
+}
+
+// ---- host side ------------------------------------------------------------------------------------------------------
+struct FastState {
+    FastTables T{};
+    uint2 *d_tw2{nullptr}, *d_itw2{nullptr}, *d_scale2{nullptr};
+    uint2 one2{};
+    int sms{148};
+};
+
+inline bool fast_supported(const DevCtx& d) {
+    return d.N == FN && d.ell == 2 && d.mod.Q < (1u << 27) && d.gbits >= 2 && d.gbits <= 16 &&
+           fast_smem_bytes(d.k, d.n) <= 227 * 1024;
+}
+
+inline cudaError_t fast_init(FastState& F, const DevCtx& d, uint32_t psi, cudaStream_t st, uint64_t* dev_bytes) {
+    const uint32_t Q = d.mod.Q, N = FN;
+    auto mul = [&](uint32_t a, uint32_t b) { return uint32_t((uint64_t(a) * b) % Q); };
+    auto pw = [&](uint32_t a, uint64_t e) {
+        uint64_t r = 1, b = a % Q;
+        for (; e; e >>= 1, b = b * b % Q)
+            if (e & 1) r = r * b % Q;
+        return uint32_t(r);
+    };
+    auto pair = [&](uint32_t w) { return make_uint2(w, uint32_t((uint64_t(w) << 32) / Q)); };
+    auto brv = [&](uint32_t x) {
+        uint32_t r = 0;
+        for (uint32_t i = 0; i < FLOGN; ++i) r |= ((x >> i) & 1u) << (FLOGN - 1 - i);
+        return r;
+    };
+    const uint32_t psi_inv = pw(psi, uint64_t(Q) - 2), omega_inv = mul(psi_inv, psi_inv), n_inv = pw(N, uint64_t(Q) - 2);
+    std::vector<uint2> tw(N), itw(N), sc(N);
+    uint32_t x = 1, xi = n_inv;
+    for (uint32_t i = 0; i < N; ++i) {
+        tw[brv(i)] = pair(x);
+        sc[i] = pair(xi);
+        x = mul(x, psi);
+        xi = mul(xi, psi_inv);
+    }
+    itw[0] = pair(1);
+    for (uint32_t t = 1; t < N; t <<= 1) {
+        const uint32_t step = pw(omega_inv, N / (2 * t));  // omega^-(N/2t): a primitive 2t-th root
+        uint32_t v = 1;
+        for (uint32_t m = 0; m < t; ++m) {
+            itw[t + m] = pair(v);
+            v = mul(v, step);
+        }
+    }
+    cudaError_t e;
+    for (auto pr : {std::make_pair(&F.d_tw2, &tw), std::make_pair(&F.d_itw2, &itw), std::make_pair(&F.d_scale2, &sc)}) {
+        if ((e = cudaMalloc(reinterpret_cast<void**>(pr.first), N * sizeof(uint2))) != cudaSuccess) return e;
+        *dev_bytes += N * sizeof(uint2);
+        if ((e = cudaMemcpyAsync(*pr.first, pr.second->data(), N * sizeof(uint2), cudaMemcpyHostToDevice, st)) != cudaSuccess) return e;
+    }
+    if ((e = cudaStreamSynchronize(st)) != cudaSuccess) return e;
+    F.T.tw2 = F.d_tw2; F.T.itw2 = F.d_itw2; F.T.scale2 = F.d_scale2;
+    for (int i = 0; i < 16; ++i) {
+        F.T.twA[i] = tw[i];
+        F.T.itwA[i] = itw[i];
+    }
+    F.one2 = pair(1);
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&F.sms, cudaDevAttrMultiProcessorCount, dev);
+    return cudaSuccess;
+}
+inline void fast_destroy(FastState& F) {
+    for (uint2* p : {F.d_tw2, F.d_itw2, F.d_scale2})
+        if (p) cudaFree(p);
+    F = FastState{};
+}
 inline cudaError_t fast_load_bk(FastState&, const DevCtx&, cudaStream_t, uint64_t*, uint64_t*) { return cudaSuccess; }
 inline cudaError_t fast_load_pkey(FastState&, const DevCtx&, cudaStream_t, uint64_t*, uint64_t*) { return cudaSuccess; }
-inline cudaError_t fast_blind_rotate(FastState&, const DevCtx&, bool, const GateIO&, uint32_t, cudaStream_t, uint64_t*) { return cudaErrorNotSupported; }
-inline cudaError_t fast_ntt(FastState&, const DevCtx&, uint32_t*, uint64_t, int, cudaStream_t, uint64_t*) { return cudaErrorNotSupported; }
+
+inline cudaError_t fast_blind_rotate(FastState& F, const DevCtx& d, bool gate, const GateIO& io, uint32_t batch, cudaStream_t st,
+                                     uint64_t* launches) {
+    const size_t smem = fast_smem_bytes(d.k, d.n);
+    cudaError_t e;
+    if (gate) {
+        if ((e = cudaFuncSetAttribute(blind_rotate_fast<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem))) != cudaSuccess) return e;
+        blind_rotate_fast<true><<<batch, FT, smem, st>>>(d, F.T, io);
+    } else {
+        if ((e = cudaFuncSetAttribute(blind_rotate_fast<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem))) != cudaSuccess) return e;
+        blind_rotate_fast<false><<<batch, FT, smem, st>>>(d, F.T, io);
+    }
+    ++*launches;
+    return cudaGetLastError();
+}
+
+inline cudaError_t fast_ntt(FastState& F, const DevCtx& d, uint32_t* polys, uint64_t batch, int inverse, cudaStream_t st,
+                            uint64_t* launches) {
+    const unsigned grid = unsigned(std::min<uint64_t>(batch, uint64_t(F.sms) * 8));
+    ntt_batch_fast<<<grid, FT, 0, st>>>(F.T, d.mod.Q, F.one2, polys, batch, inverse);
+    ++*launches;
+    return cudaGetLastError();
+}
+
 }  // namespace mkfhe

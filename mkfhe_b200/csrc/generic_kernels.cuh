@@ -113,18 +113,14 @@ struct GateIO {
     uint32_t* ms_out;         // [B][k][N] mod qKS  (extracted + modulus-switched)
 };
 
-// Shared memory: a[k][N] | D[ell][N] | V[N] | X[N] | crot[k*n] (u16)
-template <bool GATE>
-__global__ void blind_rotate_generic(const DevCtx P, const GateIO io) {
-    extern __shared__ uint32_t sm[];
-    const uint32_t N = P.N, Q = P.mod.Q, k = P.k, n = P.n, ell = P.ell, M = 2 * N;
-    uint32_t* a = sm;
-    uint32_t* D = a + k * N;
-    uint32_t* V = D + ell * N;
-    uint32_t* X = V + N;
-    uint16_t* crot = reinterpret_cast<uint16_t*>(X + N);
-    const uint32_t g = blockIdx.x, tid = threadIdx.x, T = blockDim.x;
+// ---- the three parts of one gate's blind rotation, shared by the generic kernel and (prologue, first step, epilogue) by the
+// specialised one in fast_kernels.cuh.  All threads of the CTA call them; g = gate index. ----
 
+// inputs -> rotation amounts crot[k*n] and the initial accumulator a[k][N] in COEFFICIENT form.  Ends with a barrier.
+template <bool GATE>
+__device__ __forceinline__ void rotate_prologue(const DevCtx& P, const GateIO& io, uint32_t g, uint32_t* a, uint16_t* crot) {
+    const uint32_t N = P.N, Q = P.mod.Q, k = P.k, n = P.n, ell = P.ell, M = 2 * N;
+    const uint32_t tid = threadIdx.x, T = blockDim.x;
     // ---------------- prologue ----------------
     if (GATE) {
         const uint32_t* c1 = io.ct1 + size_t(g) * k * n;
@@ -177,12 +173,17 @@ __global__ void blind_rotate_generic(const DevCtx P, const GateIO io) {
         __syncthreads();
     }
 
-    // ---------------- k*n sequential steps (mk-acc-xzw.cpp:106-129) ----------------
+}
+
+// one step s of EvalAcc (mk-acc-xzw.cpp:106-129 -> AddToAccXZW0 / AddToAccXZW -> HbProd) with rotation c.
+// Scratch: D[ell][N], V[N], X[N].  Entry: a[] visible to all threads.  Ends with a barrier.
+__device__ __forceinline__ void hbprod_step_generic(const DevCtx& P, uint32_t* a, uint32_t* D, uint32_t* V, uint32_t* X, uint32_t s,
+                                                    uint32_t c) {
+    const uint32_t N = P.N, Q = P.mod.Q, k = P.k, n = P.n, ell = P.ell, M = 2 * N;
+    const uint32_t tid = threadIdx.x, T = blockDim.x;
     const size_t per = size_t(ell) * 2 * N;
     const uint32_t* evs = P.bk + size_t(k) * P.S * n * per;
-    for (uint32_t s = 0; s < k * n; ++s) {
-        const uint32_t c = crot[s];
-        if (s > 0 && c == 0) continue;  // X^0 - 1 = 0: HbProd(0) = 0, the step leaves acc unchanged
+    {
         const uint32_t uidx = s / n, i = s - uidx * n;
         const uint32_t cneg = (M - c) & (M - 1);
         KeyView kv;
@@ -262,7 +263,13 @@ __global__ void blind_rotate_generic(const DevCtx P, const GateIO io) {
         }
         __syncthreads();
     }
+}
 
+// a[k][N] (coefficients) -> outputs
+template <bool GATE>
+__device__ __forceinline__ void rotate_epilogue(const DevCtx& P, const GateIO& io, uint32_t g, uint32_t* a) {
+    const uint32_t N = P.N, Q = P.mod.Q, k = P.k, n = P.n, ell = P.ell, M = 2 * N;
+    const uint32_t tid = threadIdx.x, T = blockDim.x;
     // ---------------- epilogue ----------------
     if (GATE) {
         // Transpose + INTT = [a0, -a_{N-1}, ..., -a_1] (poly-impl.h:349-356); then RoundqQ to qKS (mntru-pke.cpp:359-374)
@@ -278,6 +285,25 @@ __global__ void blind_rotate_generic(const DevCtx P, const GateIO io) {
         uint32_t* out = io.acc_out + size_t(g) * k * N;
         for (uint32_t e = tid; e < k * N; e += T) out[e] = a[e];
     }
+}
+
+// Shared memory: a[k][N] | D[ell][N] | V[N] | X[N] | crot[k*n] (u16)
+template <bool GATE>
+__global__ void blind_rotate_generic(const DevCtx P, const GateIO io) {
+    extern __shared__ uint32_t sm[];
+    const uint32_t N = P.N, k = P.k, n = P.n, ell = P.ell;
+    uint32_t* a = sm;
+    uint32_t* D = a + k * N;
+    uint32_t* V = D + ell * N;
+    uint32_t* X = V + N;
+    uint16_t* crot = reinterpret_cast<uint16_t*>(X + N);
+    rotate_prologue<GATE>(P, io, blockIdx.x, a, crot);
+    for (uint32_t s = 0; s < k * n; ++s) {
+        const uint32_t c = crot[s];
+        if (s > 0 && c == 0) continue;  // X^0 - 1 = 0: HbProd(0) = 0, the step leaves acc unchanged
+        hbprod_step_generic(P, a, D, V, X, s, c);
+    }
+    rotate_epilogue<GATE>(P, io, blockIdx.x, a);
 }
 
 // ---- standalone batched NTT: one CTA per polynomial (config 5 and the mkfhe_ntt entry point) ----
