@@ -1,11 +1,14 @@
 // fast_kernels.cuh -- specialised kernels for the production shape N = 2048, digitsG - 1 = 2 (every STD100_* set and the
 // STD128_*_LWE sets of binfhecontext.cpp:91-146), any party count whose accumulator fits shared memory.
 //
-// One CTA of 128 threads owns one gate.  A size-2048 transform is three register passes of 4 + 4 + 3 radix-2 stages with
-// 16 coefficients per thread; between passes the coefficients are transposed through shared memory (one cross-warp
-// exchange with a block barrier, one exchange that stays inside a warp and needs only __syncwarp).  A single XOR swizzle
-// makes every exchange access bank-conflict free.  Butterflies are lazy: no value is reduced below 2^32 until the end,
-// which Q < 2^32 / 32 allows (forward: +2Q per stage; see the bounds next to each routine).
+// One CTA of 256 threads owns one gate.  A size-2048 transform is four register passes of 3 + 3 + 3 + 2 radix-2 stages
+// with 8 coefficients per thread; between passes the coefficients are transposed through shared memory: one exchange
+// crosses warps (block barrier), the other two stay inside a warp (warp w owns coefficients [256 w, 256 w + 256) on both
+// sides, so __syncwarp suffices).  A single XOR swizzle makes every exchange access bank-conflict free.  Butterflies are
+// lazy: no value is reduced below 2^32 until the end, which Q < 2^32 / 32 allows (bounds next to each routine).
+// (A first version used 128 threads x 16 coefficients in three passes: 128 registers per thread, 4 warps per gate, a
+// 100 KB instruction footprint -- ncu showed 16% of stalls waiting for instructions and only 3.5 warps per scheduler;
+// profiles/r1_fast_v1_blind_rotate.txt.  This layout halves the unrolled code and doubles the warps.)
 //
 // Modular multiplication by a known constant (twiddles) is Shoup's: q = mulhi(y, w'), t = y*w - q*Q in [0, 2Q), with
 // w' = floor(w * 2^32 / Q) -- one IMAD.HI (half rate on sm_100a, measured by tools/pipe_microbench.cu) and two IMAD.LO, one
@@ -28,14 +31,14 @@
 
 namespace mkfhe {
 
-constexpr uint32_t FN = 2048, FLOGN = 11, FT = 128;  // ring size, threads per gate
+constexpr uint32_t FN = 2048, FLOGN = 11, FT = 256, FPT = 8;  // ring size, threads per gate, coefficients per thread
 
 struct FastTables {
     const uint2* tw2;     // [N]  forward twiddles, OpenFHE order: psi^i at bitrev(i), as Shoup pairs (w, floor(w 2^32 / Q))
     const uint2* itw2;    // [N]  cyclic inverse (DIT) twiddles: itw2[t + m] = omega^(-m N / 2t), m < t, t = 1, 2, .., N/2
     const uint2* scale2;  // [N]  psi^-i / N  (the twist and the 1/N of the inverse, folded into one Shoup multiply)
-    uint2 twA[16];        // tw2[0..15]: forward pass A twiddles are the same for every thread -> kernel-parameter constants
-    uint2 itwA[16];       // itw2[0..15]
+    uint2 twA[8];         // tw2[0..7]: the first forward pass uses the same twiddles in every thread -> kernel-parameter constants
+    uint2 itwA[4];        // itw2[0..3]
 };
 
 // y * w mod Q in [0, 2Q) for ANY 32-bit y (Harvey's lazy Shoup multiplication)
@@ -46,90 +49,111 @@ __device__ __forceinline__ uint32_t shoup_lazy(uint32_t y, uint2 w, uint32_t Q) 
 // [0, 2Q) -> [0, Q)
 __device__ __forceinline__ uint32_t fold1(uint32_t x, uint32_t Q) { return min(x, x - Q); }
 
-// swizzled position of coefficient j (11 bits) in an exchange buffer: bits 2-3 ^= bits 5-6, bits 3-4 ^= bits 7-8.
-// Keeps 16-byte groups intact (bits 0-1 untouched) so 128-bit accesses stay legal.
-__device__ __forceinline__ uint32_t swz(uint32_t j) { return j ^ (((j >> 5) & 3u) << 2) ^ (((j >> 7) & 3u) << 3); }
+// swizzled position of coefficient j (11 bits) in an exchange buffer: bits 2-4 ^= bits 5-7.  Bits 0-1 are untouched, so
+// 16-byte groups stay intact and 128-bit accesses stay legal.  Conflict-freedom of each access pattern:
+//   j = tid + 256 r, j = 256 w + 32 r + lane : bits 0-4 = lane, the XOR term is constant per instruction
+//   j = 32 (tid >> 2) + 4 r + (tid & 3)      : bits 0-1 and 5-7 vary with the lane -> bank bits (b0, b1, b2^b5, b3^b6, b4^b7)
+//   j = 8 tid + 4 c .. + 3 (128-bit)         : per quarter-warp bits 3-5 vary -> 16-byte bank groups (c^b5, b3^., b4^.) distinct
+__device__ __forceinline__ uint32_t swz(uint32_t j) { return j ^ (((j >> 5) & 7u) << 2); }
+
+#define MKFHE_BFLY(X0, X1, W)                          \
+    {                                                  \
+        const uint32_t t_ = shoup_lazy(X1, W, Q), u_ = X0; \
+        X0 = u_ + t_;                                  \
+        X1 = u_ + twoQ - t_;                           \
+    }
 
 // ---- forward negacyclic NTT, NP polynomials at once (shared twiddles), Cooley-Tukey, natural -> bit-reversed --------
-// in : x[p][r] = coefficient tid + 128 r          (values < 2Q)
-// out: x[p][i] = slot 16 tid + i (OpenFHE order)   (values < 24Q: +2Q per stage, 11 stages)
-// E: NP * 2048 words of shared memory.  Contains one __syncthreads (after the pass-A writes); the caller guarantees that
+// in : x[p][r] = coefficient tid + 256 r          (values < 2Q)
+// out: x[p][i] = slot 8 tid + i (OpenFHE order)    (values < 24Q: +2Q per stage, 11 stages)
+// E: NP * 2048 words of shared memory.  Contains one __syncthreads (after the pass-1 writes); the caller guarantees that
 // every thread is done reading E from its previous use before any thread enters (a barrier lies in between).
 template <int NP>
-__device__ __forceinline__ void fwd_ntt_regs(uint32_t (&x)[NP][16], uint32_t* E, const FastTables& T, uint32_t Q, uint32_t tid) {
+__device__ __forceinline__ void fwd_ntt_regs(uint32_t (&x)[NP][8], uint32_t* E, const FastTables& T, uint32_t Q, uint32_t tid) {
     const uint32_t twoQ = 2 * Q;
-    // pass A: t = 1024, 512, 256, 128
-#pragma unroll
-    for (int s = 0; s < 4; ++s) {
-        const int h = 8 >> s;
-#pragma unroll
-        for (int r = 0; r < 16; ++r) {
-            if (r & h) continue;
-            const uint2 w = T.twA[(1 << s) + (r >> (4 - s))];
-#pragma unroll
-            for (int p = 0; p < NP; ++p) {
-                const uint32_t t = shoup_lazy(x[p][r + h], w, Q), u = x[p][r];
-                x[p][r] = u + t;
-                x[p][r + h] = u + twoQ - t;
-            }
-        }
-    }
-#pragma unroll
-    for (int p = 0; p < NP; ++p)
-#pragma unroll
-        for (int r = 0; r < 16; ++r) E[p * FN + swz(tid + 128 * r)] = x[p][r];
-    __syncthreads();
-    const uint32_t hi4 = tid >> 3, lo3 = tid & 7;
-#pragma unroll
-    for (int p = 0; p < NP; ++p)
-#pragma unroll
-        for (int r = 0; r < 16; ++r) x[p][r] = E[p * FN + swz(hi4 * 128 + 8 * r + lo3)];
-    // pass B: t = 64, 32, 16, 8
-#pragma unroll
-    for (int s = 0; s < 4; ++s) {
-        const int h = 8 >> s;
-        const uint2* tws = T.tw2 + (16 << s) + (hi4 << s);
-#pragma unroll
-        for (int r = 0; r < 16; ++r) {
-            if (r & h) continue;
-            const uint2 w = __ldg(tws + (r >> (4 - s)));
-#pragma unroll
-            for (int p = 0; p < NP; ++p) {
-                const uint32_t t = shoup_lazy(x[p][r + h], w, Q), u = x[p][r];
-                x[p][r] = u + t;
-                x[p][r + h] = u + twoQ - t;
-            }
-        }
-    }
-    // exchange B -> C stays inside the warp: warp w holds coefficients [512 w, 512 w + 512) before and after
-    __syncwarp();
-#pragma unroll
-    for (int p = 0; p < NP; ++p)
-#pragma unroll
-        for (int r = 0; r < 16; ++r) E[p * FN + swz(hi4 * 128 + 8 * r + lo3)] = x[p][r];
-    __syncwarp();
-#pragma unroll
-    for (int p = 0; p < NP; ++p)
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            const uint4 v = *reinterpret_cast<const uint4*>(E + p * FN + swz(16 * tid + 4 * c));
-            x[p][4 * c + 0] = v.x; x[p][4 * c + 1] = v.y; x[p][4 * c + 2] = v.z; x[p][4 * c + 3] = v.w;
-        }
-    // pass C: t = 4, 2, 1
+    const uint32_t wrp = tid >> 5, lane = tid & 31, hi6 = tid >> 2, lo2 = tid & 3;
+    // pass 1: t = 1024, 512, 256  (m = 1, 2, 4 blocks; block of coefficient tid + 256 r at stage s is r >> (3 - s))
 #pragma unroll
     for (int s = 0; s < 3; ++s) {
         const int h = 4 >> s;
-        const uint2* tws = T.tw2 + (256 << s) + tid * (2 << s);
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
+        for (int r = 0; r < 8; ++r) {
+            if (r & h) continue;
+            const uint2 w = T.twA[(1 << s) + (r >> (3 - s))];
+#pragma unroll
+            for (int p = 0; p < NP; ++p) MKFHE_BFLY(x[p][r], x[p][r + h], w);
+        }
+    }
+#pragma unroll
+    for (int p = 0; p < NP; ++p)
+#pragma unroll
+        for (int r = 0; r < 8; ++r) E[p * FN + swz(tid + 256 * r)] = x[p][r];
+    __syncthreads();
+#pragma unroll
+    for (int p = 0; p < NP; ++p)
+#pragma unroll
+        for (int r = 0; r < 8; ++r) x[p][r] = E[p * FN + swz(wrp * 256 + 32 * r + lane)];
+    // pass 2: t = 128, 64, 32  (m = 8, 16, 32; block = (warp << s) + (r >> (3 - s)): the same for all lanes of a warp)
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+        const int h = 4 >> s;
+        const uint2* tws = T.tw2 + (8 << s) + (wrp << s);
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            if (r & h) continue;
+            const uint2 w = __ldg(tws + (r >> (3 - s)));
+#pragma unroll
+            for (int p = 0; p < NP; ++p) MKFHE_BFLY(x[p][r], x[p][r + h], w);
+        }
+    }
+    // the remaining exchanges stay inside the warp: warp w holds coefficients [256 w, 256 w + 256) before and after
+    __syncwarp();
+#pragma unroll
+    for (int p = 0; p < NP; ++p)
+#pragma unroll
+        for (int r = 0; r < 8; ++r) E[p * FN + swz(wrp * 256 + 32 * r + lane)] = x[p][r];
+    __syncwarp();
+#pragma unroll
+    for (int p = 0; p < NP; ++p)
+#pragma unroll
+        for (int r = 0; r < 8; ++r) x[p][r] = E[p * FN + swz(hi6 * 32 + 4 * r + lo2)];
+    // pass 3: t = 16, 8, 4  (m = 64, 128, 256; block = (hi6 << s) + (r >> (3 - s)))
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+        const int h = 4 >> s;
+        const uint2* tws = T.tw2 + (64 << s) + (hi6 << s);
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            if (r & h) continue;
+            const uint2 w = __ldg(tws + (r >> (3 - s)));
+#pragma unroll
+            for (int p = 0; p < NP; ++p) MKFHE_BFLY(x[p][r], x[p][r + h], w);
+        }
+    }
+    __syncwarp();
+#pragma unroll
+    for (int p = 0; p < NP; ++p)
+#pragma unroll
+        for (int r = 0; r < 8; ++r) E[p * FN + swz(hi6 * 32 + 4 * r + lo2)] = x[p][r];
+    __syncwarp();
+#pragma unroll
+    for (int p = 0; p < NP; ++p)
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            const uint4 v = *reinterpret_cast<const uint4*>(E + p * FN + swz(8 * tid + 4 * c));
+            x[p][4 * c + 0] = v.x; x[p][4 * c + 1] = v.y; x[p][4 * c + 2] = v.z; x[p][4 * c + 3] = v.w;
+        }
+    // pass 4: t = 2, 1  (m = 512, 1024; block = (tid << (s + 1)) + (i >> (2 - s)))
+#pragma unroll
+    for (int s = 0; s < 2; ++s) {
+        const int h = 2 >> s;
+        const uint2* tws = T.tw2 + (512 << s) + (tid << (s + 1));
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
             if (i & h) continue;
-            const uint2 w = __ldg(tws + (i >> (3 - s)));
+            const uint2 w = __ldg(tws + (i >> (2 - s)));
 #pragma unroll
-            for (int p = 0; p < NP; ++p) {
-                const uint32_t t = shoup_lazy(x[p][i + h], w, Q), u = x[p][i];
-                x[p][i] = u + t;
-                x[p][i + h] = u + twoQ - t;
-            }
+            for (int p = 0; p < NP; ++p) MKFHE_BFLY(x[p][i], x[p][i + h], w);
         }
     }
 }
@@ -138,74 +162,81 @@ __device__ __forceinline__ void fwd_ntt_regs(uint32_t (&x)[NP][16], uint32_t* E,
 // Written as the cyclic decimation-in-time transform with omega^-1 (Cooley-Tukey butterflies, so growth is additive),
 // followed by one multiplication by psi^-i / N -- the same ring map as the reference's Gentleman-Sande inverse
 // (transformnat-impl.h:491-552), hence the same canonical residues.
-// in : x[i] = slot 16 tid + i, values < 6Q
-// out: x[r] = coefficient tid + 128 r, values in [0, 2Q)
+// in : x[i] = slot 8 tid + i, values < 6Q
+// out: x[r] = coefficient tid + 256 r, values in [0, 2Q)
 // bounds: first stage (twiddle 1, no multiplication) < 12Q, then +2Q per stage: < 32Q < 2^32.
-// E: 2048 words.  One __syncthreads inside (after the pass-2 writes); same entry condition as fwd_ntt_regs.
-__device__ __forceinline__ void inv_ntt_regs(uint32_t (&x)[16], uint32_t* E, const FastTables& T, uint32_t Q, uint32_t tid) {
+// E: 2048 words.  One __syncthreads inside (after the pass-3 writes); same entry condition as fwd_ntt_regs.
+__device__ __forceinline__ void inv_ntt_regs(uint32_t (&x)[8], uint32_t* E, const FastTables& T, uint32_t Q, uint32_t tid) {
     const uint32_t twoQ = 2 * Q, sixQ = 6 * Q;
-    // pass 1: t = 1 (trivial twiddle), 2, 4, 8
+    const uint32_t wrp = tid >> 5, lane = tid & 31, hi6 = tid >> 2, lo2 = tid & 3;
+    // pass 1: t = 1 (twiddle 1), t = 2
 #pragma unroll
-    for (int i = 0; i < 16; i += 2) {
+    for (int i = 0; i < 8; i += 2) {
         const uint32_t u = x[i], v = x[i + 1];
         x[i] = u + v;
         x[i + 1] = u + sixQ - v;
     }
 #pragma unroll
-    for (int s = 1; s < 4; ++s) {
-        const int t = 1 << s;
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-            if (i & t) continue;
-            const uint2 w = T.itwA[t + (i & (t - 1))];
-            const uint32_t v = shoup_lazy(x[i + t], w, Q), u = x[i];
-            x[i] = u + v;
-            x[i + t] = u + twoQ - v;
-        }
+    for (int i = 0; i < 8; ++i) {
+        if (i & 2) continue;
+        MKFHE_BFLY(x[i], x[i + 2], T.itwA[2 + (i & 1)]);
     }
     __syncwarp();
 #pragma unroll
-    for (int c = 0; c < 4; ++c)
-        *reinterpret_cast<uint4*>(E + swz(16 * tid + 4 * c)) = make_uint4(x[4 * c], x[4 * c + 1], x[4 * c + 2], x[4 * c + 3]);
+    for (int c = 0; c < 2; ++c)
+        *reinterpret_cast<uint4*>(E + swz(8 * tid + 4 * c)) = make_uint4(x[4 * c], x[4 * c + 1], x[4 * c + 2], x[4 * c + 3]);
     __syncwarp();
-    const uint32_t hi3 = tid >> 4, lo4 = tid & 15;
 #pragma unroll
-    for (int r = 0; r < 16; ++r) x[r] = E[swz(hi3 * 256 + 16 * r + lo4)];
-    // pass 2: t = 16, 32, 64, 128   (h = t / 16 in register units)
+    for (int r = 0; r < 8; ++r) x[r] = E[swz(hi6 * 32 + 4 * r + lo2)];
+    // pass 2: t = 4, 8, 16  (h = t / 4 in register units; m = 4 (r mod h) + lo2)
 #pragma unroll
-    for (int s = 0; s < 4; ++s) {
+    for (int s = 0; s < 3; ++s) {
         const int h = 1 << s;
-        const uint2* tws = T.itw2 + 16 * h + lo4;
+        const uint2* tws = T.itw2 + 4 * h + lo2;
 #pragma unroll
-        for (int r = 0; r < 16; ++r) {
+        for (int r = 0; r < 8; ++r) {
             if (r & h) continue;
-            const uint2 w = __ldg(tws + 16 * (r & (h - 1)));
-            const uint32_t v = shoup_lazy(x[r + h], w, Q), u = x[r];
-            x[r] = u + v;
-            x[r + h] = u + twoQ - v;
+            const uint2 w = __ldg(tws + 4 * (r & (h - 1)));
+            MKFHE_BFLY(x[r], x[r + h], w);
+        }
+    }
+    // same positions written as read: no hazard inside the warp beyond the one with the next reads
+#pragma unroll
+    for (int r = 0; r < 8; ++r) E[swz(hi6 * 32 + 4 * r + lo2)] = x[r];
+    __syncwarp();
+#pragma unroll
+    for (int r = 0; r < 8; ++r) x[r] = E[swz(wrp * 256 + 32 * r + lane)];
+    // pass 3: t = 32, 64, 128  (h = t / 32; m = 32 (r mod h) + lane)
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+        const int h = 1 << s;
+        const uint2* tws = T.itw2 + 32 * h + lane;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            if (r & h) continue;
+            const uint2 w = __ldg(tws + 32 * (r & (h - 1)));
+            MKFHE_BFLY(x[r], x[r + h], w);
         }
     }
 #pragma unroll
-    for (int r = 0; r < 16; ++r) E[swz(hi3 * 256 + 16 * r + lo4)] = x[r];
+    for (int r = 0; r < 8; ++r) E[swz(wrp * 256 + 32 * r + lane)] = x[r];
     __syncthreads();
 #pragma unroll
-    for (int r = 0; r < 16; ++r) x[r] = E[swz(tid + 128 * r)];
-    // pass 3: t = 256, 512, 1024   (h = t / 128 in register units: 2, 4, 8)
+    for (int r = 0; r < 8; ++r) x[r] = E[swz(tid + 256 * r)];
+    // pass 4: t = 256, 512, 1024  (h = t / 256; m = 256 (r mod h) + tid)
 #pragma unroll
-    for (int s = 1; s < 4; ++s) {
+    for (int s = 0; s < 3; ++s) {
         const int h = 1 << s;
-        const uint2* tws = T.itw2 + 128 * h + tid;
+        const uint2* tws = T.itw2 + 256 * h + tid;
 #pragma unroll
-        for (int r = 0; r < 16; ++r) {
+        for (int r = 0; r < 8; ++r) {
             if (r & h) continue;
-            const uint2 w = __ldg(tws + 128 * (r & (h - 1)));
-            const uint32_t v = shoup_lazy(x[r + h], w, Q), u = x[r];
-            x[r] = u + v;
-            x[r + h] = u + twoQ - v;
+            const uint2 w = __ldg(tws + 256 * (r & (h - 1)));
+            MKFHE_BFLY(x[r], x[r + h], w);
         }
     }
 #pragma unroll
-    for (int r = 0; r < 16; ++r) x[r] = shoup_lazy(x[r], __ldg(T.scale2 + tid + 128 * r), Q);
+    for (int r = 0; r < 8; ++r) x[r] = shoup_lazy(x[r], __ldg(T.scale2 + tid + 256 * r), Q);
 }
 
 // ---- helpers of the specialised step ---------------------------------------------------------------------------------
@@ -271,41 +302,41 @@ __global__ void __launch_bounds__(FT, 4) blind_rotate_fast(const DevCtx P, const
     hbprod_step_generic(P, a, E1, E2, Xs, 0, crot[0]);
 
     const size_t per = size_t(2) * 2 * N;  // words of one UniEncEvalKey: [j][d|f][N]
-    const uint32_t brv7 = __brev(tid) >> 25;
+    const uint32_t brv8 = __brev(tid) >> 24;
     for (uint32_t s = 1; s < k * n; ++s) {
         const uint32_t c = crot[s];
         if (c == 0) continue;  // X^0 - 1 = 0: the step leaves acc unchanged
         const uint32_t u = s / n, i = s - u * n;
         const uint32_t cneg = (M - c) & (M - 1);
-        const uint32_t* ev1 = P.bk + (size_t(u * P.S) * n + i) * per + 16 * tid;
+        const uint32_t* ev1 = P.bk + (size_t(u * P.S) * n + i) * per + 8 * tid;
         const uint32_t* ev2 = xzw ? ev1 + size_t(n) * per : ev1;
-        const uint32_t e0 = cneg * (2 * brv7 + 1);  // exponent of psi for X^-c at this thread's first slot
-        uint32_t keep[16];                          // V while parties are processed, then X of the key owner
-        uint32_t y[16];
+        const uint32_t e0 = cneg * (2 * brv8 + 1);  // exponent of psi for X^-c at this thread's first slot
+        uint32_t keep[8];                           // V while parties are processed, then X of the key owner
+        uint32_t y[8];
 #pragma unroll 1
         for (uint32_t it = 0; it <= k; ++it) {
-            uint32_t D[2][16];
+            uint32_t D[2][8];
             uint32_t p = u;
             if (it < k) {
                 p = (it + 1 < k) ? (it < u ? it : it + 1) : u;
                 const uint32_t* ap = a + p * N;
 #pragma unroll
-                for (int r = 0; r < 16; ++r) decompose2(rot_sub(ap, c, tid + 128 * r, N, Q), Q, g, D[0][r], D[1][r]);
+                for (int r = 0; r < 8; ++r) decompose2(rot_sub(ap, c, tid + 256 * r, N, Q), Q, g, D[0][r], D[1][r]);
             } else {
 #pragma unroll
-                for (int r = 0; r < 16; ++r) decompose2(fold1(y[r], Q), Q, g, D[0][r], D[1][r]);
+                for (int r = 0; r < 8; ++r) decompose2(fold1(y[r], Q), Q, g, D[0][r], D[1][r]);
             }
             fwd_ntt_regs<2>(D, E1, T, Q, tid);
             const int col = it < k ? 0 : 1;  // "d" column for the parties, "f" column for the sumV term
-            const uint32_t* pk = P.pkey + size_t(p) * 2 * N + 16 * tid;
+            const uint32_t* pk = P.pkey + size_t(p) * 2 * N + 8 * tid;
 #pragma unroll
-            for (int ch = 0; ch < 4; ++ch) {
+            for (int ch = 0; ch < 2; ++ch) {
                 uint32_t xn[4] = {0, 0, 0, 0};
                 if (xzw) {
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
-                        const uint32_t b4 = __brev(uint32_t(4 * ch + q)) >> 28;
-                        xn[q] = __ldg(P.psipow + ((e0 + 256u * ((cneg * b4) & 15u)) & (M - 1)));
+                        const uint32_t b3 = __brev(uint32_t(4 * ch + q)) >> 29;  // slot 8 tid + i: bitrev = brv3(i) << 8 | brv8(tid)
+                        xn[q] = __ldg(P.psipow + ((e0 + 512u * ((cneg * b3) & 7u)) & (M - 1)));
                     }
                 }
                 const uint4 k0 = key4(ev1 + (0 * 2 + col) * N + 4 * ch, ev2 + (0 * 2 + col) * N + 4 * ch, xn, xzw, P.mod);
@@ -341,10 +372,10 @@ __global__ void __launch_bounds__(FT, 4) blind_rotate_fast(const DevCtx P, const
             if (it + 1 != k) {  // a_p += result (the owner's V goes on to the next iteration in registers instead)
                 uint32_t* ap = a + p * N;
 #pragma unroll
-                for (int r = 0; r < 16; ++r) {
-                    uint32_t v = ap[tid + 128 * r] + y[r];  // < 3Q
+                for (int r = 0; r < 8; ++r) {
+                    uint32_t v = ap[tid + 256 * r] + y[r];  // < 3Q
                     v = min(v, v - 2 * Q);
-                    ap[tid + 128 * r] = min(v, v - Q);
+                    ap[tid + 256 * r] = min(v, v - Q);
                 }
             }
         }
@@ -354,36 +385,36 @@ __global__ void __launch_bounds__(FT, 4) blind_rotate_fast(const DevCtx P, const
 }
 
 // ---- standalone batched transform (config 5, mkfhe_ntt): one polynomial per CTA-iteration, persistent grid -----------
-__global__ void __launch_bounds__(FT, 8) ntt_batch_fast(const FastTables T, const uint32_t Q, const uint2 one2, uint32_t* polys,
+__global__ void __launch_bounds__(FT, 4) ntt_batch_fast(const FastTables T, const uint32_t Q, const uint2 one2, uint32_t* polys,
                                                         const uint64_t batch, const int inverse) {
     __shared__ __align__(16) uint32_t E[FN];
     const uint32_t tid = threadIdx.x;
     for (uint64_t b = blockIdx.x; b < batch; b += gridDim.x) {
         uint32_t* p = polys + b * FN;
         if (!inverse) {
-            uint32_t x[1][16];
+            uint32_t x[1][8];
 #pragma unroll
-            for (int r = 0; r < 16; ++r) x[0][r] = p[tid + 128 * r];
+            for (int r = 0; r < 8; ++r) x[0][r] = p[tid + 256 * r];
             fwd_ntt_regs<1>(x, E, T, Q, tid);
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
+            for (int c = 0; c < 2; ++c) {
                 uint4 v;
                 v.x = fold1(shoup_lazy(x[0][4 * c + 0], one2, Q), Q);
                 v.y = fold1(shoup_lazy(x[0][4 * c + 1], one2, Q), Q);
                 v.z = fold1(shoup_lazy(x[0][4 * c + 2], one2, Q), Q);
                 v.w = fold1(shoup_lazy(x[0][4 * c + 3], one2, Q), Q);
-                *reinterpret_cast<uint4*>(p + 16 * tid + 4 * c) = v;
+                *reinterpret_cast<uint4*>(p + 8 * tid + 4 * c) = v;
             }
         } else {
-            uint32_t x[16];
+            uint32_t x[8];
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                const uint4 v = *reinterpret_cast<const uint4*>(p + 16 * tid + 4 * c);
+            for (int c = 0; c < 2; ++c) {
+                const uint4 v = *reinterpret_cast<const uint4*>(p + 8 * tid + 4 * c);
                 x[4 * c] = v.x; x[4 * c + 1] = v.y; x[4 * c + 2] = v.z; x[4 * c + 3] = v.w;
             }
             inv_ntt_regs(x, E, T, Q, tid);
 #pragma unroll
-            for (int r = 0; r < 16; ++r) p[tid + 128 * r] = fold1(x[r], Q);
+            for (int r = 0; r < 8; ++r) p[tid + 256 * r] = fold1(x[r], Q);
         }
         __syncthreads();  // E is reused by the next polynomial
     }
@@ -443,10 +474,8 @@ inline cudaError_t fast_init(FastState& F, const DevCtx& d, uint32_t psi, cudaSt
     }
     if ((e = cudaStreamSynchronize(st)) != cudaSuccess) return e;
     F.T.tw2 = F.d_tw2; F.T.itw2 = F.d_itw2; F.T.scale2 = F.d_scale2;
-    for (int i = 0; i < 16; ++i) {
-        F.T.twA[i] = tw[i];
-        F.T.itwA[i] = itw[i];
-    }
+    for (int i = 0; i < 8; ++i) F.T.twA[i] = tw[i];
+    for (int i = 0; i < 4; ++i) F.T.itwA[i] = itw[i];
     F.one2 = pair(1);
     int dev = 0;
     cudaGetDevice(&dev);
@@ -478,7 +507,7 @@ inline cudaError_t fast_blind_rotate(FastState& F, const DevCtx& d, bool gate, c
 
 inline cudaError_t fast_ntt(FastState& F, const DevCtx& d, uint32_t* polys, uint64_t batch, int inverse, cudaStream_t st,
                             uint64_t* launches) {
-    const unsigned grid = unsigned(std::min<uint64_t>(batch, uint64_t(F.sms) * 8));
+    const unsigned grid = unsigned(std::min<uint64_t>(batch, uint64_t(F.sms) * 4));
     ntt_batch_fast<<<grid, FT, 0, st>>>(F.T, d.mod.Q, F.one2, polys, batch, inverse);
     ++*launches;
     return cudaGetLastError();
