@@ -39,6 +39,8 @@ struct FastTables {
     const uint2* scale2;  // [N]  psi^-i / N  (the twist and the 1/N of the inverse, folded into one Shoup multiply)
     uint2 twA[8];         // tw2[0..7]: the first forward pass uses the same twiddles in every thread -> kernel-parameter constants
     uint2 itwA[4];        // itw2[0..3]
+    uint32_t zero;        // 0, opaque to the compiler: makes "u + t" a three-input add, which ptxas maps to IADD3 (alu pipe)
+                          // instead of IMAD.IADD (fma pipe, the saturated one: profiles/r1_fast_v2_blind_rotate.txt)
 };
 
 // y * w mod Q in [0, 2Q) for ANY 32-bit y (Harvey's lazy Shoup multiplication)
@@ -59,7 +61,7 @@ __device__ __forceinline__ uint32_t swz(uint32_t j) { return j ^ (((j >> 5) & 7u
 #define MKFHE_BFLY(X0, X1, W)                          \
     {                                                  \
         const uint32_t t_ = shoup_lazy(X1, W, Q), u_ = X0; \
-        X0 = u_ + t_;                                  \
+        X0 = u_ + t_ + T.zero;                         \
         X1 = u_ + twoQ - t_;                           \
     }
 
@@ -476,6 +478,7 @@ inline cudaError_t fast_init(FastState& F, const DevCtx& d, uint32_t psi, cudaSt
     F.T.tw2 = F.d_tw2; F.T.itw2 = F.d_itw2; F.T.scale2 = F.d_scale2;
     for (int i = 0; i < 8; ++i) F.T.twA[i] = tw[i];
     for (int i = 0; i < 4; ++i) F.T.itwA[i] = itw[i];
+    F.T.zero = 0;
     F.one2 = pair(1);
     int dev = 0;
     cudaGetDevice(&dev);
