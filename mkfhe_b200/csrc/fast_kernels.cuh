@@ -383,7 +383,7 @@ __global__ void __launch_bounds__(FT, 4) blind_rotate_fast(const DevCtx P, const
         }
         __syncthreads();  // a[] complete before the next step's shifted reads
     }
-    rotate_epilogue<GATE>(P, io, blockIdx.x, a);
+    rotate_epilogue<GATE>(P, io, blockIdx.x, a, E1);
 }
 
 // ---- standalone batched transform (config 5, mkfhe_ntt): one polynomial per CTA-iteration, persistent grid -----------

@@ -26,6 +26,13 @@ struct DevCtx {
     const uint32_t* psipow;  // [2N] psi^e, Montgomery form: NTT(X^c) at slot j is psi^(c*(2*bitrev(j)+1) mod 2N)
     const uint32_t* bk;      // bootstrapping key, boundary layout, Montgomery form
     const uint32_t* pkey;    // [k][ell][N], Montgomery form
+    // fused key switch (null ksk16: the gate kernel writes modulus-switched rows to GateIO::ms_out instead)
+    const uint16_t* ksk16;   // [k][ks_rows][npad] u16.  MNTRU: row l = i*dKS + j holds KSK2[u][1][l][.];  MKLWE: row
+                             // (i*baseKS + a0)*dKS + j holds A[u][i][a0][j][.] and, in column n, B[u][i][a0][j]
+    uint32_t npad;           // row length in u16, multiple of 16, >= n (+1 for MKLWE)
+    uint32_t ks_rows;        // rows per party: N*dKS (MNTRU), N*baseKS*dKS (MKLWE)
+    uint32_t ks_shift;       // log2(baseKS) when baseKS is a power of two, else 0
+    uint32_t ks_block;       // coefficients a warp may accumulate in 32 bits before reducing mod qKS
 };
 
 // ---- transforms on polynomials resident in shared memory; all threads of the CTA participate ----
@@ -110,7 +117,9 @@ struct GateIO {
     uint32_t* acc_out;        // [B][k][N] EVALUATION
     // EvalBinGate surface
     const uint32_t *ct1, *ct2, *b1, *b2, *ctnand;
-    uint32_t* ms_out;         // [B][k][N] mod qKS  (extracted + modulus-switched)
+    uint32_t* ms_out;         // [B][k][N] mod qKS  (extracted + modulus-switched); unfused key switch only
+    uint32_t* out;            // [B][k][n] mod qKS  refreshed ciphertexts (fused key switch)
+    uint32_t* bout;           // [B]                MKLWE only
 };
 
 // ---- the three parts of one gate's blind rotation, shared by the generic kernel and (prologue, first step, epilogue) by the
@@ -119,7 +128,7 @@ struct GateIO {
 // inputs -> rotation amounts crot[k*n] and the initial accumulator a[k][N] in COEFFICIENT form.  Ends with a barrier.
 template <bool GATE>
 __device__ __forceinline__ void rotate_prologue(const DevCtx& P, const GateIO& io, uint32_t g, uint32_t* a, uint16_t* crot) {
-    const uint32_t N = P.N, Q = P.mod.Q, k = P.k, n = P.n, ell = P.ell, M = 2 * N;
+    const uint32_t N = P.N, Q = P.mod.Q, k = P.k, n = P.n, M = 2 * N;
     const uint32_t tid = threadIdx.x, T = blockDim.x;
     // ---------------- prologue ----------------
     if (GATE) {
@@ -265,13 +274,95 @@ __device__ __forceinline__ void hbprod_step_generic(const DevCtx& P, uint32_t* a
     }
 }
 
-// a[k][N] (coefficients) -> outputs
-template <bool GATE>
-__device__ __forceinline__ void rotate_epilogue(const DevCtx& P, const GateIO& io, uint32_t g, uint32_t* a) {
-    const uint32_t N = P.N, Q = P.mod.Q, k = P.k, n = P.n, ell = P.ell, M = 2 * N;
+// ---- key switch of one party, fused into the gate kernel (mntru-pke.cpp:763-823 KeySwitch2, mklwe-pke.cpp:260-290 KeySwitch)
+// ms[N]: the party's extracted, modulus-switched row (shared memory).  sums[npad]: zeroed shared accumulators; on return
+// (after the caller's barrier) sums[x] = sum over the selected key rows of column x, each warp's share reduced mod qKS.
+// A warp owns the coefficients i = warp, warp + W, ..; its lanes own 8-byte chunks (4 columns) of the key rows, so every
+// load is a coalesced 256-byte read of one row and the digit is warp-uniform.  MNTRU multiplies the digit-1 row by the
+// digit (KSK2[u][j] = j * KSK2[u][1] mod qKS, mntru-pke.cpp:743-752; zero digits contribute 0 as the reference skips them);
+// MKLWE selects the row of the digit, zero digits included (mklwe-pke.cpp:271-287).
+__device__ __forceinline__ uint2 ldg_stream8(const uint2* p) {
+    uint2 v;  // read-only path, no L1 allocation: the rows are used once per gate and must not evict the twiddle tables
+    asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+    return v;
+}
+template <int DKS>  // 0: run-time digit count
+__device__ __forceinline__ void keyswitch_party(const DevCtx& P, uint32_t u, const uint32_t* ms, uint32_t* sums) {
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5, W = blockDim.x >> 5;
+    const uint32_t dks = DKS ? DKS : P.dKS, chunks = P.npad >> 2, N = P.N, base = P.baseKS, sh = P.ks_shift, q = P.qKS;
+    const bool lwe = P.scheme == 1;
+    const uint2* rows = reinterpret_cast<const uint2*>(P.ksk16) + size_t(u) * P.ks_rows * chunks;
+    for (uint32_t c4 = lane; c4 < chunks; c4 += 32) {
+        uint32_t t0 = 0, t1 = 0, t2 = 0, t3 = 0;
+        for (uint32_t ib = w; ib < N; ib += W * P.ks_block) {
+            uint32_t a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+            const uint32_t iend = min(N, ib + W * P.ks_block);
+#pragma unroll 4
+            for (uint32_t i = ib; i < iend; i += W) {
+                uint32_t v = ms[i];
+#pragma unroll
+                for (uint32_t j = 0; j < (DKS ? DKS : 16); ++j) {
+                    if (!DKS && j >= dks) break;
+                    uint32_t dig;
+                    if (sh) { dig = v & (base - 1); v >>= sh; } else { dig = v % base; v /= base; }
+                    const uint32_t row = lwe ? (i * base + dig) * dks + j : i * dks + j;
+                    const uint2 x = ldg_stream8(rows + size_t(row) * chunks + c4);
+                    const uint32_t m = lwe ? 1u : dig;
+                    a0 += m * (x.x & 0xffffu); a1 += m * (x.x >> 16);
+                    a2 += m * (x.y & 0xffffu); a3 += m * (x.y >> 16);
+                }
+            }
+            t0 = (t0 + a0 % q) % q; t1 = (t1 + a1 % q) % q; t2 = (t2 + a2 % q) % q; t3 = (t3 + a3 % q) % q;
+        }
+        atomicAdd(sums + 4 * c4 + 0, t0); atomicAdd(sums + 4 * c4 + 1, t1);
+        atomicAdd(sums + 4 * c4 + 2, t2); atomicAdd(sums + 4 * c4 + 3, t3);
+    }
+}
+
+// extraction + modulus switch + key switch of one gate, on chip.  Not inlined: it runs once per gate and must not take
+// registers from the blind-rotation loop of the calling kernel.
+__device__ __noinline__ void keyswitch_epilogue(const DevCtx& P, const GateIO& io, uint32_t g, const uint32_t* a, uint32_t* scratch) {
+    const uint32_t N = P.N, Q = P.mod.Q, k = P.k, n = P.n;
     const uint32_t tid = threadIdx.x, T = blockDim.x;
-    // ---------------- epilogue ----------------
-    if (GATE) {
+    // per party: Transpose + INTT = [a0, -a_{N-1}, ..., -a_1] (poly-impl.h:349-356), RoundqQ to qKS
+    // (mntru-pke.cpp:359-374, mklwe-pke.cpp:160-171), then the key switch
+    uint32_t* ms = scratch;
+    uint32_t* sums = scratch + N;
+    uint32_t bsum = 0;  // thread 0: sum over parties of the B column (MKLWE)
+    for (uint32_t u = 0; u < k; ++u) {
+        for (uint32_t e = tid; e < N; e += T) {
+            const uint32_t v = e == 0 ? a[u * N] : a[u * N + N - e];
+            const uint32_t ext = (e == 0 || v == 0) ? v : Q - v;
+            ms[e] = round_qQ(ext, P.qKS, Q);
+        }
+        for (uint32_t x = tid; x < P.npad; x += T) sums[x] = 0;
+        __syncthreads();
+        switch (P.dKS) {
+            case 3: keyswitch_party<3>(P, u, ms, sums); break;
+            case 4: keyswitch_party<4>(P, u, ms, sums); break;
+            default: keyswitch_party<0>(P, u, ms, sums); break;
+        }
+        __syncthreads();
+        uint32_t* o = io.out + (size_t(g) * k + u) * n;
+        for (uint32_t x = tid; x < n; x += T) {
+            const uint32_t s = sums[x] % P.qKS;
+            o[x] = P.scheme == 1 ? (s == 0 ? 0u : P.qKS - s) : s;  // MKLWE: a = 0 - sum A (mklwe-pke.cpp:283-285)
+        }
+        if (P.scheme == 1 && tid == 0) bsum = (bsum + sums[n] % P.qKS) % P.qKS;
+        __syncthreads();
+    }
+    if (P.scheme == 1 && tid == 0)  // b = RoundqQ(Q/8 + 1) - sum B (binfhe-base-scheme.cpp:450-458, mklwe-pke.cpp:277-280)
+        io.bout[g] = submod(round_qQ((Q >> 3) + 1, P.qKS, Q), bsum, P.qKS);
+}
+
+// a[k][N] (coefficients) -> outputs.  scratch: at least N + npad words of shared memory behind a[] (fused key switch).
+template <bool GATE>
+__device__ __forceinline__ void rotate_epilogue(const DevCtx& P, const GateIO& io, uint32_t g, uint32_t* a, uint32_t* scratch) {
+    const uint32_t N = P.N, Q = P.mod.Q, k = P.k;
+    const uint32_t tid = threadIdx.x, T = blockDim.x;
+    if (GATE && P.ksk16 != nullptr) {
+        keyswitch_epilogue(P, io, g, a, scratch);
+    } else if (GATE) {
         // Transpose + INTT = [a0, -a_{N-1}, ..., -a_1] (poly-impl.h:349-356); then RoundqQ to qKS (mntru-pke.cpp:359-374)
         uint32_t* out = io.ms_out + size_t(g) * k * N;
         for (uint32_t x = tid; x < k * N; x += T) {
@@ -303,7 +394,7 @@ __global__ void blind_rotate_generic(const DevCtx P, const GateIO io) {
         if (s > 0 && c == 0) continue;  // X^0 - 1 = 0: HbProd(0) = 0, the step leaves acc unchanged
         hbprod_step_generic(P, a, D, V, X, s, c);
     }
-    rotate_epilogue<GATE>(P, io, blockIdx.x, a);
+    rotate_epilogue<GATE>(P, io, blockIdx.x, a, D);
 }
 
 // ---- standalone batched NTT: one CTA per polynomial (config 5 and the mkfhe_ntt entry point) ----
@@ -337,6 +428,20 @@ __global__ void decompose_generic(const DevCtx P, const uint32_t* in, uint32_t* 
 __global__ void to_montgomery(uint32_t* dst, const uint32_t* src, uint64_t words, Mod mod, uint32_t r2) {
     for (uint64_t x = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x; x < words; x += uint64_t(gridDim.x) * blockDim.x)
         dst[x] = montmul(src[x], r2, mod);
+}
+
+// ---- key-switch keys -> the u16 row layout of the fused key switch (DevCtx::ksk16) ----
+// src rows of n words (row index identical in both layouts); bcol: the MKLWE B vector (one word per row) or null
+__global__ void pack_ksk16(uint16_t* dst, const uint32_t* src, const uint32_t* bcol, uint64_t rows, uint32_t n, uint32_t npad) {
+    const uint64_t total = rows * npad;
+    for (uint64_t t = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x; t < total; t += uint64_t(gridDim.x) * blockDim.x) {
+        const uint64_t r = t / npad;
+        const uint32_t x = uint32_t(t - r * npad);
+        uint32_t v = 0;
+        if (x < n) v = src[r * n + x];
+        else if (x == n && bcol != nullptr) v = bcol[r];
+        dst[t] = static_cast<uint16_t>(v);
+    }
 }
 
 // ---- MNTRU key switch: out[g][u][x] = sum_l digit_l(ms[g][u]) * KSK[u][l][x] mod qKS  (mntru-pke.cpp:763-823) ----

@@ -34,6 +34,8 @@ struct mkfhe_ctx {
     uint32_t *tw{nullptr}, *twi{nullptr}, *psipow{nullptr};
     // keys
     uint32_t *bk{nullptr}, *pkey{nullptr}, *ksk_mntru{nullptr}, *kskA{nullptr}, *kskB{nullptr}, *ctnand{nullptr};
+    uint16_t* ksk16{nullptr};  // fused key switch: u16 rows (generic_kernels.cuh, DevCtx::ksk16)
+    bool fuse_ks{false};
     // workspaces (grown on demand)
     uint32_t* ws_ms{nullptr};
     size_t ws_ms_words{0};
@@ -136,6 +138,28 @@ static int upload(mkfhe_ctx* ctx, uint32_t** dst, const uint32_t* src, uint64_t 
     return MKFHE_OK;
 }
 
+// key-switch key -> u16 rows in HBM (fused key switch).  src/bcol: host or device; staged through a temporary device copy.
+static int upload_ksk16(mkfhe_ctx* ctx, const uint32_t* src, uint64_t words, const uint32_t* bcol, uint64_t rows) {
+    const uint32_t n = ctx->p.n, npad = ctx->d.npad;
+    uint32_t *tmp = nullptr, *tmpb = nullptr;
+    CU(cudaMalloc(&tmp, words * 4));
+    if (bcol) CU(cudaMalloc(&tmpb, rows * 4));
+    if (!ctx->ksk16) {
+        CU(cudaMalloc(&ctx->ksk16, rows * npad * sizeof(uint16_t)));
+        ctx->dev_bytes += rows * npad * sizeof(uint16_t);
+    }
+    CU(cudaMemcpyAsync(tmp, src, words * 4, cudaMemcpyDefault, ctx->stream));
+    if (bcol) CU(cudaMemcpyAsync(tmpb, bcol, rows * 4, cudaMemcpyDefault, ctx->stream));
+    pack_ksk16<<<148 * 16, 256, 0, ctx->stream>>>(ctx->ksk16, tmp, tmpb, rows, n, npad);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(ctx->stream));
+    cudaFree(tmp);
+    if (tmpb) cudaFree(tmpb);
+    ctx->d.ksk16 = ctx->ksk16;
+    return MKFHE_OK;
+}
+
 extern "C" {
 
 const char* mkfhe_version(void) { return MKFHE_VERSION_STR; }
@@ -226,6 +250,18 @@ int mkfhe_ctx_create(const mkfhe_params* p, mkfhe_ctx** out) {
         return bail(fail(ctx, MKFHE_ECUDA, "fast path initialisation failed: %s", cudaGetErrorString(cudaGetLastError())));
     }
     if (getenv("MKFHE_FORCE_GENERIC")) ctx->use_fast = false;
+    // fused key switch: keys as u16 rows, the gate kernel finishes the gate on chip.  Needs qKS < 2^16 and N + npad words of
+    // scratch behind the accumulator ((ell + 2) * N words exist in both kernels).
+    d.npad = (p->n + (p->scheme == MKFHE_SCHEME_MKLWE ? 1u : 0u) + 15u) & ~15u;
+    d.ks_rows = p->scheme == MKFHE_SCHEME_MKLWE ? N * p->baseKS * p->dKS : N * p->dKS;
+    d.ks_shift = 0;
+    if ((p->baseKS & (p->baseKS - 1)) == 0)
+        while ((1u << d.ks_shift) < p->baseKS) ++d.ks_shift;
+    {
+        const uint64_t per = uint64_t(p->dKS) * (p->scheme == MKFHE_SCHEME_MKLWE ? 1u : p->baseKS - 1) * (p->qKS - 1);
+        d.ks_block = uint32_t(std::max<uint64_t>(1, std::min<uint64_t>(N, 0xffffffffull / std::max<uint64_t>(per, 1))));
+    }
+    ctx->fuse_ks = p->qKS < 65536 && size_t(N) + d.npad <= size_t(d.ell + 2) * N && !getenv("MKFHE_UNFUSED_KEYSWITCH");
     *out = ctx;
     return MKFHE_OK;
 }
@@ -238,6 +274,7 @@ void mkfhe_ctx_destroy(mkfhe_ctx* ctx) {
     for (uint32_t* p : {ctx->tw, ctx->twi, ctx->psipow, ctx->bk, ctx->pkey, ctx->ksk_mntru, ctx->kskA, ctx->kskB, ctx->ctnand,
                         ctx->ws_ms, ctx->ws_raw, ctx->ws_io})
         if (p) cudaFree(p);
+    if (ctx->ksk16) cudaFree(ctx->ksk16);
     for (auto& e : ctx->ev)
         if (e) cudaEventDestroy(e);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
@@ -287,6 +324,7 @@ int mkfhe_load_ksk_mntru(mkfhe_ctx* ctx, const uint32_t* ksk, uint64_t words) {
     if (ctx->p.scheme != MKFHE_SCHEME_MNTRU) return fail(ctx, MKFHE_EINVAL, "context is not MNTRU");
     if (words != uint64_t(ctx->p.k) * ctx->p.N * ctx->p.dKS * ctx->p.n) return fail(ctx, MKFHE_EINVAL, "mkfhe_load_ksk_mntru: wrong size");
     CU(cudaSetDevice(ctx->device));
+    if (ctx->fuse_ks) return upload_ksk16(ctx, ksk, words, nullptr, uint64_t(ctx->p.k) * ctx->d.ks_rows);
     return upload(ctx, &ctx->ksk_mntru, ksk, words, false);
 }
 int mkfhe_load_ksk_mklwe(mkfhe_ctx* ctx, const uint32_t* A, uint64_t wordsA, const uint32_t* B, uint64_t wordsB) {
@@ -295,6 +333,7 @@ int mkfhe_load_ksk_mklwe(mkfhe_ctx* ctx, const uint32_t* A, uint64_t wordsA, con
     const uint64_t rows = uint64_t(ctx->p.k) * ctx->p.N * ctx->p.baseKS * ctx->p.dKS;
     if (wordsB != rows || wordsA != rows * ctx->p.n) return fail(ctx, MKFHE_EINVAL, "mkfhe_load_ksk_mklwe: wrong size");
     CU(cudaSetDevice(ctx->device));
+    if (ctx->fuse_ks) return upload_ksk16(ctx, A, wordsA, B, rows);
     int rc = upload(ctx, &ctx->kskA, A, wordsA, false);
     if (rc) return rc;
     return upload(ctx, &ctx->kskB, B, wordsB, false);
@@ -379,20 +418,24 @@ int mkfhe_eval_nand_dev(mkfhe_ctx* ctx, const uint32_t* d_ct1, const uint32_t* d
     const mkfhe_params& p = ctx->p;
     const bool lwe = p.scheme == MKFHE_SCHEME_MKLWE;
     if (lwe && (!d_b1 || !d_b2 || !d_bout)) return fail(ctx, MKFHE_EINVAL, "MKLWE gates need b1, b2 and bout");
-    if (lwe ? (!ctx->kskA || !ctx->kskB) : (!ctx->ksk_mntru || !ctx->ctnand))
+    const bool have_ksk = ctx->fuse_ks ? ctx->ksk16 != nullptr : (lwe ? (ctx->kskA && ctx->kskB) : ctx->ksk_mntru != nullptr);
+    if (!have_ksk || (!lwe && !ctx->ctnand))
         return fail(ctx, MKFHE_ENOKEY, lwe ? "MKLWE key-switch key not loaded" : "MNTRU key-switch key / ctNAND not loaded");
     if (batch == 0) return MKFHE_OK;
     CU(cudaSetDevice(ctx->device));
-    int rc = grow(ctx, &ctx->ws_ms, &ctx->ws_ms_words, size_t(batch) * p.k * p.N);
+    int rc = ctx->fuse_ks ? MKFHE_OK : grow(ctx, &ctx->ws_ms, &ctx->ws_ms_words, size_t(batch) * p.k * p.N);
     if (rc) return rc;
     GateIO io{};
     io.ct1 = d_ct1; io.ct2 = d_ct2; io.b1 = d_b1; io.b2 = d_b2; io.ctnand = ctx->ctnand; io.ms_out = ctx->ws_ms;
+    io.out = d_out; io.bout = d_bout;
     CU(cudaEventRecord(ctx->ev[0], ctx->stream));
     rc = launch_rotate(ctx, true, io, batch);
     if (rc) return rc;
     CU(cudaEventRecord(ctx->ev[1], ctx->stream));
     const uint32_t B = uint32_t(batch);
-    if (!lwe) {
+    if (ctx->fuse_ks) {
+        // the gate kernel did the key switch on chip (rotate_epilogue)
+    } else if (!lwe) {
         dim3 grid((p.n + 63) / 64, (B + 63) / 64, p.k);
         keyswitch_mntru_generic<<<grid, 256, 0, ctx->stream>>>(ctx->d, ctx->ws_ms, ctx->ksk_mntru, d_out, B);
         ctx->launches++;

@@ -83,3 +83,23 @@ def test_errors_and_edge_cases(fx):
     # wrong key size is rejected, not read out of bounds
     with pytest.raises(mk.MkfheError):
         ctx.LoadKeys(g["bk"][:-1], g["pkey"])
+
+
+@pytest.mark.parametrize("name", ["toy_mkntru_k4_N256", "toy_mklwe_k2_N128"])
+def test_unfused_key_switch_path(name, monkeypatch):
+    """the stand-alone key-switch kernels (used when qKS >= 2^16 rules out the u16 rows of the fused epilogue)"""
+    from gpu_util import ctx_from_params, load_fixture_keys
+
+    monkeypatch.setenv("MKFHE_UNFUSED_KEYSWITCH", "1")
+    g = load_golden(name)
+    p = g["p"]
+    ctx = ctx_from_params(p)
+    try:
+        load_fixture_keys(ctx, g)
+        if p.scheme == 0:
+            assert (ctx.EvalBinGate("NAND", g["g_ct1"], g["g_ct2"]) == g["g_out"]).all()
+        else:
+            out, bout = ctx.EvalBinGate("NAND", g["g_ct1"], g["g_ct2"], g["g_b1"], g["g_b2"])
+            assert (out == g["g_out"]).all() and (bout == g["g_bout"]).all()
+    finally:
+        ctx.close()
