@@ -205,11 +205,39 @@ def workload_config(args, batch=None):
             "l2": "L2 flushed (256 MiB write) between timed steps", "parallelism": f"gates sharded x{args.gpus}, keys replicated"}
 
 
+def make_oracle(P):
+    from oracle import portapi
+
+    return portapi.Oracle(k=P.k, N=P.N, Q=P.Q, psi=P.psi, q=P.q, qKS=P.qKS, n=P.n, baseG_log2=P.baseG_log2, digitsG=P.digitsG,
+                          baseKS=P.baseKS, dKS=P.dKS, variant=P.variant, scheme=P.scheme)
+
+
+def check_against_oracle(P, keys, ct1, b1, ct2, b2, out, bout, count):
+    """Bit-exact check of `count` gates (first, last, evenly spread) against the CPU oracle, outside the timed region.
+    The oracle is the checker here, never the thing measured."""
+    if not count:
+        return 0
+    o = make_oracle(P)
+    B = len(out)
+    idx = sorted(set(int(x) for x in np.linspace(0, B - 1, count)))
+    t0 = time.time()
+    for i in idx:
+        eo, eb = o.eval_nand(keys["bk"], keys["pkey"], keys.get("kskA", keys.get("ksk")), keys.get("kskB"), keys.get("ctnand"),
+                             np.ascontiguousarray(ct1[i]).ravel(), int(b1[i]) if b1 is not None else 0,
+                             np.ascontiguousarray(ct2[i]).ravel(), int(b2[i]) if b2 is not None else 0)
+        ok = (out[i].ravel() == eo).all() and (bout is None or int(bout[i]) == eb)
+        if not ok:
+            raise SystemExit(f"bench.py: gate {i} differs from the oracle")
+    log(f"[bench] {len(idx)} gates bit-exact vs the CPU oracle ({time.time() - t0:.1f}s)")
+    return len(idx)
+
+
 # ---------------------------------------------------------------- GPU arm
 def run_gpu_arm(args):
     import torch
 
     import mkfhe_b200 as mk
+    from mkfhe_b200 import shard
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -236,25 +264,12 @@ def run_gpu_arm(args):
     P.device = local
     ctx = mk.BinFHEContext().GenerateFromParams(P)
     lwe = ctx.is_lwe
-    names = ["bk", "pkey"] + (["kskA", "kskB"] if lwe else ["ksk", "ctnand"])
-    t_bcast = 0.0
-    dkeys = {}
-    for nme in names:
-        if rank == 0:
-            t = torch.from_numpy(keys[nme].view(np.int32)).to(dev)
-            size = torch.tensor([t.numel()], dtype=torch.int64, device=dev)
-        else:
-            size = torch.zeros(1, dtype=torch.int64, device=dev)
-        if world > 1:
-            dist.broadcast(size, 0)
-            if rank != 0:
-                t = torch.empty(int(size.item()), dtype=torch.int32, device=dev)
-            torch.cuda.synchronize()
-            t0 = time.time()
-            dist.broadcast(t, 0)
-            torch.cuda.synchronize()
-            t_bcast += time.time() - t0
-        dkeys[nme] = t
+    # keys: rank 0 -> every rank, device to device (mkfhe_b200/shard.py)
+    torch.cuda.synchronize()
+    t0 = time.time()
+    dkeys = shard.broadcast_keys(keys, dev, dist)
+    torch.cuda.synchronize()
+    t_bcast = time.time() - t0 if world > 1 else 0.0
     ctx.LoadKeys(dkeys["bk"], dkeys["pkey"], ksk=dkeys.get("ksk"), kskA=dkeys.get("kskA"), kskB=dkeys.get("kskB"),
                  ctnand=dkeys.get("ctnand"))
     key_bytes_total = sum(t.numel() * 4 for t in dkeys.values())
@@ -357,8 +372,7 @@ def run_gpu_arm(args):
     tt = torch.tensor([dev_ms, e2e_s * 1e3, sum(rot_ms), sum(ks_ms)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)  # max over ranks
-        gathered = [torch.empty_like(d_out) for _ in range(world)] if rank == 0 else None
-        dist.gather(d_out, gathered, dst=0)  # results gathered to rank 0 (outside the timed region)
+    gathered = shard.gather_results(d_out, B * world, dist)  # results to rank 0 (outside the timed region)
     dev_ms, e2e_ms, rot_sum, ks_sum = (float(x) for x in tt.tolist())
 
     if rank == 0:
@@ -372,6 +386,9 @@ def run_gpu_arm(args):
             got = [ref.decrypt(out_np[i].ravel(), int(bo[i])) for i in idx]
             assert got == [int(expect[i]) for i in idx], "bootstrapped gates do not decrypt to NAND"
             checked = len(idx)
+        oracle_checked = check_against_oracle(P, keys, ct1, b1, ct2, b2, out_np,
+                                              d_bout.cpu().numpy().view(np.uint32) if lwe else None, args.check_oracle)
+        assert gathered is None or (gathered[:B].cpu().numpy().view(np.uint32) == out_np).all()
         wm = work_model(P)
         total_gates = B * world * args.steps
         value = total_gates / (dev_ms * 1e-3)
@@ -406,7 +423,7 @@ def run_gpu_arm(args):
                              "bytes_per_gate": wm["key_bytes"], "note": "algorithmic key bytes if every gate streamed its own copy"},
             "kernels_ms": {"blind_rotate": rot_sum / args.steps, "key_switch": ks_sum / args.steps},
             "clocks": clocks, "wall_s_timed": wall, "key_bytes_replicated": key_bytes_total, "key_broadcast_s": t_bcast,
-            "nand_checked": checked,
+            "nand_checked": checked, "oracle_checked": oracle_checked,
         }
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
@@ -421,6 +438,221 @@ def run_gpu_arm(args):
         dist.destroy_process_group()
 
 
+# ---------------------------------------------------------------- configs[3]: a fixed job sharded over the GPUs
+def run_sharded_arm(args):
+    """--workload sharded: --total-gates NAND gates (default paramset STD100_MKNTRU_2, k = 4) split into contiguous shards,
+    one per GPU; keys replicated by broadcast; inputs counter-based (mkfhe_b200/shard.py) and generated on the device by the
+    rank that owns them; one step = every rank bootstraps its whole shard in launches of --chunk gates.  Strong scaling:
+    the job is fixed.  The XOR digest of all outputs does not depend on the number of GPUs."""
+    import torch
+
+    import mkfhe_b200 as mk
+    from mkfhe_b200 import shard
+
+    rank, world, local = (int(os.environ.get(v, "0")) for v in ("RANK", "WORLD_SIZE", "LOCAL_RANK"))
+    world = max(world, 1)
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the GPU arm has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=dev)
+    method = mk.MKNTRU_LWE if "LWE" in args.paramset else mk.MKNTRU
+    P = mk.derive_params(mk.PARAMSETS[args.paramset], method)
+    keys = None
+    if rank == 0:
+        os.environ["MKFHE_BENCH_SYNTHETIC_KEYS"] = "1"  # uniform key residues: the job is about sharding and throughput
+        _, keys, *_ = make_workload(args.paramset, method, 1, seed=4)
+    P.device = local
+    ctx = mk.BinFHEContext().GenerateFromParams(P)
+    lwe = ctx.is_lwe
+    torch.cuda.synchronize()
+    t0 = time.time()
+    dkeys = shard.broadcast_keys(keys, dev, dist)
+    torch.cuda.synchronize()
+    t_bcast = time.time() - t0
+    ctx.LoadKeys(dkeys["bk"], dkeys["pkey"], ksk=dkeys.get("ksk"), kskA=dkeys.get("kskA"), kskB=dkeys.get("kskB"),
+                 ctnand=dkeys.get("ctnand"))
+    key_bytes_total = sum(t.numel() * 4 for t in dkeys.values())
+    del dkeys
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    ctx.set_stream(stream.cuda_stream)
+    T, seed = args.total_gates, 4
+    lo, hi = shard.shard_range(T, world, rank)
+    chunks = [(a, min(hi, a + args.chunk)) for a in range(lo, hi, args.chunk)]
+
+    def run_shard(collect):
+        ms, digest, sample = 0.0, 0, None
+        for a, b in chunks:
+            inp = shard.gate_inputs_torch(P, seed, a, b, dev)  # not timed: input synthesis is not part of the path
+            out = torch.empty_like(inp["ct1"])
+            bout = torch.empty(b - a, dtype=torch.int32, device=dev) if lwe else None
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            ctx.EvalBinGateDevice(inp["ct1"], inp["ct2"], out, inp.get("b1"), inp.get("b2"), bout)
+            e1.record(stream)
+            e1.synchronize()
+            ms += e0.elapsed_time(e1)
+            if collect:
+                o = out.cpu().numpy().view(np.uint32)
+                digest ^= shard.xor_hash_np(o, a)
+                if a == lo:
+                    sample = (o[0].copy(), int(bout[0].item()) & 0xffffffff if lwe else 0)
+        return ms, digest, sample
+
+    for _ in range(args.warmup):  # warm-up on the first chunk only (the job itself is minutes long)
+        a, b = chunks[0]
+        inp = shard.gate_inputs_torch(P, seed, a, min(b, a + 592), dev)
+        ctx.EvalBinGateDevice(inp["ct1"], inp["ct2"], torch.empty_like(inp["ct1"]), inp.get("b1"), inp.get("b2"),
+                              torch.empty(inp["ct1"].shape[0], dtype=torch.int32, device=dev) if lwe else None)
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    launches0 = ctx.launch_count()
+    total_ms, digest, sample = 0.0, 0, None
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    wall0 = time.time()
+    for step in range(args.steps):
+        ms, d, smp = run_shard(collect=(step == args.steps - 1))
+        total_ms += ms
+        digest, sample = d, smp
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    wall = time.time() - wall0
+    launches = ctx.launch_count() - launches0
+    clocks = sampler.stop() if rank == 0 else None
+    tt = torch.tensor([total_ms], dtype=torch.float64, device=dev)
+    digests = [digest]
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        digests = [None] * world
+        dist.all_gather_object(digests, digest)
+    if rank == 0:
+        total_ms = float(tt.item())
+        h = 0
+        for d in digests:
+            h ^= d
+        checked = 0
+        if args.check_oracle:  # gate `lo` of rank 0 regenerated on the CPU from its counter and re-computed by the oracle
+            g = shard.gate_inputs_np(P, seed, [0])
+            o = make_oracle(P)
+            eo, eb = o.eval_nand(keys["bk"], keys["pkey"], keys.get("kskA", keys.get("ksk")), keys.get("kskB"), keys.get("ctnand"),
+                                 g["ct1"][0].ravel(), int(g["b1"][0]) if lwe else 0, g["ct2"][0].ravel(), int(g["b2"][0]) if lwe else 0)
+            if not ((sample[0].ravel() == eo).all() and (not lwe or sample[1] == eb)):
+                raise SystemExit("bench.py: gate 0 differs from the oracle")
+            checked = 1
+        wm = work_model(P)
+        value = T * args.steps / (total_ms * 1e-3)
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+                "dtype": "u32", "data": "synthetic: uniform key residues, counter-based uniform ciphertexts (seed 4 ^ gate index)",
+                "config": {"workload": f"{args.paramset} k={P.k}, {T} independent NAND bootstraps sharded over {world} GPU(s)",
+                           "paramset": args.paramset, "total_gates": T, "chunk": args.chunk,
+                           "l2": "inputs of one step (>= 147 MB per launch) exceed L2; keys are re-streamed per launch",
+                           "parallelism": f"gates sharded x{world}, keys replicated"},
+                "gpu_launches": int(launches), "output_xor_digest": f"{h:016x}", "oracle_checked": checked,
+                "roofline": {"bound": "int32", "kernel": "blind_rotate", "achieved": wm["instr"] * value / world / 1e12,
+                             "unit": "Tinstr/s per GPU", "instr_per_gate": wm["instr"], "modmul_per_gate": wm["modmul"]},
+                "clocks": clocks, "wall_s_timed": wall, "key_bytes_replicated": key_bytes_total, "key_broadcast_s": t_bcast}
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+# ---------------------------------------------------------------- configs[4]: batched transform micro-benchmark
+def run_ntt_arm(args):
+    """--workload ntt: NativePoly::SetFormat on --ntt-batch polynomials of --ntt-n coefficients (forward, then inverse), in
+    place in HBM.  Parity of a sample against the CPU oracle and the round-trip identity on all, outside the timed region."""
+    import torch
+
+    import mkfhe_b200 as mk
+    from mkfhe_b200 import context as mctx
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the GPU arm has no CPU fallback")
+    dev = torch.device("cuda", 0)
+    N, B = args.ntt_n, args.ntt_batch
+    Q = mctx.previous_prime(mctx.first_prime(27, 2 * N), 2 * N)
+    psi = mctx.root_of_unity(2 * N, Q)
+    P = mk.derive_params(mk.PARAMSETS["STD100_MKNTRU"], mk.MKNTRU)
+    P.N, P.Q, P.psi, P.device = N, Q, psi, 0
+    ctx = mk.BinFHEContext().GenerateFromParams(P)
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    ctx.set_stream(stream.cuda_stream)
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(5)
+    x = torch.randint(0, Q, (B, N), dtype=torch.int32, device=dev, generator=gen)
+    x0 = x.clone()
+    for _ in range(args.warmup):
+        ctx.NTTDevice(x, inverse=False)
+        ctx.NTTDevice(x, inverse=True)
+    torch.cuda.synchronize()
+    assert torch.equal(x, x0), "round trip is not the identity"
+    sampler = ClockSampler(0)
+    sampler.start()
+    launches0 = ctx.launch_count()
+    fwd_ms, inv_ms = [], []
+    for _ in range(args.steps):
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        e[0].record(stream)
+        ctx.NTTDevice(x, inverse=False)
+        e[1].record(stream)
+        ctx.NTTDevice(x, inverse=True)
+        e[2].record(stream)
+        e[2].synchronize()
+        fwd_ms.append(e[0].elapsed_time(e[1]))
+        inv_ms.append(e[1].elapsed_time(e[2]))
+    launches = ctx.launch_count() - launches0
+    clocks = sampler.stop()
+    assert torch.equal(x, x0), "round trip is not the identity"
+    # parity sample vs the CPU oracle (1024 polynomials)
+    o = make_oracle(P)
+    samp = x0[:: max(1, B // 1024)][:1024].contiguous()
+    want = o.ntt(samp.cpu().numpy().view(np.uint32), inverse=False)
+    y = samp.clone()
+    ctx.NTTDevice(y, inverse=False)
+    torch.cuda.synchronize()
+    assert (y.cpu().numpy().view(np.uint32) == want).all(), "forward transform differs from the oracle"
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    imad_peak = ctx.measure_int32_peak()
+    tf, ti = sum(fwd_ms) / len(fwd_ms) * 1e-3, sum(inv_ms) / len(inv_ms) * 1e-3
+    bytes_per = 2 * N * 4
+    bfly = (N // 2) * (N.bit_length() - 1)
+    value = 2 * B / (tf + ti)
+    line = {"metric": "negacyclic NTT transforms/sec", "value": value, "unit": "transforms/s", "n_gpus": 1, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": (tf + ti) * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "u32", "data": "synthetic: uniform residues (torch philox, seed 5)",
+            "config": {"workload": f"NTT + INTT micro-benchmark, N={N}, Q={Q}, batch {B} polynomials in HBM",
+                       "l2": f"working set {B * N * 4 >> 20} MiB exceeds L2"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": "ntt_batch (forward)", "achieved": B * bytes_per / tf / 1e9, "peak": hbm_peak,
+                         "unit": "GB/s", "frac": B * bytes_per / tf / 1e9 / hbm_peak, "traffic": None,
+                         "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback 6650"},
+            "roofline_inverse": {"bound": "hbm", "achieved": B * bytes_per / ti / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                                 "frac": B * bytes_per / ti / 1e9 / hbm_peak},
+            "roofline_int32": {"achieved": B * bfly * 7 / tf / 1e12, "peak": imad_peak / 1e12, "unit": "Tinstr/s",
+                               "frac": B * bfly * 7 / tf / imad_peak, "model": "7 instr / butterfly"},
+            "forward_ms": tf * 1e3, "inverse_ms": ti * 1e3, "oracle_checked": int(len(samp)), "clocks": clocks}
+    print(json.dumps(line), flush=True)
+    ctx.close()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -432,9 +664,25 @@ def main():
     ap.add_argument("--ref-gates-per-thread", type=int, default=8, help="--impl reference: gates per host thread per step")
     ap.add_argument("--cpu-baseline-gates-per-thread", type=int, default=32)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--synthetic-keys", action="store_true", help="uniform random key residues instead of the reference keygen "
+                    "(throughput does not depend on key values; the reference's keygen takes minutes at k >= 8)")
+    ap.add_argument("--check-oracle", type=int, default=0, help="gates to re-compute on the CPU oracle after the run")
+    ap.add_argument("--workload", default="gates", choices=["gates", "sharded", "ntt"],
+                    help="gates: configs[1]/[2] (batch per GPU); sharded: configs[3] (--total-gates split over the GPUs, "
+                         "counter-based inputs); ntt: configs[4] (batched transform micro-benchmark)")
+    ap.add_argument("--total-gates", type=int, default=1 << 17)
+    ap.add_argument("--chunk", type=int, default=16384, help="sharded: gates per launch")
+    ap.add_argument("--ntt-n", type=int, default=2048)
+    ap.add_argument("--ntt-batch", type=int, default=1 << 18)
     args = ap.parse_args()
+    if args.synthetic_keys:
+        os.environ["MKFHE_BENCH_SYNTHETIC_KEYS"] = "1"
     if args.impl == "reference":
         run_reference_arm(args)
+    elif args.workload == "sharded":
+        run_sharded_arm(args)
+    elif args.workload == "ntt":
+        run_ntt_arm(args)
     else:
         run_gpu_arm(args)
 
