@@ -39,6 +39,27 @@ def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
+_REAL_STDOUT = None
+
+
+def capture_stdout():
+    """Libraries (NCCL's version banner, for one) write to fd 1; the contract is ONE JSON line on stdout.  Point fd 1 at
+    stderr for the duration of the run and keep the real stdout for emit()."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line: dict):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 # ---------------------------------------------------------------- algorithmic work (SURVEY.md section 8d)
 def work_model(P):
     """modmul/gate and cost-model instructions/gate: S*(T*beta + Pw) with 7 instr per butterfly, 5 per pointwise MAC."""
@@ -195,7 +216,7 @@ def run_reference_arm(args):
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_config(args, batch=None):
@@ -431,7 +452,7 @@ def run_gpu_arm(args):
             gps, kind, secs = cpu_gates_per_s(args.paramset, cores, gates, ref)
             line["cpu_baseline"] = {"value": gps, "unit": UNIT, "cores": cores, "kind": kind,
                                     "sample": f"{gates} EvalBinGate(NAND) on {cores} threads in {secs:.1f}s, same paramset"}
-        print(json.dumps(line), flush=True)
+        emit(line)
     ctx.close()
     if world > 1:
         dist.barrier()
@@ -562,7 +583,7 @@ def run_sharded_arm(args):
                 "roofline": {"bound": "int32", "kernel": "blind_rotate", "achieved": wm["instr"] * value / world / 1e12,
                              "unit": "Tinstr/s per GPU", "instr_per_gate": wm["instr"], "modmul_per_gate": wm["modmul"]},
                 "clocks": clocks, "wall_s_timed": wall, "key_bytes_replicated": key_bytes_total, "key_broadcast_s": t_bcast}
-        print(json.dumps(line), flush=True)
+        emit(line)
     ctx.close()
     if world > 1:
         dist.barrier()
@@ -649,7 +670,7 @@ def run_ntt_arm(args):
             "roofline_int32": {"achieved": B * bfly * 7 / tf / 1e12, "peak": imad_peak / 1e12, "unit": "Tinstr/s",
                                "frac": B * bfly * 7 / tf / imad_peak, "model": "7 instr / butterfly"},
             "forward_ms": tf * 1e3, "inverse_ms": ti * 1e3, "oracle_checked": int(len(samp)), "clocks": clocks}
-    print(json.dumps(line), flush=True)
+    emit(line)
     ctx.close()
 
 
@@ -677,6 +698,7 @@ def main():
     args = ap.parse_args()
     if args.synthetic_keys:
         os.environ["MKFHE_BENCH_SYNTHETIC_KEYS"] = "1"
+    capture_stdout()
     if args.impl == "reference":
         run_reference_arm(args)
     elif args.workload == "sharded":

@@ -100,6 +100,11 @@ int mkfhe_load_ksk_mklwe(mkfhe_ctx* ctx, const uint32_t* A_host_or_dev, uint64_t
 /* m_ctNAND of BinFHEContext (binfhecontext.h:88; built by ctGateGen, binfhe-base-scheme.cpp:340-376): [u < k][n]; MNTRU only */
 int mkfhe_load_ctnand(mkfhe_ctx* ctx, const uint32_t* ct_host_or_dev, uint64_t words);
 
+/* The decrypting parties' secret, only needed by mkfhe_decrypt: MNTRUPrivateKeyImpl::GetF_col0() (mntru-privatekey.h) or
+ * MKLWEPrivateKeyImpl::GetElement() (mklwe-privatekey.h), [u < k][n] residues (reduced mod q at upload, as Decrypt's
+ * SwitchModulus does for keys already stored mod q). */
+int mkfhe_load_sk(mkfhe_ctx* ctx, const uint32_t* sk_host_or_dev, uint64_t words);
+
 /* ---- the hot path ---- */
 
 /* UniEncAccumulator::EvalAcc for `batch` independent accumulators (mk-acc.h:67-71).
@@ -123,6 +128,12 @@ int mkfhe_eval_nand(mkfhe_ctx* ctx, const uint32_t* ct1, const uint32_t* b1, con
 /* same on device pointers, asynchronous on the context's stream */
 int mkfhe_eval_nand_dev(mkfhe_ctx* ctx, const uint32_t* d_ct1, const uint32_t* d_b1, const uint32_t* d_ct2,
                         const uint32_t* d_b2, uint32_t* d_out, uint32_t* d_bout, uint64_t batch);
+
+/* MNTRUEncryptionScheme::Decrypt (mntru-pke.cpp:306-341) / MKLWEEncryptionScheme::Decrypt (mklwe-pke.cpp:66-97) for `batch`
+ * ciphertexts: ct [batch][k][n] mod q, b [batch] (MKLWE; NULL for MNTRU), p = plaintext modulus (4 in both examples),
+ * m [batch] receives the plaintexts.  Host pointers, synchronous; _dev: device pointers, asynchronous. */
+int mkfhe_decrypt(mkfhe_ctx* ctx, const uint32_t* ct, const uint32_t* b, uint32_t p, uint32_t* m, uint64_t batch);
+int mkfhe_decrypt_dev(mkfhe_ctx* ctx, const uint32_t* d_ct, const uint32_t* d_b, uint32_t p, uint32_t* d_m, uint64_t batch);
 
 /* NativePoly::SetFormat on `batch` polynomials of N coefficients, in place (poly-impl.h:412-430 ->
  * transformnat-impl.h:299-354 forward, :491-552 inverse).  inverse = 0: COEFFICIENT -> EVALUATION. */

@@ -237,6 +237,31 @@ class BinFHEContext:
         g = lambda t: None if t is None else C.c_void_p(t.data_ptr())
         self._ck(self._L.mkfhe_eval_nand_dev(self._h, g(ct1), g(b1), g(ct2), g(b2), g(out), g(bout), B), "mkfhe_eval_nand_dev")
 
+    # -- BinFHEContext::Decrypt (binfhecontext.h:318-338 -> mntru-pke.cpp:306-341 / mklwe-pke.cpp:66-97), batched
+    def LoadSecretKey(self, sk):
+        """sk: uint32 [k, n] -- MNTRUPrivateKey::GetF_col0() or MKLWEPrivateKey::GetElement() of the decrypting parties"""
+        p, n = _ptr(sk)
+        self._ck(self._L.mkfhe_load_sk(self._h, p, n), "mkfhe_load_sk")
+
+    def Decrypt(self, ct, b=None, p: int = 4):
+        """ct: uint32 [B, k, n] (or [k, n]); b: uint32 [B] for MKNTRU_LWE.  Returns the plaintexts, uint32 [B]."""
+        P = self.params
+        c = np.ascontiguousarray(ct, dtype=np.uint32).reshape(-1, P.k, P.n)
+        B = c.shape[0]
+        m = np.empty(B, dtype=np.uint32)
+        bb = None
+        if self.is_lwe:
+            if b is None:
+                raise config_error("MKLWE ciphertexts carry b")
+            bb = np.ascontiguousarray(b, dtype=np.uint32).reshape(B)
+        self._ck(self._L.mkfhe_decrypt(self._h, _ptr(c)[0], _ptr(bb)[0], int(p), _ptr(m)[0], B), "mkfhe_decrypt")
+        return m
+
+    def DecryptDevice(self, ct, m, b=None, p: int = 4):
+        B = ct.numel() // (self.params.k * self.params.n)
+        g = lambda t: None if t is None else C.c_void_p(t.data_ptr())
+        self._ck(self._L.mkfhe_decrypt_dev(self._h, g(ct), g(b), int(p), g(m), B), "mkfhe_decrypt_dev")
+
     # -- UniEncAccumulator::EvalAcc (mk-acc.h:67-71), batched
     def EvalAcc(self, acc, rot, rot_mod: int):
         P = self.params

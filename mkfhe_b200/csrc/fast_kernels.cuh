@@ -387,16 +387,34 @@ __global__ void __launch_bounds__(FT, 4) blind_rotate_fast(const DevCtx P, const
 }
 
 // ---- standalone batched transform (config 5, mkfhe_ntt): one polynomial per CTA-iteration, persistent grid -----------
+// HBM-bound at large batch (16 KiB moved per 11 264 butterflies), so the next polynomial's coefficients are fetched into
+// registers before the current one is transformed: loads of iteration i+1 overlap the arithmetic of iteration i.
 __global__ void __launch_bounds__(FT, 4) ntt_batch_fast(const FastTables T, const uint32_t Q, const uint2 one2, uint32_t* polys,
                                                         const uint64_t batch, const int inverse) {
     __shared__ __align__(16) uint32_t E[FN];
     const uint32_t tid = threadIdx.x;
+    uint32_t nx[8];
+    auto fetch = [&](uint64_t b) {
+        const uint32_t* p = polys + b * FN;
+        if (!inverse) {
+#pragma unroll
+            for (int r = 0; r < 8; ++r) nx[r] = __ldcs(p + tid + 256 * r);
+        } else {
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                const uint4 v = __ldcs(reinterpret_cast<const uint4*>(p + 8 * tid + 4 * c));
+                nx[4 * c] = v.x; nx[4 * c + 1] = v.y; nx[4 * c + 2] = v.z; nx[4 * c + 3] = v.w;
+            }
+        }
+    };
+    if (blockIdx.x < batch) fetch(blockIdx.x);
     for (uint64_t b = blockIdx.x; b < batch; b += gridDim.x) {
         uint32_t* p = polys + b * FN;
         if (!inverse) {
             uint32_t x[1][8];
 #pragma unroll
-            for (int r = 0; r < 8; ++r) x[0][r] = p[tid + 256 * r];
+            for (int r = 0; r < 8; ++r) x[0][r] = nx[r];
+            if (b + gridDim.x < batch) fetch(b + gridDim.x);
             fwd_ntt_regs<1>(x, E, T, Q, tid);
 #pragma unroll
             for (int c = 0; c < 2; ++c) {
@@ -405,18 +423,16 @@ __global__ void __launch_bounds__(FT, 4) ntt_batch_fast(const FastTables T, cons
                 v.y = fold1(shoup_lazy(x[0][4 * c + 1], one2, Q), Q);
                 v.z = fold1(shoup_lazy(x[0][4 * c + 2], one2, Q), Q);
                 v.w = fold1(shoup_lazy(x[0][4 * c + 3], one2, Q), Q);
-                *reinterpret_cast<uint4*>(p + 8 * tid + 4 * c) = v;
+                __stcs(reinterpret_cast<uint4*>(p + 8 * tid + 4 * c), v);
             }
         } else {
             uint32_t x[8];
 #pragma unroll
-            for (int c = 0; c < 2; ++c) {
-                const uint4 v = *reinterpret_cast<const uint4*>(p + 8 * tid + 4 * c);
-                x[4 * c] = v.x; x[4 * c + 1] = v.y; x[4 * c + 2] = v.z; x[4 * c + 3] = v.w;
-            }
+            for (int r = 0; r < 8; ++r) x[r] = nx[r];
+            if (b + gridDim.x < batch) fetch(b + gridDim.x);
             inv_ntt_regs(x, E, T, Q, tid);
 #pragma unroll
-            for (int r = 0; r < 8; ++r) p[tid + 256 * r] = fold1(x[r], Q);
+            for (int r = 0; r < 8; ++r) __stcs(p + tid + 256 * r, fold1(x[r], Q));
         }
         __syncthreads();  // E is reused by the next polynomial
     }

@@ -531,6 +531,39 @@ __global__ void keyswitch_mklwe_finish(const DevCtx P, const uint32_t* raw, cons
     }
 }
 
+__global__ void reduce_mod(uint32_t* x, uint64_t words, uint32_t q) {
+    const uint64_t i = blockIdx.x * uint64_t(blockDim.x) + threadIdx.x;
+    if (i < words) x[i] %= q;
+}
+
+// ---- batched Decrypt: one warp per ciphertext (mntru-pke.cpp:306-341 MNTRU, mklwe-pke.cpp:66-97 MKLWE) ----
+// inner = sum_u <ct_u, sk_u> mod q.  MNTRU: m = p * (inner + q/p) / q ; MKLWE: m = p * (b - inner + q/(2p)) / q  (integer
+// division).  Products are accumulated exactly in 64 bits per lane (k*n/32 terms below 2^42 each) and reduced once, so the
+// result does not depend on the order of summation.
+__global__ void __launch_bounds__(256) decrypt_batch(const DevCtx P, const uint32_t* __restrict__ sk, const uint32_t* __restrict__ ct,
+                                                     const uint32_t* __restrict__ b, uint32_t pmod, uint32_t* __restrict__ out,
+                                                     uint64_t batch) {
+    const uint64_t g = (blockIdx.x * uint64_t(blockDim.x) + threadIdx.x) >> 5;
+    if (g >= batch) return;
+    const uint32_t lane = threadIdx.x & 31, kn = P.k * P.n, q = P.q;
+    const uint32_t* c = ct + g * kn;
+    unsigned long long acc = 0;
+    for (uint32_t x = lane; x < kn; x += 32) acc += static_cast<unsigned long long>(c[x]) * __ldg(sk + x);
+    uint32_t r = static_cast<uint32_t>(acc % q);
+#pragma unroll
+    for (int o = 16; o; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);  // 32 * q < 2^32 (q * 2N < 2^32)
+    if (lane == 0) {
+        uint32_t inner = r % q;
+        if (P.scheme == 0) {
+            inner = addmod(inner, q / pmod, q);
+        } else {
+            inner = submod(b[g] % q, inner, q);
+            inner = addmod(inner, q / (2 * pmod), q);
+        }
+        out[g] = static_cast<uint32_t>((static_cast<unsigned long long>(pmod) * inner) / q);
+    }
+}
+
 // ---- INT32 pipe micro-benchmark: 8 independent dependent-IMAD chains per thread ----
 __global__ void int32_peak_kernel(uint32_t* sink, uint32_t iters, uint32_t seed) {
     uint32_t a0 = seed + threadIdx.x, a1 = a0 ^ 0x9e3779b9u, a2 = a0 * 3u, a3 = a0 + 17u;

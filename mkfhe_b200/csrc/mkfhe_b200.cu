@@ -33,7 +33,7 @@ struct mkfhe_ctx {
     // tables
     uint32_t *tw{nullptr}, *twi{nullptr}, *psipow{nullptr};
     // keys
-    uint32_t *bk{nullptr}, *pkey{nullptr}, *ksk_mntru{nullptr}, *kskA{nullptr}, *kskB{nullptr}, *ctnand{nullptr};
+    uint32_t *bk{nullptr}, *pkey{nullptr}, *ksk_mntru{nullptr}, *kskA{nullptr}, *kskB{nullptr}, *ctnand{nullptr}, *sk{nullptr};
     uint16_t* ksk16{nullptr};  // fused key switch: u16 rows (generic_kernels.cuh, DevCtx::ksk16)
     bool fuse_ks{false};
     // workspaces (grown on demand)
@@ -271,7 +271,7 @@ void mkfhe_ctx_destroy(mkfhe_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->own_stream) cudaStreamSynchronize(ctx->own_stream);
     fast_destroy(ctx->fast);
-    for (uint32_t* p : {ctx->tw, ctx->twi, ctx->psipow, ctx->bk, ctx->pkey, ctx->ksk_mntru, ctx->kskA, ctx->kskB, ctx->ctnand,
+    for (uint32_t* p : {ctx->tw, ctx->twi, ctx->psipow, ctx->bk, ctx->pkey, ctx->ksk_mntru, ctx->kskA, ctx->kskB, ctx->ctnand, ctx->sk,
                         ctx->ws_ms, ctx->ws_raw, ctx->ws_io})
         if (p) cudaFree(p);
     if (ctx->ksk16) cudaFree(ctx->ksk16);
@@ -344,6 +344,54 @@ int mkfhe_load_ctnand(mkfhe_ctx* ctx, const uint32_t* ct, uint64_t words) {
     if (words != uint64_t(ctx->p.k) * ctx->p.n) return fail(ctx, MKFHE_EINVAL, "mkfhe_load_ctnand: wrong size");
     CU(cudaSetDevice(ctx->device));
     return upload(ctx, &ctx->ctnand, ct, words, false);
+}
+
+// the decryptor's secret (the party set that decrypts jointly): residues mod q
+int mkfhe_load_sk(mkfhe_ctx* ctx, const uint32_t* sk, uint64_t words) {
+    if (!ctx || !sk) return MKFHE_EINVAL;
+    if (words != uint64_t(ctx->p.k) * ctx->p.n) return fail(ctx, MKFHE_EINVAL, "mkfhe_load_sk: wrong size");
+    CU(cudaSetDevice(ctx->device));
+    int rc = upload(ctx, &ctx->sk, sk, words, false);
+    if (rc) return rc;
+    reduce_mod<<<unsigned((words + 255) / 256), 256, 0, ctx->stream>>>(ctx->sk, words, ctx->p.q);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(ctx->stream));
+    return MKFHE_OK;
+}
+
+int mkfhe_decrypt_dev(mkfhe_ctx* ctx, const uint32_t* d_ct, const uint32_t* d_b, uint32_t p, uint32_t* d_m, uint64_t batch) {
+    if (!ctx || !d_ct || !d_m) return MKFHE_EINVAL;
+    if (!ctx->sk) return fail(ctx, MKFHE_ENOKEY, "secret key not loaded (mkfhe_load_sk)");
+    if (ctx->p.scheme == MKFHE_SCHEME_MKLWE && !d_b) return fail(ctx, MKFHE_EINVAL, "MKLWE ciphertexts need b");
+    if (p < 2 || 2 * uint64_t(p) > ctx->p.q) return fail(ctx, MKFHE_EINVAL, "bad plaintext modulus");
+    if (batch == 0) return MKFHE_OK;
+    CU(cudaSetDevice(ctx->device));
+    const uint64_t blocks = (batch * 32 + 255) / 256;
+    if (blocks > 0x7fffffffull) return fail(ctx, MKFHE_EINVAL, "batch too large");
+    decrypt_batch<<<unsigned(blocks), 256, 0, ctx->stream>>>(ctx->d, ctx->sk, d_ct, d_b, p, d_m, batch);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    return MKFHE_OK;
+}
+
+int mkfhe_decrypt(mkfhe_ctx* ctx, const uint32_t* ct, const uint32_t* b, uint32_t p, uint32_t* m, uint64_t batch) {
+    if (!ctx || !ct || !m) return MKFHE_EINVAL;
+    const bool lwe = ctx->p.scheme == MKFHE_SCHEME_MKLWE;
+    if (lwe && !b) return fail(ctx, MKFHE_EINVAL, "MKLWE ciphertexts need b");
+    if (batch == 0) return MKFHE_OK;
+    CU(cudaSetDevice(ctx->device));
+    const size_t cw = size_t(batch) * ctx->p.k * ctx->p.n;
+    int rc = grow(ctx, &ctx->ws_io, &ctx->ws_io_words, cw + 2 * batch);
+    if (rc) return rc;
+    uint32_t *dc = ctx->ws_io, *db = dc + cw, *dm = db + batch;
+    CU(cudaMemcpyAsync(dc, ct, cw * 4, cudaMemcpyHostToDevice, ctx->stream));
+    if (lwe) CU(cudaMemcpyAsync(db, b, batch * 4, cudaMemcpyHostToDevice, ctx->stream));
+    rc = mkfhe_decrypt_dev(ctx, dc, lwe ? db : nullptr, p, dm, batch);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(m, dm, batch * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return MKFHE_OK;
 }
 
 // ---- launch helpers ----

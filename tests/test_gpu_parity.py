@@ -53,6 +53,32 @@ def test_eval_bin_gate_matches_reference(fx):
     assert bits == [int(b) for b in g["g_bits"]]
 
 
+def test_decrypt_matches_reference(fx):
+    """batched Decrypt: the reference's plaintexts of its own gate outputs (g_bits), the oracle on random ciphertexts
+    (every residue class of the rounding), and the error paths"""
+    import mkfhe_b200 as mk
+
+    g, ctx = fx
+    p = g["p"]
+    lwe = p.scheme == 1
+    with pytest.raises(mk.MkfheError):  # no secret key yet
+        ctx.Decrypt(g["g_out"].reshape(-1, p.k, p.n), g["g_bout"] if lwe else None)
+    ctx.LoadSecretKey(g["sk"])
+    got = ctx.Decrypt(g["g_out"].reshape(-1, p.k, p.n), g["g_bout"] if lwe else None)
+    assert (got == g["g_bits"]).all()
+    o = make_oracle(p)
+    rng = np.random.default_rng(9)
+    B = 257  # ragged against the 8-ciphertexts-per-block launch
+    ct = rng.integers(0, p.q, size=(B, p.k, p.n), dtype=np.uint32)
+    b = rng.integers(0, p.q, size=B, dtype=np.uint32)
+    want = np.array([o.decrypt(g["sk"], ct[i].ravel(), int(b[i])) for i in range(B)], dtype=np.uint32)
+    assert (ctx.Decrypt(ct, b if lwe else None) == want).all()
+    assert set(np.unique(want)) == {0, 1, 2, 3}
+    assert len(ctx.Decrypt(ct[:0], b[:0] if lwe else None)) == 0
+    with pytest.raises(mk.MkfheError):
+        ctx.Decrypt(ct[:1], b[:1] if lwe else None, p=1)
+
+
 def test_eval_acc_random_vs_oracle(fx):
     """fresh random accumulators / rotations (incl. ragged batch sizes) against the C oracle"""
     g, ctx = fx
