@@ -4,7 +4,7 @@
 // One CTA of 256 threads owns one gate.  A size-2048 transform is four register passes of 3 + 3 + 3 + 2 radix-2 stages
 // with 8 coefficients per thread; between passes the coefficients are transposed through shared memory: one exchange
 // crosses warps (block barrier), the other two stay inside a warp (warp w owns coefficients [256 w, 256 w + 256) on both
-// sides, so __syncwarp suffices).  A single XOR swizzle makes every exchange access bank-conflict free.  Butterflies are
+// sides, so __syncwarp suffices).  Padding (4 words per 32) makes every exchange access bank-conflict free.  Butterflies are
 // lazy: no value is reduced below 2^32 until the end, which Q < 2^32 / 32 allows (bounds next to each routine).
 // (A first version used 128 threads x 16 coefficients in three passes: 128 registers per thread, 4 warps per gate, a
 // 100 KB instruction footprint -- ncu showed 16% of stalls waiting for instructions and only 3.5 warps per scheduler;
@@ -51,12 +51,26 @@ __device__ __forceinline__ uint32_t shoup_lazy(uint32_t y, uint2 w, uint32_t Q) 
 // [0, 2Q) -> [0, Q)
 __device__ __forceinline__ uint32_t fold1(uint32_t x, uint32_t Q) { return min(x, x - Q); }
 
-// swizzled position of coefficient j (11 bits) in an exchange buffer: bits 2-4 ^= bits 5-7.  Bits 0-1 are untouched, so
-// 16-byte groups stay intact and 128-bit accesses stay legal.  Conflict-freedom of each access pattern:
-//   j = tid + 256 r, j = 256 w + 32 r + lane : bits 0-4 = lane, the XOR term is constant per instruction
-//   j = 32 (tid >> 2) + 4 r + (tid & 3)      : bits 0-1 and 5-7 vary with the lane -> bank bits (b0, b1, b2^b5, b3^b6, b4^b7)
-//   j = 8 tid + 4 c .. + 3 (128-bit)         : per quarter-warp bits 3-5 vary -> 16-byte bank groups (c^b5, b3^., b4^.) distinct
-__device__ __forceinline__ uint32_t swz(uint32_t j) { return j ^ (((j >> 5) & 7u) << 2); }
+// Position of coefficient j (11 bits) in an exchange buffer: 4 words of padding after every 32 (pad(j) = j + 4 (j >> 5)), so
+// a polynomial takes FNP = 2304 words.  Every access pattern of the transforms is then "per-thread base + compile-time
+// constant" (one LDS/STS with an immediate offset, no address arithmetic in the unrolled code), 16-byte groups stay
+// aligned, and each pattern is bank-conflict free:
+//   A  j = tid + 256 r          -> (tid + 4 (tid >> 5)) + 288 r      consecutive lanes, consecutive words
+//   B  j = 256 w + 32 r + lane  -> (288 w + lane) + 36 r             consecutive lanes, consecutive words
+//   C  j = 32 h + 4 r + l2      -> (36 h + l2) + 4 r                 h = tid >> 2, l2 = tid & 3: bank = 4 (h mod 8) + l2
+//   D  j = 8 tid + 4 c (128-bit)-> (8 tid + 4 h) + 4 c               a quarter warp covers 8 distinct 16-byte bank groups
+// (The first version XOR-swizzled bits 2-4 with bits 5-7: same conflict freedom in 2048 words, but patterns B, C and D
+// cost one LOP3 per access -- 64 per iteration of the step loop, 4% of its instructions; profiles/r1_s14_*.)
+constexpr uint32_t FNP = FN + FN / 8;
+struct ExIdx {
+    uint32_t a, b, c, d;
+    __device__ __forceinline__ explicit ExIdx(uint32_t tid)
+        : a(tid + 4 * (tid >> 5)), b(288 * (tid >> 5) + (tid & 31)), c(36 * (tid >> 2) + (tid & 3)), d(8 * tid + 4 * (tid >> 2)) {}
+    __device__ __forceinline__ uint32_t A(int r) const { return a + 288 * r; }
+    __device__ __forceinline__ uint32_t B(int r) const { return b + 36 * r; }
+    __device__ __forceinline__ uint32_t C(int r) const { return c + 4 * r; }
+    __device__ __forceinline__ uint32_t D(int ch) const { return d + 4 * ch; }
+};
 
 #define MKFHE_BFLY(X0, X1, W)                          \
     {                                                  \
@@ -68,12 +82,13 @@ __device__ __forceinline__ uint32_t swz(uint32_t j) { return j ^ (((j >> 5) & 7u
 // ---- forward negacyclic NTT, NP polynomials at once (shared twiddles), Cooley-Tukey, natural -> bit-reversed --------
 // in : x[p][r] = coefficient tid + 256 r          (values < 2Q)
 // out: x[p][i] = slot 8 tid + i (OpenFHE order)    (values < 24Q: +2Q per stage, 11 stages)
-// E: NP * 2048 words of shared memory.  Contains one __syncthreads (after the pass-1 writes); the caller guarantees that
+// E: NP * FNP words of shared memory.  Contains one __syncthreads (after the pass-1 writes); the caller guarantees that
 // every thread is done reading E from its previous use before any thread enters (a barrier lies in between).
 template <int NP>
 __device__ __forceinline__ void fwd_ntt_regs(uint32_t (&x)[NP][8], uint32_t* E, const FastTables& T, uint32_t Q, uint32_t tid) {
     const uint32_t twoQ = 2 * Q;
-    const uint32_t wrp = tid >> 5, lane = tid & 31, hi6 = tid >> 2, lo2 = tid & 3;
+    const uint32_t wrp = tid >> 5, hi6 = tid >> 2;
+    const ExIdx ex(tid);
     // pass 1: t = 1024, 512, 256  (m = 1, 2, 4 blocks; block of coefficient tid + 256 r at stage s is r >> (3 - s))
 #pragma unroll
     for (int s = 0; s < 3; ++s) {
@@ -89,12 +104,12 @@ __device__ __forceinline__ void fwd_ntt_regs(uint32_t (&x)[NP][8], uint32_t* E, 
 #pragma unroll
     for (int p = 0; p < NP; ++p)
 #pragma unroll
-        for (int r = 0; r < 8; ++r) E[p * FN + swz(tid + 256 * r)] = x[p][r];
+        for (int r = 0; r < 8; ++r) E[p * FNP + ex.A(r)] = x[p][r];
     __syncthreads();
 #pragma unroll
     for (int p = 0; p < NP; ++p)
 #pragma unroll
-        for (int r = 0; r < 8; ++r) x[p][r] = E[p * FN + swz(wrp * 256 + 32 * r + lane)];
+        for (int r = 0; r < 8; ++r) x[p][r] = E[p * FNP + ex.B(r)];
     // pass 2: t = 128, 64, 32  (m = 8, 16, 32; block = (warp << s) + (r >> (3 - s)): the same for all lanes of a warp)
 #pragma unroll
     for (int s = 0; s < 3; ++s) {
@@ -113,12 +128,12 @@ __device__ __forceinline__ void fwd_ntt_regs(uint32_t (&x)[NP][8], uint32_t* E, 
 #pragma unroll
     for (int p = 0; p < NP; ++p)
 #pragma unroll
-        for (int r = 0; r < 8; ++r) E[p * FN + swz(wrp * 256 + 32 * r + lane)] = x[p][r];
+        for (int r = 0; r < 8; ++r) E[p * FNP + ex.B(r)] = x[p][r];
     __syncwarp();
 #pragma unroll
     for (int p = 0; p < NP; ++p)
 #pragma unroll
-        for (int r = 0; r < 8; ++r) x[p][r] = E[p * FN + swz(hi6 * 32 + 4 * r + lo2)];
+        for (int r = 0; r < 8; ++r) x[p][r] = E[p * FNP + ex.C(r)];
     // pass 3: t = 16, 8, 4  (m = 64, 128, 256; block = (hi6 << s) + (r >> (3 - s)))
 #pragma unroll
     for (int s = 0; s < 3; ++s) {
@@ -136,13 +151,13 @@ __device__ __forceinline__ void fwd_ntt_regs(uint32_t (&x)[NP][8], uint32_t* E, 
 #pragma unroll
     for (int p = 0; p < NP; ++p)
 #pragma unroll
-        for (int r = 0; r < 8; ++r) E[p * FN + swz(hi6 * 32 + 4 * r + lo2)] = x[p][r];
+        for (int r = 0; r < 8; ++r) E[p * FNP + ex.C(r)] = x[p][r];
     __syncwarp();
 #pragma unroll
     for (int p = 0; p < NP; ++p)
 #pragma unroll
         for (int c = 0; c < 2; ++c) {
-            const uint4 v = *reinterpret_cast<const uint4*>(E + p * FN + swz(8 * tid + 4 * c));
+            const uint4 v = *reinterpret_cast<const uint4*>(E + p * FNP + ex.D(c));
             x[p][4 * c + 0] = v.x; x[p][4 * c + 1] = v.y; x[p][4 * c + 2] = v.z; x[p][4 * c + 3] = v.w;
         }
     // pass 4: t = 2, 1  (m = 512, 1024; block = (tid << (s + 1)) + (i >> (2 - s)))
@@ -167,10 +182,11 @@ __device__ __forceinline__ void fwd_ntt_regs(uint32_t (&x)[NP][8], uint32_t* E, 
 // in : x[i] = slot 8 tid + i, values < 6Q
 // out: x[r] = coefficient tid + 256 r, values in [0, 2Q)
 // bounds: first stage (twiddle 1, no multiplication) < 12Q, then +2Q per stage: < 32Q < 2^32.
-// E: 2048 words.  One __syncthreads inside (after the pass-3 writes); same entry condition as fwd_ntt_regs.
+// E: FNP words.  One __syncthreads inside (after the pass-3 writes); same entry condition as fwd_ntt_regs.
 __device__ __forceinline__ void inv_ntt_regs(uint32_t (&x)[8], uint32_t* E, const FastTables& T, uint32_t Q, uint32_t tid) {
     const uint32_t twoQ = 2 * Q, sixQ = 6 * Q;
-    const uint32_t wrp = tid >> 5, lane = tid & 31, hi6 = tid >> 2, lo2 = tid & 3;
+    const uint32_t lane = tid & 31, lo2 = tid & 3;
+    const ExIdx ex(tid);
     // pass 1: t = 1 (twiddle 1), t = 2
 #pragma unroll
     for (int i = 0; i < 8; i += 2) {
@@ -186,10 +202,10 @@ __device__ __forceinline__ void inv_ntt_regs(uint32_t (&x)[8], uint32_t* E, cons
     __syncwarp();
 #pragma unroll
     for (int c = 0; c < 2; ++c)
-        *reinterpret_cast<uint4*>(E + swz(8 * tid + 4 * c)) = make_uint4(x[4 * c], x[4 * c + 1], x[4 * c + 2], x[4 * c + 3]);
+        *reinterpret_cast<uint4*>(E + ex.D(c)) = make_uint4(x[4 * c], x[4 * c + 1], x[4 * c + 2], x[4 * c + 3]);
     __syncwarp();
 #pragma unroll
-    for (int r = 0; r < 8; ++r) x[r] = E[swz(hi6 * 32 + 4 * r + lo2)];
+    for (int r = 0; r < 8; ++r) x[r] = E[ex.C(r)];
     // pass 2: t = 4, 8, 16  (h = t / 4 in register units; m = 4 (r mod h) + lo2)
 #pragma unroll
     for (int s = 0; s < 3; ++s) {
@@ -204,10 +220,10 @@ __device__ __forceinline__ void inv_ntt_regs(uint32_t (&x)[8], uint32_t* E, cons
     }
     // same positions written as read: no hazard inside the warp beyond the one with the next reads
 #pragma unroll
-    for (int r = 0; r < 8; ++r) E[swz(hi6 * 32 + 4 * r + lo2)] = x[r];
+    for (int r = 0; r < 8; ++r) E[ex.C(r)] = x[r];
     __syncwarp();
 #pragma unroll
-    for (int r = 0; r < 8; ++r) x[r] = E[swz(wrp * 256 + 32 * r + lane)];
+    for (int r = 0; r < 8; ++r) x[r] = E[ex.B(r)];
     // pass 3: t = 32, 64, 128  (h = t / 32; m = 32 (r mod h) + lane)
 #pragma unroll
     for (int s = 0; s < 3; ++s) {
@@ -221,10 +237,10 @@ __device__ __forceinline__ void inv_ntt_regs(uint32_t (&x)[8], uint32_t* E, cons
         }
     }
 #pragma unroll
-    for (int r = 0; r < 8; ++r) E[swz(wrp * 256 + 32 * r + lane)] = x[r];
+    for (int r = 0; r < 8; ++r) E[ex.B(r)] = x[r];
     __syncthreads();
 #pragma unroll
-    for (int r = 0; r < 8; ++r) x[r] = E[swz(tid + 256 * r)];
+    for (int r = 0; r < 8; ++r) x[r] = E[ex.A(r)];
     // pass 4: t = 256, 512, 1024  (h = t / 256; m = 256 (r mod h) + tid)
 #pragma unroll
     for (int s = 0; s < 3; ++s) {
@@ -264,14 +280,22 @@ __device__ __forceinline__ uint32_t mac2(uint32_t a0, uint32_t k0, uint32_t a1, 
 }
 
 __device__ __forceinline__ uint4 ldg4(const uint32_t* p) { return __ldg(reinterpret_cast<const uint4*>(p)); }
+// 128-bit key load that does not allocate in L1: a key tile is used once per gate-step (it is served by L2), and letting it
+// through L1 evicts the 48 KiB of twiddle tables every transform reads (ncu: 33% L1 hit rate before, profiles/r1_s14_*)
+__device__ __forceinline__ uint4 ldg4_stream(const uint32_t* p) {
+    uint4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
 
 // 4 consecutive slots of one key polynomial as HbProd uses it in a step s > 0 (Montgomery form, canonical):
 //   XZW_B: ev1                       (mk-acc-xzw_B.cpp:306-309)
 //   XZW  : ev1 - ev2 * X^-c          (mk-acc-xzw.cpp:322-325: ev1 - ev2*(X^-c - 1) - ev2)
-__device__ __forceinline__ uint4 key4(const uint32_t* ev1, const uint32_t* ev2, const uint32_t (&xneg)[4], bool xzw, const Mod m) {
-    uint4 a = ldg4(ev1);
-    if (xzw) {
-        const uint4 b = ldg4(ev2);
+template <bool XZW>
+__device__ __forceinline__ uint4 key4(const uint32_t* ev1, const uint32_t* ev2, const uint32_t (&xneg)[4], const Mod m) {
+    uint4 a = ldg4_stream(ev1);
+    if (XZW) {
+        const uint4 b = ldg4_stream(ev2);
         a.x = submod(a.x, montmul(b.x, xneg[0], m), m.Q);
         a.y = submod(a.y, montmul(b.y, xneg[1], m), m.Q);
         a.z = submod(a.z, montmul(b.z, xneg[2], m), m.Q);
@@ -280,108 +304,176 @@ __device__ __forceinline__ uint4 key4(const uint32_t* ev1, const uint32_t* ev2, 
     return a;
 }
 
-// Shared memory of one gate: a[k][N] | E1[2][N] | E2[N] | X[N] | crot[k*n] (u16).
-// E1 / E2 / X double as D / V / X of the generic first step.
-__host__ __device__ inline size_t fast_smem_bytes(uint32_t k, uint32_t n) {
-    return (size_t(k) + 4) * FN * 4 + ((size_t(k) * n * 2 + 15) & ~size_t(15));
+// Shared memory of one gate: a[k][N] | E1[2][FNP] | E2[FNP] (absent when ALIAS) | crot[k*n] (u16).
+// ALIAS: the inverse transform exchanges through E1[0] instead of its own buffer (one more block barrier per iteration);
+// chosen by the host only when the separate buffer does not fit (see fast_use_alias).
+__host__ __device__ inline size_t fast_smem_bytes(uint32_t k, uint32_t n, bool alias) {
+    return (size_t(k) * FN + (alias ? 2 : 3) * FNP) * 4 + ((size_t(k) * n * 2 + 15) & ~size_t(15));
 }
 
-template <bool GATE>
-__global__ void __launch_bounds__(FT, 4) blind_rotate_fast(const DevCtx P, const FastTables T, const GateIO io) {
-    extern __shared__ __align__(16) uint32_t sm[];
-    const uint32_t Q = P.mod.Q, k = P.k, n = P.n, tid = threadIdx.x;
+// psi^e for the 4 slots 8 tid + 4 ch + q of X^x (x = c or -c mod 2N): slot j evaluates X at psi^(2 bitrev(j) + 1), and
+// bitrev(8 tid + i) = bitrev3(i) << 8 | bitrev8(tid), so the exponent is e0 + 512 * (x * bitrev3(i) mod 8) with
+// e0 = x * (2 bitrev8(tid) + 1).  Montgomery form (DevCtx::psipow).
+__device__ __forceinline__ void monomial4(const uint32_t* psipow, uint32_t e0, uint32_t x, int ch, uint32_t (&m)[4]) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const uint32_t b3 = __brev(uint32_t(4 * ch + q)) >> 29;
+        m[q] = __ldg(psipow + ((e0 + 512u * ((x * b3) & 7u)) & (2 * FN - 1)));
+    }
+}
+
+// One step s of EvalAcc (mk-acc-xzw.cpp:106-129, mk-acc-xzw_B.cpp:118-132) with rotation c, on the register-resident
+// transforms.  FIRST: the step (u, i) = (0, 0) -- AddToAccXZW0 (mk-acc-xzw.cpp:347-381, mk-acc-xzw_B.cpp:333-379): the KDM
+// key evs + ev1 (X^c - 1) [+ ev2 (X^-c - 1)] is assembled per slot, the accumulator itself is decomposed (no monomial) and
+// the result REPLACES it.  Runs once per gate, so it is a separate instantiation instead of selects in the hot loop.
+// Entry: a[] visible to all threads, nobody still reading E1 / E2.  Exit: as entry (ends with a block barrier).
+template <bool XZW, bool FIRST, bool ALIAS>
+__device__ __forceinline__ void fast_step(const DevCtx& P, const FastTables& T, uint32_t* a, uint32_t* E1, uint32_t* E2, uint32_t s,
+                                          uint32_t c, uint32_t tid) {
     constexpr uint32_t N = FN, M = 2 * FN;
-    uint32_t* a = sm;
-    uint32_t* E1 = a + k * N;
-    uint32_t* E2 = E1 + 2 * N;
-    uint32_t* Xs = E2 + N;
-    uint16_t* crot = reinterpret_cast<uint16_t*>(Xs + N);
-    const bool xzw = P.variant == 0;
-    const uint32_t g = P.gbits;
-
-    rotate_prologue<GATE>(P, io, blockIdx.x, a, crot);
-    // first step (AddToAccXZW0: KDM key assembled from evk*, acc replaced): once per gate, on the generic routine
-    hbprod_step_generic(P, a, E1, E2, Xs, 0, crot[0]);
-
+    const uint32_t Q = P.mod.Q, k = P.k, n = P.n, g = P.gbits;
+    const uint32_t u = FIRST ? 0u : s / n, i = FIRST ? 0u : s - u * n;
+    const uint32_t cneg = (M - c) & (M - 1);
     const size_t per = size_t(2) * 2 * N;  // words of one UniEncEvalKey: [j][d|f][N]
+    const uint32_t* ev1 = P.bk + (size_t(u * P.S) * n + i) * per + 8 * tid;
+    const uint32_t* ev2 = XZW ? ev1 + size_t(n) * per : ev1;
+    const uint32_t* evs = P.bk + size_t(k) * P.S * n * per + 8 * tid;  // evk* = ek[0][0][n] (mk-acc-xzw.cpp:51,72-74)
     const uint32_t brv8 = __brev(tid) >> 24;
-    for (uint32_t s = 1; s < k * n; ++s) {
-        const uint32_t c = crot[s];
-        if (c == 0) continue;  // X^0 - 1 = 0: the step leaves acc unchanged
-        const uint32_t u = s / n, i = s - u * n;
-        const uint32_t cneg = (M - c) & (M - 1);
-        const uint32_t* ev1 = P.bk + (size_t(u * P.S) * n + i) * per + 8 * tid;
-        const uint32_t* ev2 = xzw ? ev1 + size_t(n) * per : ev1;
-        const uint32_t e0 = cneg * (2 * brv8 + 1);  // exponent of psi for X^-c at this thread's first slot
-        uint32_t keep[8];                           // V while parties are processed, then X of the key owner
-        uint32_t y[8];
+    const uint32_t e0n = cneg * (2 * brv8 + 1), e0p = c * (2 * brv8 + 1);
+    uint32_t keep[8];  // V while parties are processed, then X of the key owner
+    uint32_t y[8];
 #pragma unroll 1
-        for (uint32_t it = 0; it <= k; ++it) {
-            uint32_t D[2][8];
-            uint32_t p = u;
-            if (it < k) {
-                p = (it + 1 < k) ? (it < u ? it : it + 1) : u;
-                const uint32_t* ap = a + p * N;
+    for (uint32_t it = 0; it <= k; ++it) {
+        uint32_t D[2][8];
+        uint32_t p = u;
+        if (it < k) {
+            p = (it + 1 < k) ? (it < u ? it : it + 1) : u;  // the key owner last: its f-term needs the complete V
+            const uint32_t* ap = a + p * N;
 #pragma unroll
-                for (int r = 0; r < 8; ++r) decompose2(rot_sub(ap, c, tid + 256 * r, N, Q), Q, g, D[0][r], D[1][r]);
-            } else {
+            for (int r = 0; r < 8; ++r)
+                decompose2(FIRST ? ap[tid + 256 * r] : rot_sub(ap, c, tid + 256 * r, N, Q), Q, g, D[0][r], D[1][r]);
+        } else {
 #pragma unroll
-                for (int r = 0; r < 8; ++r) decompose2(fold1(y[r], Q), Q, g, D[0][r], D[1][r]);
-            }
-            fwd_ntt_regs<2>(D, E1, T, Q, tid);
-            const int col = it < k ? 0 : 1;  // "d" column for the parties, "f" column for the sumV term
-            const uint32_t* pk = P.pkey + size_t(p) * 2 * N + 8 * tid;
+            for (int r = 0; r < 8; ++r) decompose2(fold1(y[r], Q), Q, g, D[0][r], D[1][r]);
+        }
+        fwd_ntt_regs<2>(D, E1, T, Q, tid);
+        const int col = it < k ? 0 : 1;  // "d" column for the parties, "f" column for the V term
+        const uint32_t* pk = P.pkey + size_t(p) * 2 * N + 8 * tid;
+        const uint32_t* k1p = ev1 + col * N;  // digit j at + 2 j N
+        const uint32_t* k2p = ev2 + col * N;
 #pragma unroll
-            for (int ch = 0; ch < 2; ++ch) {
-                uint32_t xn[4] = {0, 0, 0, 0};
-                if (xzw) {
+        for (int ch = 0; ch < 2; ++ch) {
+            uint32_t x4[4];  // <D, key> at slots 8 tid + 4 ch + q, < 3Q
+            if (FIRST) {
+                uint32_t mp[4], mn[4];
+                monomial4(P.psipow, e0p, c, ch, mp);
+                if (XZW) monomial4(P.psipow, e0n, cneg, ch, mn);
+                uint32_t kk[2][4];
+#pragma unroll
+                for (int j = 0; j < 2; ++j) {
+                    const uint4 es = ldg4_stream(evs + (2 * j + col) * N + 4 * ch), e1 = ldg4_stream(k1p + 2 * j * N + 4 * ch);
+                    const uint32_t esv[4] = {es.x, es.y, es.z, es.w}, e1v[4] = {e1.x, e1.y, e1.z, e1.w};
+                    uint32_t e2v[4] = {0, 0, 0, 0};
+                    if (XZW) {
+                        const uint4 e2 = ldg4_stream(k2p + 2 * j * N + 4 * ch);
+                        e2v[0] = e2.x; e2v[1] = e2.y; e2v[2] = e2.z; e2v[3] = e2.w;
+                    }
 #pragma unroll
                     for (int q = 0; q < 4; ++q) {
-                        const uint32_t b3 = __brev(uint32_t(4 * ch + q)) >> 29;  // slot 8 tid + i: bitrev = brv3(i) << 8 | brv8(tid)
-                        xn[q] = __ldg(P.psipow + ((e0 + 512u * ((cneg * b3) & 7u)) & (M - 1)));
+                        uint32_t r = addmod(esv[q], montmul(e1v[q], submod(mp[q], P.one_mont, Q), P.mod), Q);
+                        if (XZW) r = addmod(r, montmul(e2v[q], submod(mn[q], P.one_mont, Q), P.mod), Q);
+                        kk[j][q] = r;
                     }
                 }
-                const uint4 k0 = key4(ev1 + (0 * 2 + col) * N + 4 * ch, ev2 + (0 * 2 + col) * N + 4 * ch, xn, xzw, P.mod);
-                const uint4 k1 = key4(ev1 + (1 * 2 + col) * N + 4 * ch, ev2 + (1 * 2 + col) * N + 4 * ch, xn, xzw, P.mod);
-                const uint32_t kk0[4] = {k0.x, k0.y, k0.z, k0.w}, kk1[4] = {k1.x, k1.y, k1.z, k1.w};
-                uint32_t pp0[4] = {0, 0, 0, 0}, pp1[4] = {0, 0, 0, 0};
-                if (it < k) {
-                    const uint4 q0 = ldg4(pk + 4 * ch), q1 = ldg4(pk + N + 4 * ch);
-                    pp0[0] = q0.x; pp0[1] = q0.y; pp0[2] = q0.z; pp0[3] = q0.w;
-                    pp1[0] = q1.x; pp1[1] = q1.y; pp1[2] = q1.z; pp1[3] = q1.w;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) x4[q] = mac2(D[0][4 * ch + q], kk[0][q], D[1][4 * ch + q], kk[1][q], P.mod);
+            } else if (XZW) {
+                // sum_j D_j (ev1_j - ev2_j X^-c) = sum_j D_j ev1_j + (Q - X^-c) * redc(sum_j D_j ev2_j): two 64-bit sums,
+                // two reductions, five wide products per slot (mk-acc-xzw.cpp:322-325 assembles the key first: 2 more
+                // reductions and the conditional subtractions)
+                uint32_t mn[4];
+                monomial4(P.psipow, e0n, cneg, ch, mn);
+                const uint4 a0 = ldg4_stream(k1p + 4 * ch), a1 = ldg4_stream(k1p + 2 * N + 4 * ch);
+                const uint4 b0 = ldg4_stream(k2p + 4 * ch), b1 = ldg4_stream(k2p + 2 * N + 4 * ch);
+                const uint32_t a0v[4] = {a0.x, a0.y, a0.z, a0.w}, a1v[4] = {a1.x, a1.y, a1.z, a1.w};
+                const uint32_t b0v[4] = {b0.x, b0.y, b0.z, b0.w}, b1v[4] = {b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const uint32_t d0 = D[0][4 * ch + q], d1 = D[1][4 * ch + q];  // < 24Q
+                    const uint64_t s2 = static_cast<uint64_t>(d0) * b0v[q] + static_cast<uint64_t>(d1) * b1v[q];  // < 48 Q^2
+                    const uint32_t q2 = static_cast<uint32_t>(s2) * P.mod.qinv_neg;
+                    const uint32_t r2 = static_cast<uint32_t>((s2 + static_cast<uint64_t>(q2) * Q) >> 32);  // < 3Q
+                    const uint64_t s1 = static_cast<uint64_t>(d0) * a0v[q] + static_cast<uint64_t>(d1) * a1v[q] +
+                                        static_cast<uint64_t>(r2) * (Q - mn[q]);  // < 51 Q^2 < 2^60
+                    const uint32_t q1 = static_cast<uint32_t>(s1) * P.mod.qinv_neg;
+                    x4[q] = static_cast<uint32_t>((s1 + static_cast<uint64_t>(q1) * Q) >> 32);  // < 3Q
                 }
+            } else {
+                const uint4 a0 = ldg4_stream(k1p + 4 * ch), a1 = ldg4_stream(k1p + 2 * N + 4 * ch);
+                const uint32_t a0v[4] = {a0.x, a0.y, a0.z, a0.w}, a1v[4] = {a1.x, a1.y, a1.z, a1.w};
+#pragma unroll
+                for (int q = 0; q < 4; ++q) x4[q] = mac2(D[0][4 * ch + q], a0v[q], D[1][4 * ch + q], a1v[q], P.mod);
+            }
+            if (it < k) {
+                const uint4 q0 = ldg4(pk + 4 * ch), q1 = ldg4(pk + N + 4 * ch);
+                const uint32_t pp0[4] = {q0.x, q0.y, q0.z, q0.w}, pp1[4] = {q1.x, q1.y, q1.z, q1.w};
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
                     const int sl = 4 * ch + q;
-                    const uint32_t x = mac2(D[0][sl], kk0[q], D[1][sl], kk1[q], P.mod);  // < 3Q
-                    if (it < k) {
-                        const uint32_t v = mac2(D[0][sl], pp0[q], D[1][sl], pp1[q], P.mod);
-                        uint32_t vs = (it == 0 ? 0u : keep[sl]) + v;  // < 7Q
-                        vs = min(vs, vs - 4 * Q);                     // < 4Q
-                        if (it + 1 < k) {
-                            keep[sl] = vs;
-                            y[sl] = x;
-                        } else {  // owner: transform V next, hold X
-                            y[sl] = vs;
-                            keep[sl] = x;
-                        }
-                    } else {
-                        y[sl] = keep[sl] + x;  // < 6Q
+                    const uint32_t v = mac2(D[0][sl], pp0[q], D[1][sl], pp1[q], P.mod);
+                    uint32_t vs = (it == 0 ? 0u : keep[sl]) + v;  // < 7Q
+                    vs = min(vs, vs - 4 * Q);                     // < 4Q
+                    if (it + 1 < k) {
+                        keep[sl] = vs;
+                        y[sl] = x4[q];
+                    } else {  // owner: transform V next, hold X
+                        y[sl] = vs;
+                        keep[sl] = x4[q];
                     }
                 }
-            }
-            inv_ntt_regs(y, E2, T, Q, tid);
-            if (it + 1 != k) {  // a_p += result (the owner's V goes on to the next iteration in registers instead)
-                uint32_t* ap = a + p * N;
+            } else {
 #pragma unroll
-                for (int r = 0; r < 8; ++r) {
+                for (int q = 0; q < 4; ++q) y[4 * ch + q] = keep[4 * ch + q] + x4[q];  // < 6Q
+            }
+        }
+        inv_ntt_regs(y, ALIAS ? E1 : E2, T, Q, tid);
+        if (it + 1 != k) {  // a_p (+)= result (the owner's V goes on to the next iteration in registers instead)
+            uint32_t* ap = a + p * N;
+#pragma unroll
+            for (int r = 0; r < 8; ++r) {
+                if (FIRST) {
+                    ap[tid + 256 * r] = fold1(y[r], Q);
+                } else {
                     uint32_t v = ap[tid + 256 * r] + y[r];  // < 3Q
                     v = min(v, v - 2 * Q);
                     ap[tid + 256 * r] = min(v, v - Q);
                 }
             }
         }
-        __syncthreads();  // a[] complete before the next step's shifted reads
+        // ALIAS: everybody is done reading the inverse's last exchange before the next forward transform writes E1.
+        // (a_p itself needs no barrier here: it was read -- at shifted positions, by other threads -- before the two
+        // barriers inside this iteration's transforms, and is read again only after the barrier that ends the step.)
+        if (ALIAS) __syncthreads();
+    }
+    __syncthreads();  // a[] complete before the next step's shifted reads
+}
+
+template <bool GATE, bool XZW, bool ALIAS>
+__global__ void __launch_bounds__(FT, 4) blind_rotate_fast(const DevCtx P, const FastTables T, const GateIO io) {
+    extern __shared__ __align__(16) uint32_t sm[];
+    const uint32_t k = P.k, n = P.n, tid = threadIdx.x;
+    constexpr uint32_t N = FN;
+    uint32_t* a = sm;
+    uint32_t* E1 = a + k * N;
+    uint32_t* E2 = E1 + 2 * FNP;
+    uint16_t* crot = reinterpret_cast<uint16_t*>(ALIAS ? E2 : E2 + FNP);
+
+    rotate_prologue<GATE>(P, io, blockIdx.x, a, crot);
+    fast_step<XZW, true, ALIAS>(P, T, a, E1, E2, 0, crot[0], tid);
+    for (uint32_t s = 1; s < k * n; ++s) {
+        const uint32_t c = crot[s];
+        if (c == 0) continue;  // X^0 - 1 = 0: the step leaves acc unchanged
+        fast_step<XZW, false, ALIAS>(P, T, a, E1, E2, s, c, tid);
     }
     rotate_epilogue<GATE>(P, io, blockIdx.x, a, E1);
 }
@@ -391,7 +483,7 @@ __global__ void __launch_bounds__(FT, 4) blind_rotate_fast(const DevCtx P, const
 // registers before the current one is transformed: loads of iteration i+1 overlap the arithmetic of iteration i.
 __global__ void __launch_bounds__(FT, 4) ntt_batch_fast(const FastTables T, const uint32_t Q, const uint2 one2, uint32_t* polys,
                                                         const uint64_t batch, const int inverse) {
-    __shared__ __align__(16) uint32_t E[FN];
+    __shared__ __align__(16) uint32_t E[FNP];
     const uint32_t tid = threadIdx.x;
     uint32_t nx[8];
     auto fetch = [&](uint64_t b) {
@@ -448,7 +540,7 @@ struct FastState {
 
 inline bool fast_supported(const DevCtx& d) {
     return d.N == FN && d.ell == 2 && d.mod.Q < (1u << 27) && d.gbits >= 2 && d.gbits <= 16 &&
-           fast_smem_bytes(d.k, d.n) <= 227 * 1024;
+           fast_smem_bytes(d.k, d.n, true) <= 227 * 1024;
 }
 
 inline cudaError_t fast_init(FastState& F, const DevCtx& d, uint32_t psi, cudaStream_t st, uint64_t* dev_bytes) {
@@ -509,17 +601,38 @@ inline void fast_destroy(FastState& F) {
 inline cudaError_t fast_load_bk(FastState&, const DevCtx&, cudaStream_t, uint64_t*, uint64_t*) { return cudaSuccess; }
 inline cudaError_t fast_load_pkey(FastState&, const DevCtx&, cudaStream_t, uint64_t*, uint64_t*) { return cudaSuccess; }
 
+// gates resident per SM: 64 registers x 256 threads allow 4; shared memory (1 KiB reserved per CTA) may allow fewer
+inline int fast_gates_per_sm(size_t smem) { return int(std::min<size_t>(4, (227 * 1024) / (smem + 1024))); }
+// Measured on B200 (k = 4, STD100_MKNTRU_2): 4 gates per SM with ALIAS run at 3783 gates/s, 3 gates per SM without at
+// 4246 gates/s -- the extra block barrier per iteration costs more than the fourth resident gate brings.  So ALIAS is only
+// the fallback for party counts whose separate buffer does not fit shared memory at all.
+inline bool fast_use_alias(const DevCtx& d) {
+    if (const char* e = getenv("MKFHE_FAST_ALIAS")) return e[0] == '1';
+    return fast_smem_bytes(d.k, d.n, false) > 227 * 1024;
+}
+
 inline cudaError_t fast_blind_rotate(FastState& F, const DevCtx& d, bool gate, const GateIO& io, uint32_t batch, cudaStream_t st,
                                      uint64_t* launches) {
-    const size_t smem = fast_smem_bytes(d.k, d.n);
+    const bool alias = fast_use_alias(d), xzw = d.variant == 0;
+    const size_t smem = fast_smem_bytes(d.k, d.n, alias);
+    auto launch = [&](auto kern) -> cudaError_t {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+        if (e != cudaSuccess) return e;
+        kern<<<batch, FT, smem, st>>>(d, F.T, io);
+        return cudaSuccess;
+    };
     cudaError_t e;
-    if (gate) {
-        if ((e = cudaFuncSetAttribute(blind_rotate_fast<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem))) != cudaSuccess) return e;
-        blind_rotate_fast<true><<<batch, FT, smem, st>>>(d, F.T, io);
-    } else {
-        if ((e = cudaFuncSetAttribute(blind_rotate_fast<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem))) != cudaSuccess) return e;
-        blind_rotate_fast<false><<<batch, FT, smem, st>>>(d, F.T, io);
+    switch ((gate ? 4 : 0) | (xzw ? 2 : 0) | (alias ? 1 : 0)) {
+        case 0: e = launch(blind_rotate_fast<false, false, false>); break;
+        case 1: e = launch(blind_rotate_fast<false, false, true>); break;
+        case 2: e = launch(blind_rotate_fast<false, true, false>); break;
+        case 3: e = launch(blind_rotate_fast<false, true, true>); break;
+        case 4: e = launch(blind_rotate_fast<true, false, false>); break;
+        case 5: e = launch(blind_rotate_fast<true, false, true>); break;
+        case 6: e = launch(blind_rotate_fast<true, true, false>); break;
+        default: e = launch(blind_rotate_fast<true, true, true>); break;
     }
+    if (e != cudaSuccess) return e;
     ++*launches;
     return cudaGetLastError();
 }
