@@ -25,6 +25,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <cstdlib>
 #include <vector>
 
 #include "generic_kernels.cuh"
@@ -72,6 +73,14 @@ struct ExIdx {
     __device__ __forceinline__ uint32_t D(int ch) const { return d + 4 * ch; }
 };
 
+// barrier over the threads that share one gate's transform: the whole CTA (bar = 0), or one 256-thread group of a
+// party-parallel CTA (named barrier bar = 1 + group)
+template <bool GRP>
+__device__ __forceinline__ void gate_sync(uint32_t bar) {
+    if (GRP) asm volatile("bar.sync %0, 256;" ::"r"(bar) : "memory");
+    else __syncthreads();
+}
+
 #define MKFHE_BFLY(X0, X1, W)                          \
     {                                                  \
         const uint32_t t_ = shoup_lazy(X1, W, Q), u_ = X0; \
@@ -84,8 +93,9 @@ struct ExIdx {
 // out: x[p][i] = slot 8 tid + i (OpenFHE order)    (values < 24Q: +2Q per stage, 11 stages)
 // E: NP * FNP words of shared memory.  Contains one __syncthreads (after the pass-1 writes); the caller guarantees that
 // every thread is done reading E from its previous use before any thread enters (a barrier lies in between).
-template <int NP>
-__device__ __forceinline__ void fwd_ntt_regs(uint32_t (&x)[NP][8], uint32_t* E, const FastTables& T, uint32_t Q, uint32_t tid) {
+template <int NP, bool GRP = false>
+__device__ __forceinline__ void fwd_ntt_regs(uint32_t (&x)[NP][8], uint32_t* E, const FastTables& T, uint32_t Q, uint32_t tid,
+                                             uint32_t bar = 0) {
     const uint32_t twoQ = 2 * Q;
     const uint32_t wrp = tid >> 5, hi6 = tid >> 2;
     const ExIdx ex(tid);
@@ -105,7 +115,7 @@ __device__ __forceinline__ void fwd_ntt_regs(uint32_t (&x)[NP][8], uint32_t* E, 
     for (int p = 0; p < NP; ++p)
 #pragma unroll
         for (int r = 0; r < 8; ++r) E[p * FNP + ex.A(r)] = x[p][r];
-    __syncthreads();
+    gate_sync<GRP>(bar);
 #pragma unroll
     for (int p = 0; p < NP; ++p)
 #pragma unroll
@@ -183,7 +193,9 @@ __device__ __forceinline__ void fwd_ntt_regs(uint32_t (&x)[NP][8], uint32_t* E, 
 // out: x[r] = coefficient tid + 256 r, values in [0, 2Q)
 // bounds: first stage (twiddle 1, no multiplication) < 12Q, then +2Q per stage: < 32Q < 2^32.
 // E: FNP words.  One __syncthreads inside (after the pass-3 writes); same entry condition as fwd_ntt_regs.
-__device__ __forceinline__ void inv_ntt_regs(uint32_t (&x)[8], uint32_t* E, const FastTables& T, uint32_t Q, uint32_t tid) {
+template <bool GRP = false>
+__device__ __forceinline__ void inv_ntt_regs(uint32_t (&x)[8], uint32_t* E, const FastTables& T, uint32_t Q, uint32_t tid,
+                                             uint32_t bar = 0) {
     const uint32_t twoQ = 2 * Q, sixQ = 6 * Q;
     const uint32_t lane = tid & 31, lo2 = tid & 3;
     const ExIdx ex(tid);
@@ -238,7 +250,7 @@ __device__ __forceinline__ void inv_ntt_regs(uint32_t (&x)[8], uint32_t* E, cons
     }
 #pragma unroll
     for (int r = 0; r < 8; ++r) E[ex.B(r)] = x[r];
-    __syncthreads();
+    gate_sync<GRP>(bar);
 #pragma unroll
     for (int r = 0; r < 8; ++r) x[r] = E[ex.A(r)];
     // pass 4: t = 256, 512, 1024  (h = t / 256; m = 256 (r mod h) + tid)
@@ -322,6 +334,66 @@ __device__ __forceinline__ void monomial4(const uint32_t* psipow, uint32_t e0, u
     }
 }
 
+// <D, key> at the 4 slots 8 tid + 4 ch + q of one key column (k1p / k2p / evsp point at digit 0 of that column of ev1 /
+// ev2 / evk*, digit j at + 2 j N), result < 3Q.  D_j < 24Q (lazy transform output); keys canonical, Montgomery form.
+template <bool XZW, bool FIRST>
+__device__ __forceinline__ void key_mac4(const DevCtx& P, const uint32_t* k1p, const uint32_t* k2p, const uint32_t* evsp, uint32_t c,
+                                         uint32_t cneg, uint32_t e0p, uint32_t e0n, int ch, const uint32_t (&D)[2][8],
+                                         uint32_t (&x4)[4]) {
+    constexpr uint32_t N = FN;
+    const uint32_t Q = P.mod.Q;
+    if (FIRST) {
+        uint32_t mp[4], mn[4];
+        monomial4(P.psipow, e0p, c, ch, mp);
+        if (XZW) monomial4(P.psipow, e0n, cneg, ch, mn);
+        uint32_t kk[2][4];
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+            const uint4 es = ldg4_stream(evsp + 2 * j * N + 4 * ch), e1 = ldg4_stream(k1p + 2 * j * N + 4 * ch);
+            const uint32_t esv[4] = {es.x, es.y, es.z, es.w}, e1v[4] = {e1.x, e1.y, e1.z, e1.w};
+            uint32_t e2v[4] = {0, 0, 0, 0};
+            if (XZW) {
+                const uint4 e2 = ldg4_stream(k2p + 2 * j * N + 4 * ch);
+                e2v[0] = e2.x; e2v[1] = e2.y; e2v[2] = e2.z; e2v[3] = e2.w;
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                uint32_t r = addmod(esv[q], montmul(e1v[q], submod(mp[q], P.one_mont, Q), P.mod), Q);
+                if (XZW) r = addmod(r, montmul(e2v[q], submod(mn[q], P.one_mont, Q), P.mod), Q);
+                kk[j][q] = r;
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) x4[q] = mac2(D[0][4 * ch + q], kk[0][q], D[1][4 * ch + q], kk[1][q], P.mod);
+    } else if (XZW) {
+        // sum_j D_j (ev1_j - ev2_j X^-c) = sum_j D_j ev1_j + (Q - X^-c) * redc(sum_j D_j ev2_j): two 64-bit sums,
+        // two reductions, five wide products per slot (mk-acc-xzw.cpp:322-325 assembles the key first: 2 more
+        // reductions and the conditional subtractions)
+        uint32_t mn[4];
+        monomial4(P.psipow, e0n, cneg, ch, mn);
+        const uint4 a0 = ldg4_stream(k1p + 4 * ch), a1 = ldg4_stream(k1p + 2 * N + 4 * ch);
+        const uint4 b0 = ldg4_stream(k2p + 4 * ch), b1 = ldg4_stream(k2p + 2 * N + 4 * ch);
+        const uint32_t a0v[4] = {a0.x, a0.y, a0.z, a0.w}, a1v[4] = {a1.x, a1.y, a1.z, a1.w};
+        const uint32_t b0v[4] = {b0.x, b0.y, b0.z, b0.w}, b1v[4] = {b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const uint32_t d0 = D[0][4 * ch + q], d1 = D[1][4 * ch + q];  // < 24Q
+            const uint64_t s2 = static_cast<uint64_t>(d0) * b0v[q] + static_cast<uint64_t>(d1) * b1v[q];  // < 48 Q^2
+            const uint32_t q2 = static_cast<uint32_t>(s2) * P.mod.qinv_neg;
+            const uint32_t r2 = static_cast<uint32_t>((s2 + static_cast<uint64_t>(q2) * Q) >> 32);  // < 3Q
+            const uint64_t s1 = static_cast<uint64_t>(d0) * a0v[q] + static_cast<uint64_t>(d1) * a1v[q] +
+                                static_cast<uint64_t>(r2) * (Q - mn[q]);  // < 51 Q^2 < 2^60
+            const uint32_t q1 = static_cast<uint32_t>(s1) * P.mod.qinv_neg;
+            x4[q] = static_cast<uint32_t>((s1 + static_cast<uint64_t>(q1) * Q) >> 32);  // < 3Q
+        }
+    } else {
+        const uint4 a0 = ldg4_stream(k1p + 4 * ch), a1 = ldg4_stream(k1p + 2 * N + 4 * ch);
+        const uint32_t a0v[4] = {a0.x, a0.y, a0.z, a0.w}, a1v[4] = {a1.x, a1.y, a1.z, a1.w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) x4[q] = mac2(D[0][4 * ch + q], a0v[q], D[1][4 * ch + q], a1v[q], P.mod);
+    }
+}
+
 // One step s of EvalAcc (mk-acc-xzw.cpp:106-129, mk-acc-xzw_B.cpp:118-132) with rotation c, on the register-resident
 // transforms.  FIRST: the step (u, i) = (0, 0) -- AddToAccXZW0 (mk-acc-xzw.cpp:347-381, mk-acc-xzw_B.cpp:333-379): the KDM
 // key evs + ev1 (X^c - 1) [+ ev2 (X^-c - 1)] is assembled per slot, the accumulator itself is decomposed (no monomial) and
@@ -364,56 +436,7 @@ __device__ __forceinline__ void fast_step(const DevCtx& P, const FastTables& T, 
 #pragma unroll
         for (int ch = 0; ch < 2; ++ch) {
             uint32_t x4[4];  // <D, key> at slots 8 tid + 4 ch + q, < 3Q
-            if (FIRST) {
-                uint32_t mp[4], mn[4];
-                monomial4(P.psipow, e0p, c, ch, mp);
-                if (XZW) monomial4(P.psipow, e0n, cneg, ch, mn);
-                uint32_t kk[2][4];
-#pragma unroll
-                for (int j = 0; j < 2; ++j) {
-                    const uint4 es = ldg4_stream(evs + (2 * j + col) * N + 4 * ch), e1 = ldg4_stream(k1p + 2 * j * N + 4 * ch);
-                    const uint32_t esv[4] = {es.x, es.y, es.z, es.w}, e1v[4] = {e1.x, e1.y, e1.z, e1.w};
-                    uint32_t e2v[4] = {0, 0, 0, 0};
-                    if (XZW) {
-                        const uint4 e2 = ldg4_stream(k2p + 2 * j * N + 4 * ch);
-                        e2v[0] = e2.x; e2v[1] = e2.y; e2v[2] = e2.z; e2v[3] = e2.w;
-                    }
-#pragma unroll
-                    for (int q = 0; q < 4; ++q) {
-                        uint32_t r = addmod(esv[q], montmul(e1v[q], submod(mp[q], P.one_mont, Q), P.mod), Q);
-                        if (XZW) r = addmod(r, montmul(e2v[q], submod(mn[q], P.one_mont, Q), P.mod), Q);
-                        kk[j][q] = r;
-                    }
-                }
-#pragma unroll
-                for (int q = 0; q < 4; ++q) x4[q] = mac2(D[0][4 * ch + q], kk[0][q], D[1][4 * ch + q], kk[1][q], P.mod);
-            } else if (XZW) {
-                // sum_j D_j (ev1_j - ev2_j X^-c) = sum_j D_j ev1_j + (Q - X^-c) * redc(sum_j D_j ev2_j): two 64-bit sums,
-                // two reductions, five wide products per slot (mk-acc-xzw.cpp:322-325 assembles the key first: 2 more
-                // reductions and the conditional subtractions)
-                uint32_t mn[4];
-                monomial4(P.psipow, e0n, cneg, ch, mn);
-                const uint4 a0 = ldg4_stream(k1p + 4 * ch), a1 = ldg4_stream(k1p + 2 * N + 4 * ch);
-                const uint4 b0 = ldg4_stream(k2p + 4 * ch), b1 = ldg4_stream(k2p + 2 * N + 4 * ch);
-                const uint32_t a0v[4] = {a0.x, a0.y, a0.z, a0.w}, a1v[4] = {a1.x, a1.y, a1.z, a1.w};
-                const uint32_t b0v[4] = {b0.x, b0.y, b0.z, b0.w}, b1v[4] = {b1.x, b1.y, b1.z, b1.w};
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                    const uint32_t d0 = D[0][4 * ch + q], d1 = D[1][4 * ch + q];  // < 24Q
-                    const uint64_t s2 = static_cast<uint64_t>(d0) * b0v[q] + static_cast<uint64_t>(d1) * b1v[q];  // < 48 Q^2
-                    const uint32_t q2 = static_cast<uint32_t>(s2) * P.mod.qinv_neg;
-                    const uint32_t r2 = static_cast<uint32_t>((s2 + static_cast<uint64_t>(q2) * Q) >> 32);  // < 3Q
-                    const uint64_t s1 = static_cast<uint64_t>(d0) * a0v[q] + static_cast<uint64_t>(d1) * a1v[q] +
-                                        static_cast<uint64_t>(r2) * (Q - mn[q]);  // < 51 Q^2 < 2^60
-                    const uint32_t q1 = static_cast<uint32_t>(s1) * P.mod.qinv_neg;
-                    x4[q] = static_cast<uint32_t>((s1 + static_cast<uint64_t>(q1) * Q) >> 32);  // < 3Q
-                }
-            } else {
-                const uint4 a0 = ldg4_stream(k1p + 4 * ch), a1 = ldg4_stream(k1p + 2 * N + 4 * ch);
-                const uint32_t a0v[4] = {a0.x, a0.y, a0.z, a0.w}, a1v[4] = {a1.x, a1.y, a1.z, a1.w};
-#pragma unroll
-                for (int q = 0; q < 4; ++q) x4[q] = mac2(D[0][4 * ch + q], a0v[q], D[1][4 * ch + q], a1v[q], P.mod);
-            }
+            key_mac4<XZW, FIRST>(P, k1p, k2p, evs + col * N, c, cneg, e0p, e0n, ch, D, x4);
             if (it < k) {
                 const uint4 q0 = ldg4(pk + 4 * ch), q1 = ldg4(pk + N + 4 * ch);
                 const uint32_t pp0[4] = {q0.x, q0.y, q0.z, q0.w}, pp1[4] = {q1.x, q1.y, q1.z, q1.w};
@@ -476,6 +499,132 @@ __global__ void __launch_bounds__(FT, 4) blind_rotate_fast(const DevCtx P, const
         fast_step<XZW, false, ALIAS>(P, T, a, E1, E2, s, c, tid);
     }
     rotate_epilogue<GATE>(P, io, blockIdx.x, a, E1);
+}
+
+// ---- party-parallel variant for large party counts ----------------------------------------------------------------------
+// At k >= 8 one gate's accumulator takes 64-128 KiB of shared memory, so only 2 (k = 8) or 1 (k = 16) gates fit an SM and a
+// 256-thread CTA per gate leaves the SM with 16 or 8 warps.  Here one CTA of G x 256 threads owns one gate and the G groups
+// process different parties of the same step concurrently: the parties' terms of HbProd (mk-acc-xzw.cpp:240-271) are
+// independent except for sumV, which the groups accumulate in shared memory with atomic adds (sums of canonical residues:
+// k Q < 2^32).  Then one group runs the sumV term (:273-289) while the others wait: a step takes ceil(k / G) + 1 transform
+// rounds instead of k + 1.  Group barriers are named barriers (1 + group); block barriers separate the phases.
+// Shared memory: a[k][N] | per group E1[2][FNP] | E2[FNP] (absent when ALIAS) | Vs[N] | crot[k*n] (u16).
+__host__ __device__ inline size_t grouped_smem_bytes(uint32_t k, uint32_t n, uint32_t G, bool alias) {
+    return (size_t(k) * FN + size_t(G) * (alias ? 2 : 3) * FNP + FN) * 4 + ((size_t(k) * n * 2 + 15) & ~size_t(15));
+}
+
+template <bool XZW, bool FIRST, bool ALIAS>
+__device__ __forceinline__ void grouped_step(const DevCtx& P, const FastTables& T, uint32_t* a, uint32_t* E1, uint32_t* E2, uint32_t* Vs,
+                                             uint32_t s, uint32_t c, uint32_t tid, uint32_t grp, uint32_t G) {
+    constexpr uint32_t N = FN, M = 2 * FN;
+    const uint32_t Q = P.mod.Q, k = P.k, n = P.n, g = P.gbits, bar = 1 + grp;
+    const uint32_t u = FIRST ? 0u : s / n, i = FIRST ? 0u : s - u * n;
+    const uint32_t cneg = (M - c) & (M - 1);
+    const size_t per = size_t(2) * 2 * N;
+    const uint32_t* ev1 = P.bk + (size_t(u * P.S) * n + i) * per + 8 * tid;
+    const uint32_t* ev2 = XZW ? ev1 + size_t(n) * per : ev1;
+    const uint32_t* evs = P.bk + size_t(k) * P.S * n * per + 8 * tid;
+    const uint32_t brv8 = __brev(tid) >> 24;
+    const uint32_t e0n = cneg * (2 * brv8 + 1), e0p = c * (2 * brv8 + 1);
+    uint32_t y[8];
+    // ---- phase 1: the parties, round-robin over the groups (order index k - 1 = the key owner).  The owner's <D_u, d> is
+    // transformed back and added to a_u like everybody else's (one more inverse transform per step than the sequential
+    // schedule, which adds it to <g^-1(sumV), f> in the evaluation domain: same sum, and no registers held across phases) ----
+#pragma unroll 1
+    for (uint32_t it = grp; it < k; it += G) {
+        uint32_t D[2][8];
+        const uint32_t p = (it + 1 < k) ? (it < u ? it : it + 1) : u;
+        uint32_t* ap = a + p * N;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) decompose2(FIRST ? ap[tid + 256 * r] : rot_sub(ap, c, tid + 256 * r, N, Q), Q, g, D[0][r], D[1][r]);
+        fwd_ntt_regs<2, true>(D, E1, T, Q, tid, bar);
+        const uint32_t* pk = P.pkey + size_t(p) * 2 * N + 8 * tid;
+#pragma unroll
+        for (int ch = 0; ch < 2; ++ch) {
+            uint32_t x4[4];
+            key_mac4<XZW, FIRST>(P, ev1, ev2, evs, c, cneg, e0p, e0n, ch, D, x4);
+            const uint4 q0 = ldg4(pk + 4 * ch), q1 = ldg4(pk + N + 4 * ch);
+            const uint32_t pp0[4] = {q0.x, q0.y, q0.z, q0.w}, pp1[4] = {q1.x, q1.y, q1.z, q1.w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int sl = 4 * ch + q;
+                uint32_t v = mac2(D[0][sl], pp0[q], D[1][sl], pp1[q], P.mod);  // < 3Q
+                v = min(v, v - 2 * Q);
+                atomicAdd(Vs + 256 * sl + tid, min(v, v - Q));  // canonical: the sum over k <= 16 parties stays below 2^31
+                y[sl] = x4[q];
+            }
+        }
+        {
+            inv_ntt_regs<true>(y, ALIAS ? E1 : E2, T, Q, tid, bar);
+#pragma unroll
+            for (int r = 0; r < 8; ++r) {
+                if (FIRST) {
+                    ap[tid + 256 * r] = fold1(y[r], Q);
+                } else {
+                    uint32_t v = ap[tid + 256 * r] + y[r];  // < 3Q
+                    v = min(v, v - 2 * Q);
+                    ap[tid + 256 * r] = min(v, v - Q);
+                }
+            }
+            if (ALIAS) gate_sync<true>(bar);
+        }
+    }
+    __syncthreads();  // sumV complete in Vs
+    // ---- phase 2: the sumV term <g^-1(sumV), f>, added to a_u by the group that processed the owner ----
+    if (grp == (k - 1) % G) {
+        uint32_t D[2][8];
+#pragma unroll
+        for (int sl = 0; sl < 8; ++sl) {  // Vs[256 sl + tid] = slot 8 tid + sl: conflict-free for the atomics and here
+            uint32_t v = Vs[256 * sl + tid];  // < 16Q
+            Vs[256 * sl + tid] = 0;           // ready for the next step
+            v = min(v, v - 8 * Q);
+            y[sl] = min(v, v - 4 * Q);        // < 4Q
+        }
+        inv_ntt_regs<true>(y, ALIAS ? E1 : E2, T, Q, tid, bar);
+        if (ALIAS) gate_sync<true>(bar);
+#pragma unroll
+        for (int r = 0; r < 8; ++r) decompose2(fold1(y[r], Q), Q, g, D[0][r], D[1][r]);
+        fwd_ntt_regs<2, true>(D, E1, T, Q, tid, bar);
+#pragma unroll
+        for (int ch = 0; ch < 2; ++ch) {
+            uint32_t x4[4];
+            key_mac4<XZW, FIRST>(P, ev1 + N, ev2 + N, evs + N, c, cneg, e0p, e0n, ch, D, x4);  // the "f" column
+#pragma unroll
+            for (int q = 0; q < 4; ++q) y[4 * ch + q] = x4[q];  // < 3Q
+        }
+        inv_ntt_regs<true>(y, ALIAS ? E1 : E2, T, Q, tid, bar);
+        uint32_t* ap = a + u * N;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            uint32_t v = ap[tid + 256 * r] + y[r];
+            v = min(v, v - 2 * Q);
+            ap[tid + 256 * r] = min(v, v - Q);
+        }
+    }
+    __syncthreads();  // a[] complete (and every group past its last exchange) before the next step
+}
+
+template <bool GATE, bool XZW, bool ALIAS>
+__global__ void __launch_bounds__(1024, 1) blind_rotate_grouped(const DevCtx P, const FastTables T, const GateIO io) {
+    extern __shared__ __align__(16) uint32_t sm[];
+    const uint32_t k = P.k, n = P.n, G = blockDim.x >> 8, grp = threadIdx.x >> 8, tid = threadIdx.x & 255;
+    constexpr uint32_t N = FN;
+    constexpr uint32_t EW = (ALIAS ? 2 : 3) * FNP;  // exchange words per group
+    uint32_t* a = sm;
+    uint32_t* E1 = a + k * N + grp * EW;
+    uint32_t* E2 = E1 + 2 * FNP;
+    uint32_t* Vs = a + k * N + G * EW;
+    uint16_t* crot = reinterpret_cast<uint16_t*>(Vs + N);
+
+    for (uint32_t e = threadIdx.x; e < N; e += blockDim.x) Vs[e] = 0;
+    rotate_prologue<GATE>(P, io, blockIdx.x, a, crot);  // ends with a block barrier
+    grouped_step<XZW, true, ALIAS>(P, T, a, E1, E2, Vs, 0, crot[0], tid, grp, G);
+    for (uint32_t s = 1; s < k * n; ++s) {
+        const uint32_t c = crot[s];
+        if (c == 0) continue;
+        grouped_step<XZW, false, ALIAS>(P, T, a, E1, E2, Vs, s, c, tid, grp, G);
+    }
+    rotate_epilogue<GATE>(P, io, blockIdx.x, a, a + k * N);  // scratch: group 0's exchange buffer
 }
 
 // ---- standalone batched transform (config 5, mkfhe_ntt): one polynomial per CTA-iteration, persistent grid -----------
@@ -611,26 +760,54 @@ inline bool fast_use_alias(const DevCtx& d) {
     return fast_smem_bytes(d.k, d.n, false) > 227 * 1024;
 }
 
+// party-parallel groups per gate, overridable for experiments with MKFHE_GROUPS.  Measured on B200 (profiles/r1_s17_*):
+// k = 16: 4 groups 235 gates/s vs 200 for one group (1 gate per SM either way: 32 warps instead of 8);  k = 8: 866 vs 957,
+// k = 4 (2 groups): 3013 vs 4246 -- where several gates fit an SM anyway, the idle groups of the sumV phase cost more than
+// the shorter step brings.  So: grouped from k = 16 on.
+inline uint32_t fast_groups(const DevCtx& d) {
+    uint32_t G = d.k >= 16 ? 4 : 1;
+    if (const char* e = getenv("MKFHE_GROUPS")) G = uint32_t(atoi(e));
+    if (G != 2 && G != 4) return 1;
+    if (d.k > 16 || d.k < G) return 1;
+    return grouped_smem_bytes(d.k, d.n, G, true) <= 227 * 1024 ? G : 1;
+}
+
 inline cudaError_t fast_blind_rotate(FastState& F, const DevCtx& d, bool gate, const GateIO& io, uint32_t batch, cudaStream_t st,
                                      uint64_t* launches) {
-    const bool alias = fast_use_alias(d), xzw = d.variant == 0;
-    const size_t smem = fast_smem_bytes(d.k, d.n, alias);
+    const bool xzw = d.variant == 0;
+    const uint32_t G = fast_groups(d);
+    const bool alias = G > 1 ? grouped_smem_bytes(d.k, d.n, G, false) > 227 * 1024 : fast_use_alias(d);
+    const size_t smem = G > 1 ? grouped_smem_bytes(d.k, d.n, G, alias) : fast_smem_bytes(d.k, d.n, alias);
     auto launch = [&](auto kern) -> cudaError_t {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
         if (e != cudaSuccess) return e;
-        kern<<<batch, FT, smem, st>>>(d, F.T, io);
+        kern<<<batch, FT * G, smem, st>>>(d, F.T, io);
         return cudaSuccess;
     };
     cudaError_t e;
-    switch ((gate ? 4 : 0) | (xzw ? 2 : 0) | (alias ? 1 : 0)) {
-        case 0: e = launch(blind_rotate_fast<false, false, false>); break;
-        case 1: e = launch(blind_rotate_fast<false, false, true>); break;
-        case 2: e = launch(blind_rotate_fast<false, true, false>); break;
-        case 3: e = launch(blind_rotate_fast<false, true, true>); break;
-        case 4: e = launch(blind_rotate_fast<true, false, false>); break;
-        case 5: e = launch(blind_rotate_fast<true, false, true>); break;
-        case 6: e = launch(blind_rotate_fast<true, true, false>); break;
-        default: e = launch(blind_rotate_fast<true, true, true>); break;
+    const int sel = (gate ? 4 : 0) | (xzw ? 2 : 0) | (alias ? 1 : 0);
+    if (G > 1) {
+        switch (sel) {
+            case 0: e = launch(blind_rotate_grouped<false, false, false>); break;
+            case 1: e = launch(blind_rotate_grouped<false, false, true>); break;
+            case 2: e = launch(blind_rotate_grouped<false, true, false>); break;
+            case 3: e = launch(blind_rotate_grouped<false, true, true>); break;
+            case 4: e = launch(blind_rotate_grouped<true, false, false>); break;
+            case 5: e = launch(blind_rotate_grouped<true, false, true>); break;
+            case 6: e = launch(blind_rotate_grouped<true, true, false>); break;
+            default: e = launch(blind_rotate_grouped<true, true, true>); break;
+        }
+    } else {
+        switch (sel) {
+            case 0: e = launch(blind_rotate_fast<false, false, false>); break;
+            case 1: e = launch(blind_rotate_fast<false, false, true>); break;
+            case 2: e = launch(blind_rotate_fast<false, true, false>); break;
+            case 3: e = launch(blind_rotate_fast<false, true, true>); break;
+            case 4: e = launch(blind_rotate_fast<true, false, false>); break;
+            case 5: e = launch(blind_rotate_fast<true, false, true>); break;
+            case 6: e = launch(blind_rotate_fast<true, true, false>); break;
+            default: e = launch(blind_rotate_fast<true, true, true>); break;
+        }
     }
     if (e != cudaSuccess) return e;
     ++*launches;
