@@ -93,7 +93,11 @@ __device__ __forceinline__ void gate_sync(uint32_t bar) {
 // out: x[p][i] = slot 8 tid + i (OpenFHE order)    (values < 24Q: +2Q per stage, 11 stages)
 // E: NP * FNP words of shared memory.  Contains one __syncthreads (after the pass-1 writes); the caller guarantees that
 // every thread is done reading E from its previous use before any thread enters (a barrier lies in between).
-template <int NP, bool GRP = false>
+// HALF: the 2048 words are TWO polynomials of 1024 coefficients ([0, 1024) and [1024, 2048)).  A size-2048 Cooley-Tukey
+// transform is one stage (t = 1024) followed by two independent size-1024 transforms of the halves, so skipping that stage
+// and indexing the twiddles per half (the table built by fast_init for N = 1024: entry m + b = twiddle of block b mod m/2
+// of the size-1024 stage with m/2 blocks) transforms both polynomials with the same code, layouts and exchanges.
+template <int NP, bool GRP = false, bool HALF = false>
 __device__ __forceinline__ void fwd_ntt_regs(uint32_t (&x)[NP][8], uint32_t* E, const FastTables& T, uint32_t Q, uint32_t tid,
                                              uint32_t bar = 0) {
     const uint32_t twoQ = 2 * Q;
@@ -101,7 +105,7 @@ __device__ __forceinline__ void fwd_ntt_regs(uint32_t (&x)[NP][8], uint32_t* E, 
     const ExIdx ex(tid);
     // pass 1: t = 1024, 512, 256  (m = 1, 2, 4 blocks; block of coefficient tid + 256 r at stage s is r >> (3 - s))
 #pragma unroll
-    for (int s = 0; s < 3; ++s) {
+    for (int s = HALF ? 1 : 0; s < 3; ++s) {
         const int h = 4 >> s;
 #pragma unroll
         for (int r = 0; r < 8; ++r) {
@@ -193,7 +197,7 @@ __device__ __forceinline__ void fwd_ntt_regs(uint32_t (&x)[NP][8], uint32_t* E, 
 // out: x[r] = coefficient tid + 256 r, values in [0, 2Q)
 // bounds: first stage (twiddle 1, no multiplication) < 12Q, then +2Q per stage: < 32Q < 2^32.
 // E: FNP words.  One __syncthreads inside (after the pass-3 writes); same entry condition as fwd_ntt_regs.
-template <bool GRP = false>
+template <bool GRP = false, bool HALF = false>
 __device__ __forceinline__ void inv_ntt_regs(uint32_t (&x)[8], uint32_t* E, const FastTables& T, uint32_t Q, uint32_t tid,
                                              uint32_t bar = 0) {
     const uint32_t twoQ = 2 * Q, sixQ = 6 * Q;
@@ -253,9 +257,9 @@ __device__ __forceinline__ void inv_ntt_regs(uint32_t (&x)[8], uint32_t* E, cons
     gate_sync<GRP>(bar);
 #pragma unroll
     for (int r = 0; r < 8; ++r) x[r] = E[ex.A(r)];
-    // pass 4: t = 256, 512, 1024  (h = t / 256; m = 256 (r mod h) + tid)
+    // pass 4: t = 256, 512, 1024  (h = t / 256; m = 256 (r mod h) + tid); HALF: the halves stay separate (no t = 1024)
 #pragma unroll
-    for (int s = 0; s < 3; ++s) {
+    for (int s = 0; s < (HALF ? 2 : 3); ++s) {
         const int h = 1 << s;
         const uint2* tws = T.itw2 + 256 * h + tid;
 #pragma unroll
@@ -340,7 +344,8 @@ template <bool XZW, bool FIRST>
 __device__ __forceinline__ void key_mac4(const DevCtx& P, const uint32_t* k1p, const uint32_t* k2p, const uint32_t* evsp, uint32_t c,
                                          uint32_t cneg, uint32_t e0p, uint32_t e0n, int ch, const uint32_t (&D)[2][8],
                                          uint32_t (&x4)[4]) {
-    constexpr uint32_t N = FN;
+    constexpr uint32_t N = FN, KCH = FN / 2;  // key polynomials are stored in register order: chunk ch of thread t at
+                                              // words KCH ch + 4 t .. + 3 (fast_permute_keys), so a warp load is 512 contiguous bytes
     const uint32_t Q = P.mod.Q;
     if (FIRST) {
         uint32_t mp[4], mn[4];
@@ -349,11 +354,11 @@ __device__ __forceinline__ void key_mac4(const DevCtx& P, const uint32_t* k1p, c
         uint32_t kk[2][4];
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
-            const uint4 es = ldg4_stream(evsp + 2 * j * N + 4 * ch), e1 = ldg4_stream(k1p + 2 * j * N + 4 * ch);
+            const uint4 es = ldg4_stream(evsp + 2 * j * N + KCH * ch), e1 = ldg4_stream(k1p + 2 * j * N + KCH * ch);
             const uint32_t esv[4] = {es.x, es.y, es.z, es.w}, e1v[4] = {e1.x, e1.y, e1.z, e1.w};
             uint32_t e2v[4] = {0, 0, 0, 0};
             if (XZW) {
-                const uint4 e2 = ldg4_stream(k2p + 2 * j * N + 4 * ch);
+                const uint4 e2 = ldg4_stream(k2p + 2 * j * N + KCH * ch);
                 e2v[0] = e2.x; e2v[1] = e2.y; e2v[2] = e2.z; e2v[3] = e2.w;
             }
 #pragma unroll
@@ -371,8 +376,8 @@ __device__ __forceinline__ void key_mac4(const DevCtx& P, const uint32_t* k1p, c
         // reductions and the conditional subtractions)
         uint32_t mn[4];
         monomial4(P.psipow, e0n, cneg, ch, mn);
-        const uint4 a0 = ldg4_stream(k1p + 4 * ch), a1 = ldg4_stream(k1p + 2 * N + 4 * ch);
-        const uint4 b0 = ldg4_stream(k2p + 4 * ch), b1 = ldg4_stream(k2p + 2 * N + 4 * ch);
+        const uint4 a0 = ldg4_stream(k1p + KCH * ch), a1 = ldg4_stream(k1p + 2 * N + KCH * ch);
+        const uint4 b0 = ldg4_stream(k2p + KCH * ch), b1 = ldg4_stream(k2p + 2 * N + KCH * ch);
         const uint32_t a0v[4] = {a0.x, a0.y, a0.z, a0.w}, a1v[4] = {a1.x, a1.y, a1.z, a1.w};
         const uint32_t b0v[4] = {b0.x, b0.y, b0.z, b0.w}, b1v[4] = {b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
@@ -387,7 +392,7 @@ __device__ __forceinline__ void key_mac4(const DevCtx& P, const uint32_t* k1p, c
             x4[q] = static_cast<uint32_t>((s1 + static_cast<uint64_t>(q1) * Q) >> 32);  // < 3Q
         }
     } else {
-        const uint4 a0 = ldg4_stream(k1p + 4 * ch), a1 = ldg4_stream(k1p + 2 * N + 4 * ch);
+        const uint4 a0 = ldg4_stream(k1p + KCH * ch), a1 = ldg4_stream(k1p + 2 * N + KCH * ch);
         const uint32_t a0v[4] = {a0.x, a0.y, a0.z, a0.w}, a1v[4] = {a1.x, a1.y, a1.z, a1.w};
 #pragma unroll
         for (int q = 0; q < 4; ++q) x4[q] = mac2(D[0][4 * ch + q], a0v[q], D[1][4 * ch + q], a1v[q], P.mod);
@@ -407,9 +412,9 @@ __device__ __forceinline__ void fast_step(const DevCtx& P, const FastTables& T, 
     const uint32_t u = FIRST ? 0u : s / n, i = FIRST ? 0u : s - u * n;
     const uint32_t cneg = (M - c) & (M - 1);
     const size_t per = size_t(2) * 2 * N;  // words of one UniEncEvalKey: [j][d|f][N]
-    const uint32_t* ev1 = P.bk + (size_t(u * P.S) * n + i) * per + 8 * tid;
+    const uint32_t* ev1 = P.bk + (size_t(u * P.S) * n + i) * per + 4 * tid;
     const uint32_t* ev2 = XZW ? ev1 + size_t(n) * per : ev1;
-    const uint32_t* evs = P.bk + size_t(k) * P.S * n * per + 8 * tid;  // evk* = ek[0][0][n] (mk-acc-xzw.cpp:51,72-74)
+    const uint32_t* evs = P.bk + size_t(k) * P.S * n * per + 4 * tid;  // evk* = ek[0][0][n] (mk-acc-xzw.cpp:51,72-74)
     const uint32_t brv8 = __brev(tid) >> 24;
     const uint32_t e0n = cneg * (2 * brv8 + 1), e0p = c * (2 * brv8 + 1);
     uint32_t keep[8];  // V while parties are processed, then X of the key owner
@@ -430,7 +435,7 @@ __device__ __forceinline__ void fast_step(const DevCtx& P, const FastTables& T, 
         }
         fwd_ntt_regs<2>(D, E1, T, Q, tid);
         const int col = it < k ? 0 : 1;  // "d" column for the parties, "f" column for the V term
-        const uint32_t* pk = P.pkey + size_t(p) * 2 * N + 8 * tid;
+        const uint32_t* pk = P.pkey + size_t(p) * 2 * N + 4 * tid;
         const uint32_t* k1p = ev1 + col * N;  // digit j at + 2 j N
         const uint32_t* k2p = ev2 + col * N;
 #pragma unroll
@@ -438,7 +443,7 @@ __device__ __forceinline__ void fast_step(const DevCtx& P, const FastTables& T, 
             uint32_t x4[4];  // <D, key> at slots 8 tid + 4 ch + q, < 3Q
             key_mac4<XZW, FIRST>(P, k1p, k2p, evs + col * N, c, cneg, e0p, e0n, ch, D, x4);
             if (it < k) {
-                const uint4 q0 = ldg4(pk + 4 * ch), q1 = ldg4(pk + N + 4 * ch);
+                const uint4 q0 = ldg4(pk + (N / 2) * ch), q1 = ldg4(pk + N + (N / 2) * ch);
                 const uint32_t pp0[4] = {q0.x, q0.y, q0.z, q0.w}, pp1[4] = {q1.x, q1.y, q1.z, q1.w};
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
@@ -521,9 +526,9 @@ __device__ __forceinline__ void grouped_step(const DevCtx& P, const FastTables& 
     const uint32_t u = FIRST ? 0u : s / n, i = FIRST ? 0u : s - u * n;
     const uint32_t cneg = (M - c) & (M - 1);
     const size_t per = size_t(2) * 2 * N;
-    const uint32_t* ev1 = P.bk + (size_t(u * P.S) * n + i) * per + 8 * tid;
+    const uint32_t* ev1 = P.bk + (size_t(u * P.S) * n + i) * per + 4 * tid;
     const uint32_t* ev2 = XZW ? ev1 + size_t(n) * per : ev1;
-    const uint32_t* evs = P.bk + size_t(k) * P.S * n * per + 8 * tid;
+    const uint32_t* evs = P.bk + size_t(k) * P.S * n * per + 4 * tid;
     const uint32_t brv8 = __brev(tid) >> 24;
     const uint32_t e0n = cneg * (2 * brv8 + 1), e0p = c * (2 * brv8 + 1);
     uint32_t y[8];
@@ -538,12 +543,12 @@ __device__ __forceinline__ void grouped_step(const DevCtx& P, const FastTables& 
 #pragma unroll
         for (int r = 0; r < 8; ++r) decompose2(FIRST ? ap[tid + 256 * r] : rot_sub(ap, c, tid + 256 * r, N, Q), Q, g, D[0][r], D[1][r]);
         fwd_ntt_regs<2, true>(D, E1, T, Q, tid, bar);
-        const uint32_t* pk = P.pkey + size_t(p) * 2 * N + 8 * tid;
+        const uint32_t* pk = P.pkey + size_t(p) * 2 * N + 4 * tid;
 #pragma unroll
         for (int ch = 0; ch < 2; ++ch) {
             uint32_t x4[4];
             key_mac4<XZW, FIRST>(P, ev1, ev2, evs, c, cneg, e0p, e0n, ch, D, x4);
-            const uint4 q0 = ldg4(pk + 4 * ch), q1 = ldg4(pk + N + 4 * ch);
+            const uint4 q0 = ldg4(pk + (N / 2) * ch), q1 = ldg4(pk + N + (N / 2) * ch);
             const uint32_t pp0[4] = {q0.x, q0.y, q0.z, q0.w}, pp1[4] = {q1.x, q1.y, q1.z, q1.w};
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
@@ -630,6 +635,7 @@ __global__ void __launch_bounds__(1024, 1) blind_rotate_grouped(const DevCtx P, 
 // ---- standalone batched transform (config 5, mkfhe_ntt): one polynomial per CTA-iteration, persistent grid -----------
 // HBM-bound at large batch (16 KiB moved per 11 264 butterflies), so the next polynomial's coefficients are fetched into
 // registers before the current one is transformed: loads of iteration i+1 overlap the arithmetic of iteration i.
+template <bool HALF>  // HALF: N = 1024, one CTA-iteration transforms the polynomials 2b and 2b + 1 (batch counts pairs)
 __global__ void __launch_bounds__(FT, 4) ntt_batch_fast(const FastTables T, const uint32_t Q, const uint2 one2, uint32_t* polys,
                                                         const uint64_t batch, const int inverse) {
     __shared__ __align__(16) uint32_t E[FNP];
@@ -656,7 +662,7 @@ __global__ void __launch_bounds__(FT, 4) ntt_batch_fast(const FastTables T, cons
 #pragma unroll
             for (int r = 0; r < 8; ++r) x[0][r] = nx[r];
             if (b + gridDim.x < batch) fetch(b + gridDim.x);
-            fwd_ntt_regs<1>(x, E, T, Q, tid);
+            fwd_ntt_regs<1, false, HALF>(x, E, T, Q, tid);
 #pragma unroll
             for (int c = 0; c < 2; ++c) {
                 uint4 v;
@@ -671,7 +677,7 @@ __global__ void __launch_bounds__(FT, 4) ntt_batch_fast(const FastTables T, cons
 #pragma unroll
             for (int r = 0; r < 8; ++r) x[r] = nx[r];
             if (b + gridDim.x < batch) fetch(b + gridDim.x);
-            inv_ntt_regs(x, E, T, Q, tid);
+            inv_ntt_regs<false, HALF>(x, E, T, Q, tid);
 #pragma unroll
             for (int r = 0; r < 8; ++r) __stcs(p + tid + 256 * r, fold1(x[r], Q));
         }
@@ -685,6 +691,7 @@ struct FastState {
     uint2 *d_tw2{nullptr}, *d_itw2{nullptr}, *d_scale2{nullptr};
     uint2 one2{};
     int sms{148};
+    bool half{false};  // tables for N = 1024 (two polynomials per 2048-word pass): only the batched transform uses them
 };
 
 inline bool fast_supported(const DevCtx& d) {
@@ -692,8 +699,13 @@ inline bool fast_supported(const DevCtx& d) {
            fast_smem_bytes(d.k, d.n, true) <= 227 * 1024;
 }
 
+// N = 1024 with a modulus the lazy butterflies can take: the batched transform (mkfhe_ntt, config 5) runs on the HALF path
+inline bool fast_ntt_half_supported(const DevCtx& d) { return d.N == FN / 2 && d.mod.Q < (1u << 27); }
+
 inline cudaError_t fast_init(FastState& F, const DevCtx& d, uint32_t psi, cudaStream_t st, uint64_t* dev_bytes) {
     const uint32_t Q = d.mod.Q, N = FN;
+    const bool half = d.N == FN / 2;
+    const uint32_t NT = half ? FN / 2 : FN, LOGT = half ? FLOGN - 1 : FLOGN;  // size of the transform the tables describe
     auto mul = [&](uint32_t a, uint32_t b) { return uint32_t((uint64_t(a) * b) % Q); };
     auto pw = [&](uint32_t a, uint64_t e) {
         uint64_t r = 1, b = a % Q;
@@ -704,21 +716,34 @@ inline cudaError_t fast_init(FastState& F, const DevCtx& d, uint32_t psi, cudaSt
     auto pair = [&](uint32_t w) { return make_uint2(w, uint32_t((uint64_t(w) << 32) / Q)); };
     auto brv = [&](uint32_t x) {
         uint32_t r = 0;
-        for (uint32_t i = 0; i < FLOGN; ++i) r |= ((x >> i) & 1u) << (FLOGN - 1 - i);
+        for (uint32_t i = 0; i < LOGT; ++i) r |= ((x >> i) & 1u) << (LOGT - 1 - i);
         return r;
     };
-    const uint32_t psi_inv = pw(psi, uint64_t(Q) - 2), omega_inv = mul(psi_inv, psi_inv), n_inv = pw(N, uint64_t(Q) - 2);
+    const uint32_t psi_inv = pw(psi, uint64_t(Q) - 2), omega_inv = mul(psi_inv, psi_inv), n_inv = pw(NT, uint64_t(Q) - 2);
     std::vector<uint2> tw(N), itw(N), sc(N);
     uint32_t x = 1, xi = n_inv;
-    for (uint32_t i = 0; i < N; ++i) {
+    for (uint32_t i = 0; i < NT; ++i) {
         tw[brv(i)] = pair(x);
         sc[i] = pair(xi);
         x = mul(x, psi);
         xi = mul(xi, psi_inv);
     }
+    if (half) {
+        // 2048-word view of two size-1024 transforms: stage with m blocks (m = 2 .. 1024) = the size-1024 stage with m/2
+        // blocks in each half, block b of the view = block b mod m/2 of its half; scale by coefficient index mod 1024
+        std::vector<uint2> t1(tw.begin(), tw.begin() + NT);
+        for (uint32_t m = 2; m < N; m <<= 1)
+            for (uint32_t b = 0; b < m; ++b) tw[m + b] = t1[m / 2 + (b & (m / 2 - 1))];
+        tw[0] = tw[1] = pair(1);
+        for (uint32_t i = 0; i < NT; ++i) sc[NT + i] = sc[i];
+    }
     itw[0] = pair(1);
     for (uint32_t t = 1; t < N; t <<= 1) {
-        const uint32_t step = pw(omega_inv, N / (2 * t));  // omega^-(N/2t): a primitive 2t-th root
+        if (t >= NT) {  // HALF: no stage joins the halves; entries unused
+            for (uint32_t m = 0; m < t; ++m) itw[t + m] = pair(1);
+            continue;
+        }
+        const uint32_t step = pw(omega_inv, NT / (2 * t));  // omega^-(NT/2t): a primitive 2t-th root
         uint32_t v = 1;
         for (uint32_t m = 0; m < t; ++m) {
             itw[t + m] = pair(v);
@@ -737,6 +762,7 @@ inline cudaError_t fast_init(FastState& F, const DevCtx& d, uint32_t psi, cudaSt
     for (int i = 0; i < 4; ++i) F.T.itwA[i] = itw[i];
     F.T.zero = 0;
     F.one2 = pair(1);
+    F.half = half;
     int dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&F.sms, cudaDevAttrMultiProcessorCount, dev);
@@ -747,8 +773,28 @@ inline void fast_destroy(FastState& F) {
         if (p) cudaFree(p);
     F = FastState{};
 }
-inline cudaError_t fast_load_bk(FastState&, const DevCtx&, cudaStream_t, uint64_t*, uint64_t*) { return cudaSuccess; }
-inline cudaError_t fast_load_pkey(FastState&, const DevCtx&, cudaStream_t, uint64_t*, uint64_t*) { return cudaSuccess; }
+// Key polynomials -> register order, in place, one CTA per polynomial: thread t of a gate holds the slots 8t .. 8t+7 after
+// a forward transform and multiplies them by the key in two chunks of 4; chunk ch of thread t moves to words 1024 ch + 4 t,
+// so each 128-bit key load of a warp reads 512 contiguous bytes (slot order would read half of every 32-byte sector twice).
+__global__ void __launch_bounds__(FT) fast_permute_keys(uint32_t* polys) {
+    uint32_t* p = polys + size_t(blockIdx.x) * FN;
+    const uint32_t t = threadIdx.x;
+    const uint4 c0 = *reinterpret_cast<const uint4*>(p + 8 * t), c1 = *reinterpret_cast<const uint4*>(p + 8 * t + 4);
+    __syncthreads();
+    *reinterpret_cast<uint4*>(p + 4 * t) = c0;
+    *reinterpret_cast<uint4*>(p + FN / 2 + 4 * t) = c1;
+}
+inline cudaError_t fast_permute(uint32_t* polys, uint64_t words, cudaStream_t st, uint64_t* launches) {
+    fast_permute_keys<<<unsigned(words / FN), FT, 0, st>>>(polys);
+    ++*launches;
+    return cudaGetLastError();
+}
+inline cudaError_t fast_load_bk(FastState&, const DevCtx& d, uint64_t words, cudaStream_t st, uint64_t*, uint64_t* launches) {
+    return fast_permute(const_cast<uint32_t*>(d.bk), words, st, launches);
+}
+inline cudaError_t fast_load_pkey(FastState&, const DevCtx& d, uint64_t words, cudaStream_t st, uint64_t*, uint64_t* launches) {
+    return fast_permute(const_cast<uint32_t*>(d.pkey), words, st, launches);
+}
 
 // gates resident per SM: 64 registers x 256 threads allow 4; shared memory (1 KiB reserved per CTA) may allow fewer
 inline int fast_gates_per_sm(size_t smem) { return int(std::min<size_t>(4, (227 * 1024) / (smem + 1024))); }
@@ -816,8 +862,10 @@ inline cudaError_t fast_blind_rotate(FastState& F, const DevCtx& d, bool gate, c
 
 inline cudaError_t fast_ntt(FastState& F, const DevCtx& d, uint32_t* polys, uint64_t batch, int inverse, cudaStream_t st,
                             uint64_t* launches) {
+    // HALF: batch counts PAIRS of size-1024 polynomials (the caller sends an odd last one through the generic kernel)
     const unsigned grid = unsigned(std::min<uint64_t>(batch, uint64_t(F.sms) * 4));
-    ntt_batch_fast<<<grid, FT, 0, st>>>(F.T, d.mod.Q, F.one2, polys, batch, inverse);
+    if (F.half) ntt_batch_fast<true><<<grid, FT, 0, st>>>(F.T, d.mod.Q, F.one2, polys, batch, inverse);
+    else ntt_batch_fast<false><<<grid, FT, 0, st>>>(F.T, d.mod.Q, F.one2, polys, batch, inverse);
     ++*launches;
     return cudaGetLastError();
 }

@@ -46,6 +46,7 @@ struct mkfhe_ctx {
     uint32_t r2{0};  // 2^64 mod Q
     FastState fast{};
     bool use_fast{false};
+    bool ntt_half{false};  // N = 1024: batched transforms on the two-polynomials-per-pass path of fast_kernels.cuh
     cudaEvent_t ev[3]{nullptr, nullptr, nullptr};  // before blind rotation | after it | after key switch (last gate batch)
     bool ev_valid{false};
 };
@@ -249,7 +250,11 @@ int mkfhe_ctx_create(const mkfhe_params* p, mkfhe_ctx** out) {
     if (ctx->use_fast && (rc = fast_init(ctx->fast, d, p->psi, ctx->stream, &ctx->dev_bytes))) {
         return bail(fail(ctx, MKFHE_ECUDA, "fast path initialisation failed: %s", cudaGetErrorString(cudaGetLastError())));
     }
-    if (getenv("MKFHE_FORCE_GENERIC")) ctx->use_fast = false;
+    ctx->ntt_half = !ctx->use_fast && fast_ntt_half_supported(d);
+    if (ctx->ntt_half && (rc = fast_init(ctx->fast, d, p->psi, ctx->stream, &ctx->dev_bytes))) {
+        return bail(fail(ctx, MKFHE_ECUDA, "N = 1024 transform tables: %s", cudaGetErrorString(cudaGetLastError())));
+    }
+    if (getenv("MKFHE_FORCE_GENERIC")) ctx->use_fast = ctx->ntt_half = false;
     // fused key switch: keys as u16 rows, the gate kernel finishes the gate on chip.  Needs qKS < 2^16 and N + npad words of
     // scratch behind the accumulator ((ell + 2) * N words exist in both kernels).
     d.npad = (p->n + (p->scheme == MKFHE_SCHEME_MKLWE ? 1u : 0u) + 15u) & ~15u;
@@ -302,7 +307,7 @@ int mkfhe_load_bk(mkfhe_ctx* ctx, const uint32_t* bk, uint64_t words) {
     int rc = upload(ctx, &ctx->bk, bk, words, true);
     ctx->d.bk = ctx->bk;
     if (!rc && ctx->use_fast) {
-        cudaError_t e = fast_load_bk(ctx->fast, ctx->d, ctx->stream, &ctx->dev_bytes, &ctx->launches);
+        cudaError_t e = fast_load_bk(ctx->fast, ctx->d, words, ctx->stream, &ctx->dev_bytes, &ctx->launches);
         if (e != cudaSuccess) return fail(ctx, MKFHE_ECUDA, "fast_load_bk: %s", cudaGetErrorString(e));
     }
     return rc;
@@ -314,7 +319,7 @@ int mkfhe_load_pkey(mkfhe_ctx* ctx, const uint32_t* pk, uint64_t words) {
     int rc = upload(ctx, &ctx->pkey, pk, words, true);
     ctx->d.pkey = ctx->pkey;
     if (!rc && ctx->use_fast) {
-        cudaError_t e = fast_load_pkey(ctx->fast, ctx->d, ctx->stream, &ctx->dev_bytes, &ctx->launches);
+        cudaError_t e = fast_load_pkey(ctx->fast, ctx->d, words, ctx->stream, &ctx->dev_bytes, &ctx->launches);
         if (e != cudaSuccess) return fail(ctx, MKFHE_ECUDA, "fast_load_pkey: %s", cudaGetErrorString(e));
     }
     return rc;
@@ -554,6 +559,15 @@ int mkfhe_ntt_dev(mkfhe_ctx* ctx, uint32_t* d_polys, uint64_t batch, int inverse
         cudaError_t e = fast_ntt(ctx->fast, ctx->d, d_polys, batch, inverse, ctx->stream, &ctx->launches);
         if (e != cudaSuccess) return fail(ctx, MKFHE_ECUDA, "fast_ntt: %s", cudaGetErrorString(e));
         return MKFHE_OK;
+    }
+    if (ctx->ntt_half) {  // pairs on the specialised kernel, an odd last polynomial on the generic one
+        if (batch / 2) {
+            cudaError_t e = fast_ntt(ctx->fast, ctx->d, d_polys, batch / 2, inverse, ctx->stream, &ctx->launches);
+            if (e != cudaSuccess) return fail(ctx, MKFHE_ECUDA, "fast_ntt: %s", cudaGetErrorString(e));
+        }
+        if ((batch & 1) == 0) return MKFHE_OK;
+        d_polys += (batch - 1) * ctx->p.N;
+        batch = 1;
     }
     const unsigned threads = std::max(32u, std::min(1024u, ctx->p.N / 2));
     ntt_batch_generic<<<unsigned(batch), threads, ctx->p.N * 4, ctx->stream>>>(ctx->d, d_polys, inverse);

@@ -95,3 +95,27 @@ def test_drop_in_accumulator_through_reference_api(full):
         r.use_accumulator_b200(LIB_PATH, restore=True)
     assert (cpu_out == gpu_out).all() and cpu_b == gpu_b
     assert r.decrypt(gpu_out, gpu_b) == 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("batch", [1, 2, 7, 64])
+def test_ntt_n1024_vs_oracle(batch):
+    """Config 5 at N = 1024 (Q = 134215681, psi = 282116: SURVEY.md 8c): the batched transform runs two polynomials per
+    2048-word pass of the specialised kernel (an odd last one on the generic kernel); bit-exact against the C oracle, whose
+    transform is pinned to NativePoly::SetFormat (tests/test_oracle.py)."""
+    from types import SimpleNamespace
+
+    from gpu_util import ctx_from_params
+    from util import make_oracle
+
+    p = SimpleNamespace(k=2, N=1024, Q=134215681, psi=282116, q=32749, qKS=32749, n=16, baseG_log2=9, digitsG=3, baseKS=32, dKS=3,
+                        variant=1, scheme=1)
+    ctx = ctx_from_params(p)
+    o = make_oracle(p)
+    x = np.random.default_rng(50 + batch).integers(0, p.Q, size=(batch, p.N), dtype=np.uint32)
+    x[0, :4] = [0, 1, p.Q - 1, p.Q - 2]
+    f = ctx.NTT(x)
+    assert (f == o.ntt(x, False)).all()
+    assert (ctx.NTT(x, inverse=True) == o.ntt(x, True)).all()
+    assert (ctx.NTT(f, inverse=True) == x).all()
+    ctx.close()
