@@ -77,6 +77,16 @@ def work_model(P):
                 key_bytes=S * key_bytes_step)
 
 
+def ncu_traffic(paramset, batch):
+    """DRAM bytes (read + write) of one gate-kernel launch, from the committed ncu --set full capture of the same workload
+    (profiles/ncu_traffic.json, written from profiles/r1_*_<workload>.txt); None when no capture matches this launch shape."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        return t.get(f"{paramset}:{batch}", {}).get("dram_bytes")
+    except Exception:
+        return None
+
+
 # ---------------------------------------------------------------- clocks sampling (B200_PROFILING.md recipe)
 class ClockSampler:
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
@@ -415,6 +425,7 @@ def run_gpu_arm(args):
         value = total_gates / (dev_ms * 1e-3)
         e2e = total_gates / (e2e_ms * 1e-3)
         imad_peak = ctx.measure_int32_peak()
+        bfly_peak = ctx.measure_butterfly_peak()
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -424,7 +435,9 @@ def run_gpu_arm(args):
         rot_s = rot_sum * 1e-3 / args.steps  # average blind-rotation launch duration (max over ranks)
         instr_per_launch = wm["instr"] * B
         ach = instr_per_launch / rot_s
+        mm_ach = wm["modmul"] * B / rot_s  # modular multiplications per second (SURVEY 8d per-gate figure x gates per launch)
         key_ach = wm["key_bytes"] * B / rot_s / 1e9
+        traffic = ncu_traffic(args.paramset, B)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -433,13 +446,19 @@ def run_gpu_arm(args):
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": int((2 * B * P.k * P.n + (2 * B if lwe else 0)) * 4),
                     "d2h_bytes_per_step": int((B * P.k * P.n + (B if lwe else 0)) * 4)},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "int32", "kernel": "blind_rotate", "achieved": ach / 1e12, "peak": imad_peak / 1e12,
-                         "unit": "Tinstr/s", "frac": ach / imad_peak, "traffic": None,
-                         "model": "SURVEY 8d: 7 instr/butterfly + 5/pointwise MAC; peak = IMAD chain micro-kernel measured in this run",
-                         "modmul_per_gate": wm["modmul"], "instr_per_gate": wm["instr"],
-                         "kernel_ms": rot_s * 1e3, "share_of_step": rot_sum / dev_ms},
+            "roofline": {"bound": "int32", "kernel": "blind_rotate", "achieved": mm_ach / 1e12, "peak": bfly_peak / 1e12,
+                         "unit": "Tmodmul/s", "frac": mm_ach / bfly_peak, "traffic": traffic,
+                         "model": "achieved = SURVEY 8d modular multiplications per gate (butterflies + pointwise MACs) x gates "
+                                  "per launch / launch time; peak = register-resident lazy Shoup butterflies/s measured on this "
+                                  "GPU in this run (mkfhe_measure_butterfly_peak: nothing but butterflies, no memory traffic)",
+                         "modmul_per_gate": wm["modmul"], "kernel_ms": rot_s * 1e3, "share_of_step": rot_sum / dev_ms},
+            "roofline_imad_model": {"bound": "int32", "achieved": ach / 1e12, "peak": imad_peak / 1e12, "unit": "Tinstr/s",
+                                    "frac": ach / imad_peak, "instr_per_gate": wm["instr"],
+                                    "model": "SURVEY 8d fixed cost model: 7 instr/butterfly + 5/pointwise MAC against the IMAD-chain "
+                                             "rate measured in this run; the kernel's butterfly is 5 instructions on two pipes, so "
+                                             "this fraction can exceed 1 -- kept for continuity with earlier rounds"},
             "roofline_hbm": {"bound": "hbm", "kernel": "blind_rotate key stream", "achieved": key_ach, "peak": hbm_peak,
-                             "unit": "GB/s", "frac": key_ach / hbm_peak, "traffic": None,
+                             "unit": "GB/s", "frac": key_ach / hbm_peak, "traffic": traffic,
                              "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback 6650",
                              "bytes_per_gate": wm["key_bytes"], "note": "algorithmic key bytes if every gate streamed its own copy"},
             "kernels_ms": {"blind_rotate": rot_sum / args.steps, "key_switch": ks_sum / args.steps},

@@ -157,6 +157,10 @@ const char* mkfhe_version(void);
 /* INT32 pipe micro-benchmark (dependent IMAD chains on every SM): returns thread-level IMAD/s in *imad_per_s.
  * Used by bench.py as the denominator of the integer roofline (SURVEY.md section 8d asks for a measured peak). */
 int mkfhe_measure_int32_peak(mkfhe_ctx* ctx, double* imad_per_s);
+/* Modular-butterfly micro-benchmark: register-resident lazy Shoup butterflies (the instruction sequence of the transforms,
+ * replacing transformnat-impl.h:299-354 inner loops) on every SM, no memory traffic; returns butterflies/s.  bench.py quotes
+ * the gate kernel's modular multiplications per second (SURVEY.md section 8d figure) against this measured peak. */
+int mkfhe_measure_butterfly_peak(mkfhe_ctx* ctx, double* bfly_per_s);
 
 #ifdef __cplusplus
 }

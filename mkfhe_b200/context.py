@@ -311,3 +311,9 @@ class BinFHEContext:
         v = C.c_double(0)
         self._ck(self._L.mkfhe_measure_int32_peak(self._h, C.byref(v)), "mkfhe_measure_int32_peak")
         return float(v.value)
+
+    def measure_butterfly_peak(self) -> float:
+        """Lazy Shoup butterflies per second this GPU sustains on registers alone (mkfhe_measure_butterfly_peak)."""
+        v = C.c_double(0)
+        self._ck(self._L.mkfhe_measure_butterfly_peak(self._h, C.byref(v)), "mkfhe_measure_butterfly_peak")
+        return float(v.value)

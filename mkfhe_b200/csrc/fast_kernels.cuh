@@ -685,6 +685,41 @@ __global__ void __launch_bounds__(FT, 4) ntt_batch_fast(const FastTables T, cons
     }
 }
 
+// ---- butterfly micro-benchmark: the measured peak the gate kernel's roofline is quoted against -----------------------------
+// Register-resident lazy Shoup butterflies (the exact instruction sequence of the transforms: IMAD.HI + 2 IMAD + 2 IADD3), 16
+// values per thread, 4 radix-2 stages per iteration, twiddles in registers, no memory traffic: what the integer pipes of
+// this GPU sustain when they do nothing but modular butterflies.
+__global__ void __launch_bounds__(256) butterfly_peak_kernel(uint32_t* sink, uint32_t iters, uint32_t Q, uint32_t zero, uint32_t seed) {
+    struct { uint32_t zero; } T{zero};
+    const uint32_t twoQ = 2 * Q;
+    uint32_t x[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) x[i] = (threadIdx.x * 2654435761u + i * 40503u + seed) % Q;
+    uint2 w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const uint32_t v = ((threadIdx.x + i + seed) * 2246822519u) % Q;
+        w[i] = make_uint2(v, uint32_t((uint64_t(v) << 32) / Q));
+    }
+    for (uint32_t it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int st = 0; st < 4; ++st) {
+            const int h = 8 >> st;
+#pragma unroll
+            for (int b = 0; b < 8; ++b) {
+                const int lo = (b / h) * 2 * h + (b % h);
+                MKFHE_BFLY(x[lo], x[lo + h], w[st]);
+            }
+        }
+#pragma unroll
+        for (int i = 0; i < 16; ++i) x[i] &= 0x07ffffffu;  // keep the lazy values bounded: 16 alu ops per 32 butterflies
+    }
+    uint32_t r = 0;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) r ^= x[i];
+    if (r == 0x12345678u) sink[0] = r;
+}
+
 // ---- host side ------------------------------------------------------------------------------------------------------
 struct FastState {
     FastTables T{};

@@ -606,6 +606,37 @@ int mkfhe_decompose(mkfhe_ctx* ctx, const uint32_t* polys, uint32_t* out, uint64
     return MKFHE_OK;
 }
 
+int mkfhe_measure_butterfly_peak(mkfhe_ctx* ctx, double* bfly_per_s) {
+    if (!ctx || !bfly_per_s) return MKFHE_EINVAL;
+    CU(cudaSetDevice(ctx->device));
+    int sms = 0;
+    CU(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device));
+    uint32_t* sink = nullptr;
+    CU(cudaMalloc(&sink, 4));
+    const uint32_t iters = 4096, blocks = sms * 4, threads = 256, Q = ctx->p.Q < (1u << 27) ? ctx->p.Q : 134176769u;
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0));
+    CU(cudaEventCreate(&e1));
+    butterfly_peak_kernel<<<blocks, threads, 0, ctx->stream>>>(sink, 64, Q, 0u, 1u);  // warm-up
+    float best = 1e30f;
+    for (int rep = 0; rep < 5; ++rep) {
+        CU(cudaEventRecord(e0, ctx->stream));
+        butterfly_peak_kernel<<<blocks, threads, 0, ctx->stream>>>(sink, iters, Q, 0u, 2u + rep);
+        CU(cudaEventRecord(e1, ctx->stream));
+        CU(cudaEventSynchronize(e1));
+        float ms = 0;
+        CU(cudaEventElapsedTime(&ms, e0, e1));
+        best = std::min(best, ms);
+        ctx->launches++;
+    }
+    CU(cudaGetLastError());
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(sink);
+    *bfly_per_s = double(blocks) * threads * double(iters) * 32 / (best * 1e-3);
+    return MKFHE_OK;
+}
+
 int mkfhe_measure_int32_peak(mkfhe_ctx* ctx, double* imad_per_s) {
     if (!ctx || !imad_per_s) return MKFHE_EINVAL;
     CU(cudaSetDevice(ctx->device));

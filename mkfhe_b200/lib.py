@@ -23,7 +23,7 @@ SYMBOLS = [
     "mkfhe_load_bk", "mkfhe_load_pkey", "mkfhe_load_ksk_mntru", "mkfhe_load_ksk_mklwe", "mkfhe_load_ctnand",
     "mkfhe_eval_acc", "mkfhe_eval_acc_dev", "mkfhe_eval_nand", "mkfhe_eval_nand_dev", "mkfhe_ntt", "mkfhe_ntt_dev",
     "mkfhe_load_sk", "mkfhe_decrypt", "mkfhe_decrypt_dev",
-    "mkfhe_decompose", "mkfhe_last_gate_timing", "mkfhe_launch_count", "mkfhe_device_bytes", "mkfhe_version", "mkfhe_measure_int32_peak",
+    "mkfhe_decompose", "mkfhe_last_gate_timing", "mkfhe_launch_count", "mkfhe_device_bytes", "mkfhe_version", "mkfhe_measure_int32_peak", "mkfhe_measure_butterfly_peak",
 ]
 
 
@@ -77,5 +77,6 @@ def load():
     L.mkfhe_device_bytes.restype = u64
     L.mkfhe_version.restype = C.c_char_p
     L.mkfhe_measure_int32_peak.argtypes = [vp, C.POINTER(C.c_double)]
+    L.mkfhe_measure_butterfly_peak.argtypes = [vp, C.POINTER(C.c_double)]
     _lib = L
     return L
