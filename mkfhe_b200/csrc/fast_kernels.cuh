@@ -486,8 +486,11 @@ __device__ __forceinline__ void fast_step(const DevCtx& P, const FastTables& T, 
     __syncthreads();  // a[] complete before the next step's shifted reads
 }
 
-template <bool GATE, bool XZW, bool ALIAS>
-__global__ void __launch_bounds__(FT, 4) blind_rotate_fast(const DevCtx P, const FastTables T, const GateIO io) {
+// MINB: gates the launch bounds promise per SM = the register budget (4: 64 registers, 3: 80, 2: 128).  The host picks the
+// largest MINB shared memory allows anyway, so party counts that fit fewer gates per SM get the registers the absent gates
+// would have used (no spills, longer load-to-use distances).
+template <bool GATE, bool XZW, bool ALIAS, int MINB>
+__global__ void __launch_bounds__(FT, MINB) blind_rotate_fast(const DevCtx P, const FastTables T, const GateIO io) {
     extern __shared__ __align__(16) uint32_t sm[];
     const uint32_t k = P.k, n = P.n, tid = threadIdx.x;
     constexpr uint32_t N = FN;
@@ -867,6 +870,9 @@ inline cudaError_t fast_blind_rotate(FastState& F, const DevCtx& d, bool gate, c
     };
     cudaError_t e;
     const int sel = (gate ? 4 : 0) | (xzw ? 2 : 0) | (alias ? 1 : 0);
+    int minb = G > 1 ? 1 : std::max(2, fast_gates_per_sm(smem));
+    if (const char* ev = getenv("MKFHE_MINB")) minb = std::min(4, std::max(2, atoi(ev)));
+    if (alias) minb = 4;  // the fallback layout is built for the 64-register budget only
     if (G > 1) {
         switch (sel) {
             case 0: e = launch(blind_rotate_grouped<false, false, false>); break;
@@ -878,17 +884,24 @@ inline cudaError_t fast_blind_rotate(FastState& F, const DevCtx& d, bool gate, c
             case 6: e = launch(blind_rotate_grouped<true, true, false>); break;
             default: e = launch(blind_rotate_grouped<true, true, true>); break;
         }
-    } else {
-        switch (sel) {
-            case 0: e = launch(blind_rotate_fast<false, false, false>); break;
-            case 1: e = launch(blind_rotate_fast<false, false, true>); break;
-            case 2: e = launch(blind_rotate_fast<false, true, false>); break;
-            case 3: e = launch(blind_rotate_fast<false, true, true>); break;
-            case 4: e = launch(blind_rotate_fast<true, false, false>); break;
-            case 5: e = launch(blind_rotate_fast<true, false, true>); break;
-            case 6: e = launch(blind_rotate_fast<true, true, false>); break;
-            default: e = launch(blind_rotate_fast<true, true, true>); break;
+    } else if (alias) {
+        switch (sel >> 1) {
+            case 0: e = launch(blind_rotate_fast<false, false, true, 4>); break;
+            case 1: e = launch(blind_rotate_fast<false, true, true, 4>); break;
+            case 2: e = launch(blind_rotate_fast<true, false, true, 4>); break;
+            default: e = launch(blind_rotate_fast<true, true, true, 4>); break;
         }
+    } else {
+#define MKFHE_LAUNCH_MINB(G_, X_)                                                      \
+    (minb >= 4 ? launch(blind_rotate_fast<G_, X_, false, 4>)                           \
+               : minb == 3 ? launch(blind_rotate_fast<G_, X_, false, 3>) : launch(blind_rotate_fast<G_, X_, false, 2>))
+        switch (sel >> 1) {
+            case 0: e = MKFHE_LAUNCH_MINB(false, false); break;
+            case 1: e = MKFHE_LAUNCH_MINB(false, true); break;
+            case 2: e = MKFHE_LAUNCH_MINB(true, false); break;
+            default: e = MKFHE_LAUNCH_MINB(true, true); break;
+        }
+#undef MKFHE_LAUNCH_MINB
     }
     if (e != cudaSuccess) return e;
     ++*launches;
