@@ -153,6 +153,22 @@ int mkfhe_last_gate_timing(mkfhe_ctx* ctx, float* rotate_ms, float* keyswitch_ms
 /* bytes of HBM held by this context (keys + tables + workspaces) */
 uint64_t mkfhe_device_bytes(const mkfhe_ctx* ctx);
 /* build-time identity: "mkfhe_b200 <version> sm_100a" */
+/* Bootstrapping-key generation on the GPU with the randomness supplied by the caller.  Replaces
+ * UniEncAccumulatorXZW{,_B}::KeyGenAcc -> KeyGenXZW / KDMKeyGenXZW (mk-acc-xzw.cpp:38-87,132-228; mk-acc-xzw_B.cpp:40-102) for a
+ * host that samples (r, e0, e1) itself -- the reference samples inside KeyGenXZW (GetDggR / GetDgg) and its MKKeyGen is
+ * clock-seeded, so bit-exact parity is defined on identical randomness.
+ *   sinv [k][N]  : f_u^-1, EVALUATION (invskNTT, binfhe-base-scheme.cpp:214-229)      crs [ell][N]: EVALUATION
+ *   r [E][N], e [E][ell][2][N] (e[.][j][0] = noise of d_j, [1] = noise of f_j): coefficient-domain residues in [0, Q)
+ *   m [E]        : encrypted bit per evk (s == 1 for evk+, s == q-1 for evk-, 1 for evk*: mk-acc-xzw.cpp:61-84)
+ *   E = k*S*n + 1 evks in the mkfhe_load_bk order [u][s][i] then evk*; (u, i) = (0, 0) and evk* are KDM encryptions.
+ * bk_out (may be NULL when load != 0): mkfhe_load_bk layout, plain residues.  load != 0: also install it in ctx.
+ * All pointers: host or device memory. */
+int mkfhe_keygen_bk(mkfhe_ctx* ctx, const uint32_t* sinv, const uint32_t* crs, const uint32_t* r, const uint32_t* e,
+                    const uint8_t* m, uint32_t* bk_out, int load);
+/* Pkey[u][j] = NTT(e_j) - CRS_j * f_u (binfhe-base-scheme.cpp:250-269).  s [k][N]: f_u EVALUATION; e [k][ell][N] coefficient
+ * residues; pkey_out: mkfhe_load_pkey layout (may be NULL when load != 0). */
+int mkfhe_keygen_pkey(mkfhe_ctx* ctx, const uint32_t* s, const uint32_t* crs, const uint32_t* e, uint32_t* pkey_out, int load);
+
 const char* mkfhe_version(void);
 /* INT32 pipe micro-benchmark (dependent IMAD chains on every SM): returns thread-level IMAD/s in *imad_per_s.
  * Used by bench.py as the denominator of the integer roofline (SURVEY.md section 8d asks for a measured peak). */

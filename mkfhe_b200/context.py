@@ -317,3 +317,29 @@ class BinFHEContext:
         v = C.c_double(0)
         self._ck(self._L.mkfhe_measure_butterfly_peak(self._h, C.byref(v)), "mkfhe_measure_butterfly_peak")
         return float(v.value)
+
+    # -- key generation with caller-supplied randomness (UniEncAccumulatorXZW{,_B}::KeyGenAcc, mk-acc-xzw.cpp:38-87,132-228;
+    #    Pkey: binfhe-base-scheme.cpp:250-269).  Host numpy arrays in, host numpy arrays out; load=True also installs the keys.
+    def KeyGenAcc(self, sinv, crs, r, e, m, load: bool = False):
+        P = self.params
+        ell = P.digitsG - 1
+        S = 2 if P.variant == 0 else 1
+        E = P.k * S * P.n + 1
+        u32 = lambda a, shape: np.ascontiguousarray(a, dtype=np.uint32).reshape(shape)
+        sinv, crs = u32(sinv, (P.k, P.N)), u32(crs, (ell, P.N))
+        r, e = u32(r, (E, P.N)), u32(e, (E, ell, 2, P.N))
+        m = np.ascontiguousarray(m, dtype=np.uint8).reshape(E)
+        out = np.empty((E, ell, 2, P.N), dtype=np.uint32)
+        self._ck(self._L.mkfhe_keygen_bk(self._h, _ptr(sinv)[0], _ptr(crs)[0], _ptr(r)[0], _ptr(e)[0],
+                                         C.c_void_p(m.ctypes.data), _ptr(out)[0], int(load)), "mkfhe_keygen_bk")
+        return out.reshape(-1)
+
+    def KeyGenPkey(self, s, crs, e, load: bool = False):
+        P = self.params
+        ell = P.digitsG - 1
+        u32 = lambda a, shape: np.ascontiguousarray(a, dtype=np.uint32).reshape(shape)
+        s, crs, e = u32(s, (P.k, P.N)), u32(crs, (ell, P.N)), u32(e, (P.k, ell, P.N))
+        out = np.empty((P.k, ell, P.N), dtype=np.uint32)
+        self._ck(self._L.mkfhe_keygen_pkey(self._h, _ptr(s)[0], _ptr(crs)[0], _ptr(e)[0], _ptr(out)[0], int(load)),
+                 "mkfhe_keygen_pkey")
+        return out.reshape(-1)

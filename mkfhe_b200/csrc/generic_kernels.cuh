@@ -564,6 +564,70 @@ __global__ void __launch_bounds__(256) decrypt_batch(const DevCtx P, const uint3
     }
 }
 
+// ---- bootstrapping-key generation with caller-supplied randomness ----
+// One CTA per uni-encryption evk, in the boundary order [u][s][i] + evk*:  KeyGenXZW (mk-acc-xzw.cpp:132-186, identical in
+// mk-acc-xzw_B.cpp) and, for (u, i) = (0, 0) and evk*, KDMKeyGenXZW (:188-228), as KeyGenAcc selects them (:61-84):
+//   f_j = (NTT(e1_j) + g_j NTT(r)) s_inv,   d_j = NTT(e0_j) + [m] g_j (s_inv if KDM) + R[j] CRS_j,   g_j = B^(j+1)
+// ("skrPoly[i] * CRS[i]" in the reference multiplies by the scalar slot j of R = NTT(r); restated as written).
+// sinv_m, crs_m: Montgomery form.  r [E][N], e [E][ell][2][N]: coefficient residues.  out [E][ell][2][N] plain residues.
+// Shared memory: (1 + 2 ell) N words.
+struct GadgetPow {
+    uint32_t plain[8], mont[8];  // B^(j+1) mod Q, and the same times 2^32
+};
+__global__ void keygen_bk_kernel(const DevCtx P, const GadgetPow G, const uint32_t* __restrict__ sinv_m, const uint32_t* __restrict__ crs_m,
+                                 const uint32_t* __restrict__ r, const uint32_t* __restrict__ e, const uint8_t* __restrict__ m,
+                                 uint32_t* __restrict__ out) {
+    extern __shared__ uint32_t sm[];
+    const uint32_t N = P.N, Q = P.mod.Q, ell = P.ell, n = P.n;
+    const uint32_t ev = blockIdx.x, last = gridDim.x - 1;
+    uint32_t u = 0;
+    bool kdm = true;
+    if (ev != last) {
+        u = ev / (P.S * n);
+        const uint32_t i = (ev - u * P.S * n) % n;
+        kdm = (u == 0 && i == 0);
+    }
+    const uint32_t* rr = r + size_t(ev) * N;
+    const uint32_t* ee = e + size_t(ev) * 2 * ell * N;
+    for (uint32_t x = threadIdx.x; x < N; x += blockDim.x) sm[x] = rr[x];
+    for (uint32_t x = threadIdx.x; x < 2 * ell * N; x += blockDim.x) sm[N + x] = ee[x];
+    __syncthreads();
+    ntt_fwd_smem(sm, 1 + 2 * ell, P);
+    const uint32_t* R = sm;
+    const uint32_t* sv = sinv_m + size_t(u) * N;
+    const bool msg = m[ev] != 0;
+    uint32_t* o = out + size_t(ev) * 2 * ell * N;
+    for (uint32_t j = 0; j < ell; ++j) {
+        const uint32_t* D = sm + N + size_t(2 * j) * N;
+        const uint32_t* F = D + N;
+        const uint32_t Rj = R[j];
+        for (uint32_t x = threadIdx.x; x < N; x += blockDim.x) {
+            const uint32_t s = sv[x];
+            const uint32_t f = montmul(addmod(F[x], montmul(R[x], G.mont[j], P.mod), Q), s, P.mod);
+            uint32_t d = D[x];
+            if (msg) d = addmod(d, kdm ? montmul(G.plain[j], s, P.mod) : G.plain[j], Q);
+            d = addmod(d, montmul(Rj, crs_m[size_t(j) * N + x], P.mod), Q);
+            o[size_t(2 * j) * N + x] = d;
+            o[size_t(2 * j + 1) * N + x] = f;
+        }
+    }
+}
+// Pkey[u][j] = NTT(e_j) - CRS_j f_u (binfhe-base-scheme.cpp:250-269).  One CTA per party; s_m, crs_m Montgomery form.
+__global__ void keygen_pkey_kernel(const DevCtx P, const uint32_t* __restrict__ s_m, const uint32_t* __restrict__ crs_m,
+                                   const uint32_t* __restrict__ e, uint32_t* __restrict__ out) {
+    extern __shared__ uint32_t sm[];
+    const uint32_t N = P.N, Q = P.mod.Q, ell = P.ell, u = blockIdx.x;
+    for (uint32_t x = threadIdx.x; x < ell * N; x += blockDim.x) sm[x] = e[size_t(u) * ell * N + x];
+    __syncthreads();
+    ntt_fwd_smem(sm, ell, P);
+    for (uint32_t x = threadIdx.x; x < ell * N; x += blockDim.x) {
+        const uint32_t c = crs_m[x], s = s_m[size_t(u) * N + (x & (N - 1))];
+        // CRS_j * f_u: one operand must be plain for montmul to return the plain product -> strip the factor from c
+        const uint32_t c_plain = montmul(c, 1u, P.mod);
+        out[size_t(u) * ell * N + x] = submod(sm[x], montmul(c_plain, s, P.mod), Q);
+    }
+}
+
 // ---- INT32 pipe micro-benchmark: 8 independent dependent-IMAD chains per thread ----
 __global__ void int32_peak_kernel(uint32_t* sink, uint32_t iters, uint32_t seed) {
     uint32_t a0 = seed + threadIdx.x, a1 = a0 ^ 0x9e3779b9u, a2 = a0 * 3u, a3 = a0 + 17u;

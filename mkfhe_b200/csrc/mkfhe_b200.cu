@@ -161,6 +161,19 @@ static int upload_ksk16(mkfhe_ctx* ctx, const uint32_t* src, uint64_t words, con
     return MKFHE_OK;
 }
 
+namespace {
+struct TmpBuf {  // device scratch of one call, freed on every exit path
+    std::vector<void*> p;
+    ~TmpBuf() { for (void* x : p) cudaFree(x); }
+    template <class T>
+    cudaError_t get(T** out, size_t count) {
+        cudaError_t e = cudaMalloc(reinterpret_cast<void**>(out), count * sizeof(T));
+        if (e == cudaSuccess) p.push_back(*out);
+        return e;
+    }
+};
+}  // namespace
+
 extern "C" {
 
 const char* mkfhe_version(void) { return MKFHE_VERSION_STR; }
@@ -603,6 +616,78 @@ int mkfhe_decompose(mkfhe_ctx* ctx, const uint32_t* polys, uint32_t* out, uint64
     CU(cudaGetLastError());
     CU(cudaMemcpyAsync(out, ctx->ws_io + w, w * ell * 4, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
+    return MKFHE_OK;
+}
+
+// ---- key generation with caller-supplied randomness ----
+
+int mkfhe_keygen_bk(mkfhe_ctx* ctx, const uint32_t* sinv, const uint32_t* crs, const uint32_t* r, const uint32_t* e, const uint8_t* m,
+                    uint32_t* bk_out, int load) {
+    if (!ctx || !sinv || !crs || !r || !e || !m || (!bk_out && !load)) return MKFHE_EINVAL;
+    const mkfhe_params& p = ctx->p;
+    const uint32_t N = p.N, ell = p.digitsG - 1, Q = p.Q;
+    if (ell > 8) return fail(ctx, MKFHE_EINVAL, "mkfhe_keygen_bk: at most 8 gadget digits");
+    const size_t S = p.variant == MKFHE_VARIANT_XZW ? 2 : 1, E = size_t(p.k) * S * p.n + 1, words = bk_words(p);
+    const size_t smem = size_t(1 + 2 * ell) * N * 4;
+    CU(cudaSetDevice(ctx->device));
+    TmpBuf tmp;
+    uint32_t *d_sinv, *d_crs, *d_r, *d_e, *d_out;
+    uint8_t* d_m;
+    CU(tmp.get(&d_sinv, size_t(p.k) * N));
+    CU(tmp.get(&d_crs, size_t(ell) * N));
+    CU(tmp.get(&d_r, E * N));
+    CU(tmp.get(&d_e, words));
+    CU(tmp.get(&d_out, words));
+    CU(tmp.get(&d_m, E));
+    CU(cudaMemcpyAsync(d_sinv, sinv, size_t(p.k) * N * 4, cudaMemcpyDefault, ctx->stream));
+    CU(cudaMemcpyAsync(d_crs, crs, size_t(ell) * N * 4, cudaMemcpyDefault, ctx->stream));
+    CU(cudaMemcpyAsync(d_r, r, E * N * 4, cudaMemcpyDefault, ctx->stream));
+    CU(cudaMemcpyAsync(d_e, e, words * 4, cudaMemcpyDefault, ctx->stream));
+    CU(cudaMemcpyAsync(d_m, m, E, cudaMemcpyDefault, ctx->stream));
+    to_montgomery<<<unsigned((size_t(p.k) * N + 255) / 256), 256, 0, ctx->stream>>>(d_sinv, d_sinv, size_t(p.k) * N, ctx->d.mod, ctx->r2);
+    to_montgomery<<<unsigned((size_t(ell) * N + 255) / 256), 256, 0, ctx->stream>>>(d_crs, d_crs, size_t(ell) * N, ctx->d.mod, ctx->r2);
+    GadgetPow G{};
+    const uint32_t R = uint32_t((uint64_t(1) << 32) % Q);
+    uint32_t g = 1;
+    for (uint32_t j = 0; j < ell; ++j) {
+        g = h_mulmod(g, (1u << p.baseG_log2) % Q, Q);
+        G.plain[j] = g;
+        G.mont[j] = h_mulmod(g, R, Q);
+    }
+    CU(cudaFuncSetAttribute(keygen_bk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    keygen_bk_kernel<<<unsigned(E), 256, smem, ctx->stream>>>(ctx->d, G, d_sinv, d_crs, d_r, d_e, d_m, d_out);
+    ctx->launches += 3;
+    CU(cudaGetLastError());
+    if (bk_out) CU(cudaMemcpyAsync(bk_out, d_out, words * 4, cudaMemcpyDefault, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    if (load) return mkfhe_load_bk(ctx, d_out, words);  // device source: converted and re-laid out on the device
+    return MKFHE_OK;
+}
+
+int mkfhe_keygen_pkey(mkfhe_ctx* ctx, const uint32_t* s, const uint32_t* crs, const uint32_t* e, uint32_t* pkey_out, int load) {
+    if (!ctx || !s || !crs || !e || (!pkey_out && !load)) return MKFHE_EINVAL;
+    const mkfhe_params& p = ctx->p;
+    const uint32_t N = p.N, ell = p.digitsG - 1;
+    const size_t words = size_t(p.k) * ell * N, smem = size_t(ell) * N * 4;
+    CU(cudaSetDevice(ctx->device));
+    TmpBuf tmp;
+    uint32_t *d_s, *d_crs, *d_e, *d_out;
+    CU(tmp.get(&d_s, size_t(p.k) * N));
+    CU(tmp.get(&d_crs, size_t(ell) * N));
+    CU(tmp.get(&d_e, words));
+    CU(tmp.get(&d_out, words));
+    CU(cudaMemcpyAsync(d_s, s, size_t(p.k) * N * 4, cudaMemcpyDefault, ctx->stream));
+    CU(cudaMemcpyAsync(d_crs, crs, size_t(ell) * N * 4, cudaMemcpyDefault, ctx->stream));
+    CU(cudaMemcpyAsync(d_e, e, words * 4, cudaMemcpyDefault, ctx->stream));
+    to_montgomery<<<unsigned((size_t(p.k) * N + 255) / 256), 256, 0, ctx->stream>>>(d_s, d_s, size_t(p.k) * N, ctx->d.mod, ctx->r2);
+    to_montgomery<<<unsigned((size_t(ell) * N + 255) / 256), 256, 0, ctx->stream>>>(d_crs, d_crs, size_t(ell) * N, ctx->d.mod, ctx->r2);
+    CU(cudaFuncSetAttribute(keygen_pkey_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+    keygen_pkey_kernel<<<p.k, 256, smem, ctx->stream>>>(ctx->d, d_s, d_crs, d_e, d_out);
+    ctx->launches += 3;
+    CU(cudaGetLastError());
+    if (pkey_out) CU(cudaMemcpyAsync(pkey_out, d_out, words * 4, cudaMemcpyDefault, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    if (load) return mkfhe_load_pkey(ctx, d_out, words);
     return MKFHE_OK;
 }
 

@@ -417,6 +417,48 @@ void orc_eval_nand(const orc_ctx* c, const uint32_t* bk, const uint32_t* pkey, c
 }
 
 /* ---------- decryption ---------- */
+/* ---------- key generation with the randomness as an input ----------
+ * One uni-encryption evk = (d_j, f_j), j < ell, of the bit m under party secret s (s_inv = its inverse, EVALUATION):
+ *   KeyGenXZW    mk-acc-xzw.cpp:132-186 (== mk-acc-xzw_B.cpp KeyGenXZW):  f_j = (NTT(e1_j) + g_j * R) * s_inv
+ *                                                                         d_j = NTT(e0_j) + [m] g_j + R[j] * CRS_j
+ *   KDMKeyGenXZW mk-acc-xzw.cpp:188-228:                                  d_j = NTT(e0_j) + [m] g_j * s_inv + R[j] * CRS_j
+ * with g_j = B^(j+1) (Gpower[j+1]), R = NTT(r), and -- as written in the reference -- "skrPoly[i] * CRS[i]" multiplying
+ * CRS_j by the SCALAR R[j] (slot j of R), not by the polynomial r.  r, e: coefficient-domain residues in [0, Q).
+ * e layout [ell][2][N]: e[j][0] = noise of d_j (sampled first), e[j][1] = noise of f_j.  out layout [ell][2][N] (d | f). */
+void orc_keygen_evk(const orc_ctx* c, const uint32_t* sinv, const uint32_t* crs, const uint32_t* r, const uint32_t* e, int m,
+                    int kdm, uint32_t* out) {
+    const uint32_t N = c->p.N, Q = c->p.Q, ell = c->ell;
+    uint32_t* R = (uint32_t*)malloc(sizeof(uint32_t) * N);
+    memcpy(R, r, sizeof(uint32_t) * N);
+    orc_ntt(c, R, 0);
+    uint32_t g = 1;
+    for (uint32_t j = 0; j < ell; ++j) {
+        g = mulmod(g, 1u << c->p.baseG_log2, Q);
+        uint32_t* d = out + (size_t)(2 * j) * N;
+        uint32_t* f = d + N;
+        memcpy(d, e + (size_t)(2 * j) * N, sizeof(uint32_t) * N);
+        memcpy(f, e + (size_t)(2 * j + 1) * N, sizeof(uint32_t) * N);
+        orc_ntt(c, d, 0);
+        orc_ntt(c, f, 0);
+        for (uint32_t x = 0; x < N; ++x) {
+            f[x] = mulmod(addmod(f[x], mulmod(g, R[x], Q), Q), sinv[x], Q);
+            if (m) d[x] = addmod(d[x], kdm ? mulmod(g, sinv[x], Q) : g, Q);
+            d[x] = addmod(d[x], mulmod(R[j], crs[(size_t)j * N + x], Q), Q);
+        }
+    }
+    free(R);
+}
+/* Pkey[u][j] = NTT(e_j) - CRS_j * f_u  (binfhe-base-scheme.cpp:250-269); s = f_u in EVALUATION form; e, out: [ell][N] */
+void orc_keygen_pkey(const orc_ctx* c, const uint32_t* s, const uint32_t* crs, const uint32_t* e, uint32_t* out) {
+    const uint32_t N = c->p.N, Q = c->p.Q;
+    for (uint32_t j = 0; j < c->ell; ++j) {
+        uint32_t* o = out + (size_t)j * N;
+        memcpy(o, e + (size_t)j * N, sizeof(uint32_t) * N);
+        orc_ntt(c, o, 0);
+        for (uint32_t x = 0; x < N; ++x) o[x] = submod(o[x], mulmod(crs[(size_t)j * N + x], s[x], Q), Q);
+    }
+}
+
 int orc_decrypt(const orc_ctx* c, const uint32_t* sk, const uint32_t* ct, uint32_t b) {
     const uint32_t k = c->p.k, n = c->p.n, q = c->p.q, p = 4;
     uint32_t inner = 0;

@@ -68,6 +68,12 @@ void orc_keyswitch_mklwe(const orc_ctx* c, const uint32_t* kskA, const uint32_t*
 /* decryption with exported secret material (mntru-pke.cpp:306-357 with F_col0 [k][n]; mklwe-pke.cpp Decrypt with s [k][n]) */
 int orc_decrypt(const orc_ctx* c, const uint32_t* sk, const uint32_t* ct, uint32_t b);
 
+/* key generation with the randomness supplied by the caller (mk-acc-xzw.cpp:132-228, binfhe-base-scheme.cpp:250-269);
+ * layouts in mkfhe_oracle.c */
+void orc_keygen_evk(const orc_ctx* c, const uint32_t* sinv, const uint32_t* crs, const uint32_t* r, const uint32_t* e, int m,
+                    int kdm, uint32_t* out);
+void orc_keygen_pkey(const orc_ctx* c, const uint32_t* s, const uint32_t* crs, const uint32_t* e, uint32_t* out);
+
 /* CPU baseline helper: run `gates` NAND bootstraps over `threads` pthreads (same inputs each), return wall seconds */
 double orc_bench_gates(const orc_ctx* c, const uint32_t* bk, const uint32_t* pkey, const uint32_t* kskA, const uint32_t* kskB,
                        const uint32_t* ctnand, const uint32_t* ct1, uint32_t b1, const uint32_t* ct2, uint32_t b2,

@@ -61,6 +61,8 @@ def lib():
         L.orc_keyswitch_mklwe.argtypes = [C.c_void_p, U32P, U32P, U32P, C.c_uint32, U32P, U32P]
         L.orc_decrypt.restype = C.c_int
         L.orc_decrypt.argtypes = [C.c_void_p, U32P, U32P, C.c_uint32]
+        L.orc_keygen_evk.argtypes = [C.c_void_p, U32P, U32P, U32P, U32P, C.c_int, C.c_int, U32P]
+        L.orc_keygen_pkey.argtypes = [C.c_void_p, U32P, U32P, U32P, U32P]
         L.orc_bench_gates.restype = C.c_double
         L.orc_bench_gates.argtypes = [C.c_void_p, U32P, U32P, U32P, U32P, U32P, U32P, C.c_uint32, U32P, C.c_uint32,
                                       C.c_uint32, C.c_uint32]
@@ -151,6 +153,17 @@ class Oracle:
 
     def decrypt(self, sk, ct, b=0) -> int:
         return int(self.L.orc_decrypt(self.h, _p(_c(sk)), _p(_c(ct)), int(b)))
+
+    def keygen_evk(self, sinv, crs, r, e, m: int, kdm: bool):
+        """One evk [ell][2][N] from the randomness r [N], e [ell][2][N] (coefficient residues): KeyGenXZW / KDMKeyGenXZW."""
+        out = np.zeros((self.ell, 2, self.N), dtype=np.uint32)
+        self.L.orc_keygen_evk(self.h, _p(_c(sinv)), _p(_c(crs)), _p(_c(r)), _p(_c(e)), int(m), int(bool(kdm)), _p(out))
+        return out
+
+    def keygen_pkey(self, s, crs, e):
+        out = np.zeros((self.ell, self.N), dtype=np.uint32)
+        self.L.orc_keygen_pkey(self.h, _p(_c(s)), _p(_c(crs)), _p(_c(e)), _p(out))
+        return out
 
     def bench_gates(self, bk, pkey, kskA, kskB, ctnand, ct1, b1, ct2, b2, gates, threads) -> float:
         return float(self.L.orc_bench_gates(self.h, _p(_c(bk)), _p(_c(pkey)), _p(_c(kskA)), _p(_c(kskB)), _p(_c(ctnand)),

@@ -255,6 +255,27 @@ int ref_export_sk(void* h, uint32_t* out) {
     });
 }
 
+// Uni-encryption secrets f_u in EVALUATION form [k][N] (UniEncBTKey::f, binfhe-base-scheme.cpp:229) and the common reference
+// string CRS [ell][N] (EVALUATION, mk-cryptoparameters.h): the inputs of KeyGenAcc / Pkey generation besides the randomness.
+// Used by the key-generation parity tests to recover the randomness the reference sampled (it is not exposed otherwise).
+int ref_export_unienc_sk(void* h, uint32_t* out) {
+    auto* c = static_cast<RefCtx*>(h);
+    return guarded(c, [&] {
+        for (uint32_t u = 0; u < c->k; ++u) put(out + size_t(u) * c->N, c->ek.f[u]);
+    });
+}
+int ref_export_crs(void* h, uint32_t* out) {
+    auto* c = static_cast<RefCtx*>(h);
+    return guarded(c, [&] {
+        const auto& crs = c->unienc->GetCRS();
+        for (uint32_t j = 0; j + 1 < c->digitsG; ++j) {
+            NativePoly p = crs[j];
+            p.SetFormat(Format::EVALUATION);
+            put(out + size_t(j) * c->N, p);
+        }
+    });
+}
+
 // ---- encrypt / decrypt (reference code) ----
 int ref_encrypt(void* h, int m, uint32_t* ct, uint32_t* b) {
     auto* c = static_cast<RefCtx*>(h);

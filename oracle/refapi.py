@@ -41,7 +41,7 @@ def lib():
         L.ref_keygen.argtypes = [C.c_void_p]
         L.ref_bk_words.restype = C.c_uint64
         L.ref_bk_words.argtypes = [C.c_void_p]
-        for name in ("ref_export_bk", "ref_export_pkey", "ref_export_ctnand", "ref_export_sk"):
+        for name in ("ref_export_bk", "ref_export_pkey", "ref_export_ctnand", "ref_export_sk", "ref_export_unienc_sk", "ref_export_crs"):
             getattr(L, name).argtypes = [C.c_void_p, U32P]
         L.ref_export_ksk_mntru.argtypes = [C.c_void_p, U32P, C.POINTER(C.c_uint64)]
         L.ref_export_ksk_mklwe.argtypes = [C.c_void_p, U32P, U32P]
@@ -164,6 +164,18 @@ class Ref:
         a = np.zeros(self.p.k * self.p.n, dtype=np.uint32)
         self._ck(self.L.ref_export_sk(self.h, _p(a)), "ref_export_sk")
         return a
+
+    def unienc_sk(self) -> np.ndarray:
+        """f_u in EVALUATION form, [k][N] (UniEncBTKey::f)."""
+        a = np.zeros(self.p.k * self.p.N, dtype=np.uint32)
+        self._ck(self.L.ref_export_unienc_sk(self.h, _p(a)), "ref_export_unienc_sk")
+        return a.reshape(self.p.k, self.p.N)
+
+    def crs(self) -> np.ndarray:
+        """CRS in EVALUATION form, [ell][N]."""
+        a = np.zeros(self.p.ell * self.p.N, dtype=np.uint32)
+        self._ck(self.L.ref_export_crs(self.h, _p(a)), "ref_export_crs")
+        return a.reshape(self.p.ell, self.p.N)
 
     # ---- scheme ops ----
     def encrypt(self, m: int):

@@ -1,0 +1,99 @@
+"""Key-generation parity helpers (test infrastructure).
+
+The reference's MKKeyGen samples its randomness internally (clock-seeded) and does not expose it.  It can be
+recovered exactly from the keys it produced together with the secrets: with s = f_u (EVALUATION) and g_j = B^(j+1),
+    f_j * s            = NTT(e1_j) + g_j * NTT(r)      ->  r = round(centred(INTT(f_0 s)) / B),  e1_j = the rest
+    d_j - R[j] CRS_j - [m] g_j (* s_inv if KDM) = NTT(e0_j)                       (m is the one that leaves a small e0_j)
+    Pkey_j + CRS_j s   = NTT(e_j)
+(mk-acc-xzw.cpp:132-228, binfhe-base-scheme.cpp:250-269).  Feeding the recovered randomness to a key generator must give the
+reference's key bytes back, which pins the generator's formulas, transform ordering and layouts against the reference.
+"""
+import numpy as np
+
+
+def slot_inverse(f, Q):
+    return np.array([[pow(int(x), Q - 2, Q) for x in row] for row in f], dtype=np.uint32)
+
+
+def evk_index(p, e):
+    """evk number e of the boundary layout [u][s][i] + evk*  ->  (u, s, i, kdm)."""
+    S = 2 if p.variant == 0 else 1
+    E = p.k * S * p.n + 1
+    if e == E - 1:
+        return 0, 0, p.n, True
+    u, rem = divmod(e, S * p.n)
+    s, i = divmod(rem, p.n)
+    return u, s, i, (u == 0 and i == 0)
+
+
+def extract_randomness(p, o, bk, pkey, f, crs, small=64):
+    """Returns dict(r [E][N], e [E][ell][2][N], m [E], kdm [E], party [E], pk_e [k][ell][N]) as uint32 residues mod Q."""
+    Q, N, ell = p.Q, p.N, p.digitsG - 1
+    B = 1 << p.baseG_log2
+    bk = np.asarray(bk, dtype=np.uint32).reshape(-1, ell, 2, N).astype(np.int64)
+    pkey = np.asarray(pkey, dtype=np.uint32).reshape(p.k, ell, N).astype(np.int64)
+    f = np.asarray(f, dtype=np.uint32).reshape(p.k, N).astype(np.int64)
+    crs = np.asarray(crs, dtype=np.uint32).reshape(ell, N).astype(np.int64)
+    inv = slot_inverse(f, Q).astype(np.int64)
+    E = bk.shape[0]
+
+    def intt(x):
+        return o.ntt(np.asarray(x % Q, dtype=np.uint32), True).astype(np.int64)
+
+    def ntt(x):
+        return o.ntt(np.asarray(x % Q, dtype=np.uint32), False).astype(np.int64)
+
+    def cen(x):
+        x = x % Q
+        return np.where(x > Q // 2, x - Q, x)
+
+    out = dict(r=np.zeros((E, N), np.uint32), e=np.zeros((E, ell, 2, N), np.uint32), m=np.zeros(E, np.uint8),
+               kdm=np.zeros(E, np.uint8), party=np.zeros(E, np.uint32), pk_e=np.zeros((p.k, ell, N), np.uint32))
+    for e in range(E):
+        u, _, _, kdm = evk_index(p, e)
+        c = [cen(intt(bk[e, j, 1] * f[u] % Q)) for j in range(ell)]
+        rr = np.rint(c[0] / B).astype(np.int64)
+        R = ntt(rr)
+        g = 1
+        for j in range(ell):
+            g = g * B % Q
+            e1 = c[j] - g * rr
+            assert np.abs(e1).max() < small, "f-noise not small: wrong secret or layout"
+            out["e"][e, j, 1] = (e1 % Q).astype(np.uint32)
+        found = None
+        for m in (0, 1):
+            e0s, g = [], 1
+            for j in range(ell):
+                g = g * B % Q
+                d = bk[e, j, 0] - R[j] * crs[j]
+                if m:
+                    d = d - (g * inv[u] if kdm else g)
+                e0s.append(cen(intt(d % Q)))
+            if max(np.abs(x).max() for x in e0s) < small:
+                found = (m, e0s)
+                break
+        assert found is not None, "d-noise not small for either message"
+        out["m"][e], out["kdm"][e], out["party"][e] = found[0], int(kdm), u
+        out["r"][e] = (rr % Q).astype(np.uint32)
+        for j in range(ell):
+            out["e"][e, j, 0] = (found[1][j] % Q).astype(np.uint32)
+    for u in range(p.k):
+        for j in range(ell):
+            ee = cen(intt((pkey[u, j] + crs[j] * f[u]) % Q))
+            assert np.abs(ee).max() < small
+            out["pk_e"][u, j] = (ee % Q).astype(np.uint32)
+    return out
+
+
+def expected_messages(p, sk):
+    """m per evk from the LWE secret as KeyGenAcc derives it (mk-acc-xzw.cpp:61-84, mk-acc-xzw_B.cpp:48-62)."""
+    S = 2 if p.variant == 0 else 1
+    sk = np.asarray(sk).reshape(p.k, p.n)
+    E = p.k * S * p.n + 1
+    m = np.zeros(E, np.uint8)
+    for e in range(E - 1):
+        u, s, i, _ = evk_index(p, e)
+        v = int(sk[u, i])
+        m[e] = int(v == 1) if s == 0 else int(v == p.qKS - 1)
+    m[E - 1] = 1
+    return m

@@ -118,3 +118,42 @@ def test_oracle_matches_compiled_reference_full_size_eval_acc_prefix():
     assert (o.ntt(x, False) == r.ntt(x, False)).all()
     assert (o.ntt(x, True) == r.ntt(x, True)).all()
     assert (o.decompose(x[0]) == r.decompose(x[0])).all()
+
+
+@pytest.mark.skipif(not refapi.available(), reason="oracle/_ref/libmkfhe_ref.so not present")
+@pytest.mark.parametrize("scheme", [0, 1])
+def test_oracle_keygen_reproduces_reference_keys(scheme):
+    """Key generation: the randomness recovered from the reference's keys + secrets, fed to the oracle's
+    restatement of KeyGenXZW / KDMKeyGenXZW / Pkey, gives the reference's key bytes back; the recovered messages are the ones
+    KeyGenAcc derives from the LWE secret."""
+    from keygen_util import expected_messages, extract_randomness, slot_inverse
+
+    r = refapi.Ref(0, 2, 27, 512, 8, 45181, 45181, 0.75, 32, 1 << 9, 32) if scheme == 0 else \
+        refapi.Ref(1, 3, 27, 128, 6, 32749, 32749, 1.9, 32, 1 << 7, 2)
+    r.keygen()
+    p = params_from_ref(r.p)
+    o = make_oracle(p)
+    bk, pkey, f, crs = r.bk(), r.pkey(), r.unienc_sk(), r.crs()
+    x = extract_randomness(p, o, bk, pkey, f, crs)
+    assert (x["m"] == expected_messages(p, r.sk())).all()
+    inv = slot_inverse(f, p.Q)
+    ell = p.digitsG - 1
+    ref_bk = bk.reshape(-1, ell, 2, p.N)
+    for e in range(ref_bk.shape[0]):
+        got = o.keygen_evk(inv[x["party"][e]], crs, x["r"][e], x["e"][e], int(x["m"][e]), bool(x["kdm"][e]))
+        assert (got == ref_bk[e]).all(), f"evk {e}"
+    ref_pk = pkey.reshape(p.k, ell, p.N)
+    for u in range(p.k):
+        assert (o.keygen_pkey(f[u], crs, x["pk_e"][u]) == ref_pk[u]).all()
+    # the r != 0 branch (the reference's DggR has sigma 0.15: r is 0 in practice): linearity in r of the restated formula
+    rng = np.random.default_rng(7)
+    rr = rng.integers(0, p.Q, p.N, dtype=np.uint32)
+    a = o.keygen_evk(inv[0], crs, rr, x["e"][0], 0, False).astype(np.int64)
+    b = o.keygen_evk(inv[0], crs, np.zeros(p.N, np.uint32), x["e"][0], 0, False).astype(np.int64)
+    R = o.ntt(rr, False).astype(np.int64)
+    g = 1
+    for j in range(ell):
+        g = g * (1 << p.baseG_log2) % p.Q
+        assert ((a[j, 1] - b[j, 1]) % p.Q == g * R % p.Q * inv[0].astype(np.int64) % p.Q).all()
+        assert ((a[j, 0] - b[j, 0]) % p.Q == R[j] * crs[j].astype(np.int64) % p.Q).all()
+    r.close()
