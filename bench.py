@@ -693,6 +693,107 @@ def run_ntt_arm(args):
     ctx.close()
 
 
+def run_keygen_arm(args):
+    """--workload keygen: bootstrapping-key generation for --paramset, randomness supplied (synthetic small
+    residues).  value = evks/s with inputs and output resident in HBM; e2e = the same through host buffers (H2D of the
+    randomness, D2H of the key).  cpu_baseline = the oracle's restatement of KeyGenXZW (one thread, bounded sample); the
+    reference's own KeyGenAcc for k = 2 takes 2.46 s on one core."""
+    import ctypes as C
+
+    import torch
+
+    import mkfhe_b200 as mk
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the GPU arm has no CPU fallback")
+    dev = torch.device("cuda", 0)
+    method = mk.MKNTRU_LWE if "LWE" in args.paramset else mk.MKNTRU
+    P = mk.derive_params(mk.PARAMSETS[args.paramset], method)
+    P.device = 0
+    ctx = mk.BinFHEContext().GenerateFromParams(P)
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    ctx.set_stream(stream.cuda_stream)
+    ell, N, Q = P.digitsG - 1, P.N, P.Q
+    S = 2 if P.variant == 0 else 1
+    E = P.k * S * P.n + 1
+    rng = np.random.default_rng(8)
+    small = lambda shape: (rng.integers(-3, 4, size=shape) % Q).astype(np.uint32)
+    sinv = rng.integers(1, Q, size=(P.k, N), dtype=np.uint32)
+    crs = rng.integers(0, Q, size=(ell, N), dtype=np.uint32)
+    r, e = small((E, N)), small((E, ell, 2, N))
+    m = rng.integers(0, 2, size=E, dtype=np.uint8)
+    out = np.empty((E, ell, 2, N), dtype=np.uint32)
+    t = lambda a: torch.from_numpy(a.view(np.int32) if a.dtype == np.uint32 else a).to(dev)
+    d_sinv, d_crs, d_r, d_e, d_m = t(sinv), t(crs), t(r), t(e), t(m)
+    d_out = torch.empty((E, ell, 2, N), dtype=torch.int32, device=dev)
+    L, h = ctx._L, ctx._h
+    vp = lambda x: C.c_void_p(x.data_ptr() if hasattr(x, "data_ptr") else x.ctypes.data)
+
+    def dev_call():
+        ctx._ck(L.mkfhe_keygen_bk(h, vp(d_sinv), vp(d_crs), vp(d_r), vp(d_e), vp(d_m), vp(d_out), 0), "mkfhe_keygen_bk")
+
+    def host_call():
+        ctx._ck(L.mkfhe_keygen_bk(h, vp(sinv), vp(crs), vp(r), vp(e), vp(m), vp(out), 0), "mkfhe_keygen_bk")
+
+    for _ in range(args.warmup):
+        dev_call()
+    sampler = ClockSampler(0)
+    sampler.start()
+    launches0 = ctx.launch_count()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    torch.cuda.synchronize()
+    ev[0].record(stream)
+    for _ in range(args.steps):
+        dev_call()
+    ev[1].record(stream)
+    ev[1].synchronize()
+    dev_ms = ev[0].elapsed_time(ev[1])
+    launches = ctx.launch_count() - launches0
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        host_call()
+    e2e_s = time.perf_counter() - t0
+    clocks = sampler.stop()
+    assert (d_out.cpu().numpy().view(np.uint32) == out).all()
+    # parity sample + CPU baseline: the oracle's restatement on one thread
+    o = make_oracle(P)
+    idx = [0, 1, E // 2, E - 1]
+    for i in idx:
+        u = 0 if i == E - 1 else i // (S * P.n)
+        kdm = i == E - 1 or (u == 0 and (i % P.n) == 0)
+        assert (out[i] == o.keygen_evk(sinv[u], crs, r[i], e[i], int(m[i]), kdm)).all(), "GPU evk differs from the oracle"
+    nb = min(E, 256)
+    t0 = time.perf_counter()
+    for i in range(nb):
+        o.keygen_evk(sinv[0], crs, r[i], e[i], int(m[i]), False)
+    cpu_s = time.perf_counter() - t0
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    step_s = dev_ms * 1e-3 / args.steps
+    bytes_step = E * (N + 2 * ell * N + 2 * ell * N) * 4  # r + e read, evk written (device-resident call also copies e, r once)
+    line = {"metric": "uni-encryption evaluation keys generated/sec", "value": E / step_s, "unit": "evks/s", "n_gpus": 1,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u32", "data": "synthetic randomness (small residues), uniform secrets / CRS",
+            "config": {"workload": f"{args.paramset} bootstrapping-key generation, {E} evks of {2 * ell * N * 4 >> 10} KiB",
+                       "paramset": args.paramset, "l2": f"key of {E * 2 * ell * N * 4 >> 20} MiB written per step"},
+            "e2e": {"value": E * args.steps / e2e_s, "unit": "evks/s", "h2d_bytes_per_step": int(E * (N + 2 * ell * N) * 4),
+                    "d2h_bytes_per_step": int(E * 2 * ell * N * 4)},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": "keygen_bk_kernel (+ staging copies)", "achieved": bytes_step / step_s / 1e9,
+                         "peak": hbm_peak, "unit": "GB/s", "frac": bytes_step / step_s / 1e9 / hbm_peak, "traffic": None,
+                         "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback 6650"},
+            "cpu_baseline": {"value": nb / cpu_s, "unit": "evks/s", "cores": 1, "kind": "port",
+                             "sample": f"{nb} evks through oracle/mkfhe_oracle.c orc_keygen_evk in {cpu_s:.2f}s"},
+            "oracle_checked": len(idx), "clocks": clocks}
+    emit(line)
+    ctx.close()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -707,7 +808,7 @@ def main():
     ap.add_argument("--synthetic-keys", action="store_true", help="uniform random key residues instead of the reference keygen "
                     "(throughput does not depend on key values; the reference's keygen takes minutes at k >= 8)")
     ap.add_argument("--check-oracle", type=int, default=0, help="gates to re-compute on the CPU oracle after the run")
-    ap.add_argument("--workload", default="gates", choices=["gates", "sharded", "ntt"],
+    ap.add_argument("--workload", default="gates", choices=["gates", "sharded", "ntt", "keygen"],
                     help="gates: configs[1]/[2] (batch per GPU); sharded: configs[3] (--total-gates split over the GPUs, "
                          "counter-based inputs); ntt: configs[4] (batched transform micro-benchmark)")
     ap.add_argument("--total-gates", type=int, default=1 << 17)
@@ -724,6 +825,8 @@ def main():
         run_sharded_arm(args)
     elif args.workload == "ntt":
         run_ntt_arm(args)
+    elif args.workload == "keygen":
+        run_keygen_arm(args)
     else:
         run_gpu_arm(args)
 
