@@ -169,6 +169,20 @@ int mkfhe_keygen_bk(mkfhe_ctx* ctx, const uint32_t* sinv, const uint32_t* crs, c
  * residues; pkey_out: mkfhe_load_pkey layout (may be NULL when load != 0). */
 int mkfhe_keygen_pkey(mkfhe_ctx* ctx, const uint32_t* s, const uint32_t* crs, const uint32_t* e, uint32_t* pkey_out, int load);
 
+/* Key-switch key generation on the GPU with the noise supplied by the caller (all values residues mod qKS).
+ * MNTRU: replaces MNTRUEncryptionScheme::KeySwitchGen2 (mntru-pke.cpp:624-760) for the independent digit-1 slice
+ *   (KSK2[u][j] = j * KSK2[u][1], :743-752):  ksk[u] = centred(E_u + gadget(s_u)) x centred(F_u^-1) mod qKS.
+ *   s_q [k][N]: uni-encryption secret coefficients after SwitchModulus(qKS) (:649); e [k][N*dKS][n] (the reference fills it
+ *   with copies of one sampled row per party, :646); finv [k][n][n] = sk->GetF_inv(), row-major; ksk_out [k][N*dKS][n] =
+ *   the mkfhe_load_ksk_mntru layout.
+ * MKLWE: replaces MKLWEEncryptionScheme::KeySwitchGen (mklwe-pke.cpp:176-256):
+ *   B[u][i][a0][j] = e + sN_q[u][i] * (a0 * baseKS^j) + <A[u][i][a0][j], s_u> mod qKS; A [k][N][baseKS][dKS][n] are the sampled
+ *   vectors (part of the key as they are), e [k][N][baseKS][dKS], s [k][n] the LWE secret; B_out: mkfhe_load_ksk_mklwe's B.
+ * load != 0 installs the key in ctx (outputs may then be NULL).  All pointers: host or device memory. */
+int mkfhe_keygen_ksk_mntru(mkfhe_ctx* ctx, const uint32_t* s_q, const uint32_t* e, const uint32_t* finv, uint32_t* ksk_out, int load);
+int mkfhe_keygen_ksk_mklwe(mkfhe_ctx* ctx, const uint32_t* A, const uint32_t* e, const uint32_t* s, const uint32_t* sN_q,
+                           uint32_t* B_out, int load);
+
 const char* mkfhe_version(void);
 /* INT32 pipe micro-benchmark (dependent IMAD chains on every SM): returns thread-level IMAD/s in *imad_per_s.
  * Used by bench.py as the denominator of the integer roofline (SURVEY.md section 8d asks for a measured peak). */

@@ -343,3 +343,24 @@ class BinFHEContext:
         self._ck(self._L.mkfhe_keygen_pkey(self._h, _ptr(s)[0], _ptr(crs)[0], _ptr(e)[0], _ptr(out)[0], int(load)),
                  "mkfhe_keygen_pkey")
         return out.reshape(-1)
+
+    # -- key-switch key generation with caller-supplied noise (mntru-pke.cpp:624-760 digit-1 slice; mklwe-pke.cpp:176-256)
+    def KeySwitchGen2(self, s_q, e, finv, load: bool = False):
+        P = self.params
+        L = P.N * P.dKS
+        u32 = lambda a, shape: np.ascontiguousarray(a, dtype=np.uint32).reshape(shape)
+        s_q, e, finv = u32(s_q, (P.k, P.N)), u32(e, (P.k, L, P.n)), u32(finv, (P.k, P.n, P.n))
+        out = np.empty((P.k, L, P.n), dtype=np.uint32)
+        self._ck(self._L.mkfhe_keygen_ksk_mntru(self._h, _ptr(s_q)[0], _ptr(e)[0], _ptr(finv)[0], _ptr(out)[0], int(load)),
+                 "mkfhe_keygen_ksk_mntru")
+        return out.reshape(-1)
+
+    def KeySwitchGenLWE(self, A, e, s, sN_q, load: bool = False):
+        P = self.params
+        rows = P.k * P.N * P.baseKS * P.dKS
+        u32 = lambda a, shape: np.ascontiguousarray(a, dtype=np.uint32).reshape(shape)
+        A, e, s, sN_q = u32(A, (rows, P.n)), u32(e, (rows,)), u32(s, (P.k, P.n)), u32(sN_q, (P.k, P.N))
+        out = np.empty(rows, dtype=np.uint32)
+        self._ck(self._L.mkfhe_keygen_ksk_mklwe(self._h, _ptr(A)[0], _ptr(e)[0], _ptr(s)[0], _ptr(sN_q)[0], _ptr(out)[0],
+                                                int(load)), "mkfhe_keygen_ksk_mklwe")
+        return out

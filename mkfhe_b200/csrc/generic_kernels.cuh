@@ -628,6 +628,91 @@ __global__ void keygen_pkey_kernel(const DevCtx P, const uint32_t* __restrict__ 
     }
 }
 
+// ---- key-switch key generation with caller-supplied noise ----
+__device__ __forceinline__ int32_t centre_q(uint32_t v, uint32_t q) { return v > q / 2 ? int32_t(v) - int32_t(q) : int32_t(v); }
+// MNTRU KeySwitchGen2, digit-1 slice (mntru-pke.cpp:624-760): out[u] = centred(E + gadget(s_u)) x centred(F_u^-1) mod qKS,
+// an [N dKS x n] x [n x n] integer product per party, exact in 64 bits (|terms| < 2^30, n of them), reduced once (mod_q,
+// :408-418).  gadget(s) adds s_i baseKS^j to column 0 of row i dKS + j (:652-671).  64 x 64 tile per CTA, 4 x 4 per thread.
+__global__ void __launch_bounds__(256) keygen_ksk_mntru_kernel(const DevCtx P, const uint32_t* __restrict__ s_q,
+                                                               const uint32_t* __restrict__ e, const uint32_t* __restrict__ finv,
+                                                               uint32_t* __restrict__ out) {
+    __shared__ int32_t Gs[32][64 + 1];  // [x][row]
+    __shared__ int32_t Fs[32][64];      // [x][col]
+    const uint32_t u = blockIdx.z, l0 = blockIdx.y * 64, y0 = blockIdx.x * 64;
+    const uint32_t tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    const uint32_t L = P.N * P.dKS, n = P.n, q = P.qKS;
+    long long acc[4][4] = {};
+    for (uint32_t x0 = 0; x0 < n; x0 += 32) {
+        for (uint32_t t = threadIdx.x; t < 32 * 64; t += 256) {
+            const uint32_t rl = t >> 5, xl = t & 31, l = l0 + rl, x = x0 + xl;
+            int32_t g = 0;
+            if (l < L && x < n) {
+                uint32_t v = e[(size_t(u) * L + l) * n + x] % q;
+                if (x == 0) {
+                    const uint32_t i = l / P.dKS;
+                    uint32_t pw = s_q[size_t(u) * P.N + i] % q;
+                    for (uint32_t j = l - i * P.dKS; j > 0; --j) pw = uint32_t((uint64_t(pw) * (P.baseKS % q)) % q);
+                    v = addmod(v, pw, q);
+                }
+                g = centre_q(v, q);
+            }
+            Gs[xl][rl] = g;
+        }
+        for (uint32_t t = threadIdx.x; t < 32 * 64; t += 256) {
+            const uint32_t xl = t >> 6, yl = t & 63, x = x0 + xl, y = y0 + yl;
+            Fs[xl][yl] = (x < n && y < n) ? centre_q(finv[(size_t(u) * n + x) * n + y] % q, q) : 0;
+        }
+        __syncthreads();
+#pragma unroll 8
+        for (uint32_t xl = 0; xl < 32; ++xl) {
+            int32_t gv[4], fv[4];
+#pragma unroll
+            for (int a = 0; a < 4; ++a) gv[a] = Gs[xl][ty * 4 + a];
+#pragma unroll
+            for (int b = 0; b < 4; ++b) fv[b] = Fs[xl][tx * 4 + b];
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int b = 0; b < 4; ++b) acc[a][b] += static_cast<long long>(gv[a]) * fv[b];
+        }
+        __syncthreads();
+    }
+    for (int a = 0; a < 4; ++a)
+        for (int b = 0; b < 4; ++b) {
+            const uint32_t l = l0 + ty * 4 + a, y = y0 + tx * 4 + b;
+            if (l < L && y < n) {
+                long long v = acc[a][b] % static_cast<long long>(q);
+                out[(size_t(u) * L + l) * n + y] = static_cast<uint32_t>(v < 0 ? v + q : v);
+            }
+        }
+}
+// MKLWE KeySwitchGen (mklwe-pke.cpp:176-256): B[u][i][a0][j] = e + sN_i (a0 baseKS^j) + <A[u][i][a0][j], s_u> mod qKS.
+// One warp per row (a coalesced read of the n-word vector), exact in 64 bits.
+__global__ void __launch_bounds__(256) keygen_ksk_mklwe_kernel(const DevCtx P, const uint32_t* __restrict__ A, const uint32_t* __restrict__ e,
+                                                               const uint32_t* __restrict__ s, const uint32_t* __restrict__ sN_q,
+                                                               uint32_t* __restrict__ Bout, uint64_t rows_total) {
+    const uint64_t row = (blockIdx.x * uint64_t(blockDim.x) + threadIdx.x) >> 5;
+    if (row >= rows_total) return;
+    const uint32_t lane = threadIdx.x & 31, n = P.n, q = P.qKS, d = P.dKS, base = P.baseKS;
+    const uint64_t per = uint64_t(P.N) * base * d;
+    const uint32_t u = uint32_t(row / per);
+    const uint64_t rr = row - u * per;
+    const uint32_t i = uint32_t(rr / (base * d)), a0 = uint32_t((rr / d) % base), j = uint32_t(rr % d);
+    const uint32_t* a = A + row * n;
+    const uint32_t* su = s + size_t(u) * n;
+    unsigned long long acc = 0;
+    for (uint32_t x = lane; x < n; x += 32) acc += static_cast<unsigned long long>(a[x] % q) * (su[x] % q);
+    uint32_t v = static_cast<uint32_t>(acc % q);
+#pragma unroll
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);  // 32 q < 2^32 (qKS < 2^24)
+    if (lane == 0) {
+        uint32_t pw = 1;
+        for (uint32_t t = 0; t < j; ++t) pw = uint32_t((uint64_t(pw) * (base % q)) % q);
+        const uint32_t msg = uint32_t((uint64_t(sN_q[size_t(u) * P.N + i] % q) * ((uint64_t(a0 % q) * pw) % q)) % q);
+        Bout[row] = addmod(addmod(e[row] % q, msg, q), v % q, q);
+    }
+}
+
 // ---- INT32 pipe micro-benchmark: 8 independent dependent-IMAD chains per thread ----
 __global__ void int32_peak_kernel(uint32_t* sink, uint32_t iters, uint32_t seed) {
     uint32_t a0 = seed + threadIdx.x, a1 = a0 ^ 0x9e3779b9u, a2 = a0 * 3u, a3 = a0 + 17u;

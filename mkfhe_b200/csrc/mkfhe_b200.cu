@@ -691,6 +691,58 @@ int mkfhe_keygen_pkey(mkfhe_ctx* ctx, const uint32_t* s, const uint32_t* crs, co
     return MKFHE_OK;
 }
 
+int mkfhe_keygen_ksk_mntru(mkfhe_ctx* ctx, const uint32_t* s_q, const uint32_t* e, const uint32_t* finv, uint32_t* ksk_out, int load) {
+    if (!ctx || !s_q || !e || !finv || (!ksk_out && !load)) return MKFHE_EINVAL;
+    const mkfhe_params& p = ctx->p;
+    if (p.scheme != MKFHE_SCHEME_MNTRU) return fail(ctx, MKFHE_EINVAL, "context is not MNTRU");
+    const size_t L = size_t(p.N) * p.dKS, words = size_t(p.k) * L * p.n;
+    CU(cudaSetDevice(ctx->device));
+    TmpBuf tmp;
+    uint32_t *d_s, *d_e, *d_f, *d_out;
+    CU(tmp.get(&d_s, size_t(p.k) * p.N));
+    CU(tmp.get(&d_e, words));
+    CU(tmp.get(&d_f, size_t(p.k) * p.n * p.n));
+    CU(tmp.get(&d_out, words));
+    CU(cudaMemcpyAsync(d_s, s_q, size_t(p.k) * p.N * 4, cudaMemcpyDefault, ctx->stream));
+    CU(cudaMemcpyAsync(d_e, e, words * 4, cudaMemcpyDefault, ctx->stream));
+    CU(cudaMemcpyAsync(d_f, finv, size_t(p.k) * p.n * p.n * 4, cudaMemcpyDefault, ctx->stream));
+    const dim3 grid((p.n + 63) / 64, unsigned((L + 63) / 64), p.k);
+    keygen_ksk_mntru_kernel<<<grid, 256, 0, ctx->stream>>>(ctx->d, d_s, d_e, d_f, d_out);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    if (ksk_out) CU(cudaMemcpyAsync(ksk_out, d_out, words * 4, cudaMemcpyDefault, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    if (load) return mkfhe_load_ksk_mntru(ctx, d_out, words);
+    return MKFHE_OK;
+}
+
+int mkfhe_keygen_ksk_mklwe(mkfhe_ctx* ctx, const uint32_t* A, const uint32_t* e, const uint32_t* s, const uint32_t* sN_q,
+                           uint32_t* B_out, int load) {
+    if (!ctx || !A || !e || !s || !sN_q || (!B_out && !load)) return MKFHE_EINVAL;
+    const mkfhe_params& p = ctx->p;
+    if (p.scheme != MKFHE_SCHEME_MKLWE) return fail(ctx, MKFHE_EINVAL, "context is not MKLWE");
+    const size_t rows = size_t(p.k) * p.N * p.baseKS * p.dKS, wordsA = rows * p.n;
+    CU(cudaSetDevice(ctx->device));
+    TmpBuf tmp;
+    uint32_t *d_A, *d_e, *d_s, *d_sN, *d_B;
+    CU(tmp.get(&d_A, wordsA));
+    CU(tmp.get(&d_e, rows));
+    CU(tmp.get(&d_s, size_t(p.k) * p.n));
+    CU(tmp.get(&d_sN, size_t(p.k) * p.N));
+    CU(tmp.get(&d_B, rows));
+    CU(cudaMemcpyAsync(d_A, A, wordsA * 4, cudaMemcpyDefault, ctx->stream));
+    CU(cudaMemcpyAsync(d_e, e, rows * 4, cudaMemcpyDefault, ctx->stream));
+    CU(cudaMemcpyAsync(d_s, s, size_t(p.k) * p.n * 4, cudaMemcpyDefault, ctx->stream));
+    CU(cudaMemcpyAsync(d_sN, sN_q, size_t(p.k) * p.N * 4, cudaMemcpyDefault, ctx->stream));
+    keygen_ksk_mklwe_kernel<<<unsigned((rows * 32 + 255) / 256), 256, 0, ctx->stream>>>(ctx->d, d_A, d_e, d_s, d_sN, d_B, rows);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    if (B_out) CU(cudaMemcpyAsync(B_out, d_B, rows * 4, cudaMemcpyDefault, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    if (load) return mkfhe_load_ksk_mklwe(ctx, d_A, wordsA, d_B, rows);
+    return MKFHE_OK;
+}
+
 int mkfhe_measure_butterfly_peak(mkfhe_ctx* ctx, double* bfly_per_s) {
     if (!ctx || !bfly_per_s) return MKFHE_EINVAL;
     CU(cudaSetDevice(ctx->device));

@@ -459,6 +459,53 @@ void orc_keygen_pkey(const orc_ctx* c, const uint32_t* s, const uint32_t* crs, c
     }
 }
 
+/* Key-switch key generation with the randomness as an input, one party.
+ * MNTRU  KeySwitchGen2 (mntru-pke.cpp:624-760), the independent digit-1 slice:  KSK = centred(E + gadget(s)) x centred(F^-1)
+ *   mod qKS, where gadget(s) adds s_i * baseKS^j to column 0 of row i*dKS + j (:652-671), products accumulated in 64 bits
+ *   and reduced once (mod_q, :408-418).  s_q [N]: the uni-encryption secret after SwitchModulus(qKS); e [N*dKS][n];
+ *   finv [n][n] row-major; out [N*dKS][n].  (The reference fills E with copies of ONE sampled row, :646: the caller
+ *   replicates it.) */
+static int64_t centre(uint32_t v, uint32_t q) { return v > q / 2 ? (int64_t)v - (int64_t)q : (int64_t)v; }
+void orc_keygen_ksk_mntru(const orc_ctx* c, const uint32_t* s_q, const uint32_t* e, const uint32_t* finv, uint32_t* out) {
+    const uint32_t N = c->p.N, n = c->p.n, d = c->p.dKS, q = c->p.qKS;
+    int64_t* row = (int64_t*)malloc(sizeof(int64_t) * n);
+    int64_t* acc = (int64_t*)malloc(sizeof(int64_t) * n);
+    for (uint32_t i = 0; i < N; ++i) {
+        uint32_t pw = s_q[i] % q;
+        for (uint32_t j = 0; j < d; ++j) {
+            const size_t l = (size_t)i * d + j;
+            for (uint32_t x = 0; x < n; ++x) row[x] = centre(x == 0 ? addmod(e[l * n] % q, pw, q) : e[l * n + x] % q, q);
+            memset(acc, 0, sizeof(int64_t) * n);
+            for (uint32_t x = 0; x < n; ++x)
+                for (uint32_t y = 0; y < n; ++y) acc[y] += row[x] * centre(finv[(size_t)x * n + y], q);
+            for (uint32_t y = 0; y < n; ++y) {
+                int64_t v = acc[y] % (int64_t)q;
+                out[l * n + y] = (uint32_t)(v < 0 ? v + q : v);
+            }
+            pw = mulmod(pw, c->p.baseKS % q, q);
+        }
+    }
+    free(row);
+    free(acc);
+}
+/* MKLWE KeySwitchGen (mklwe-pke.cpp:176-256), one party: B[i][a0][j] = e + sN_i * (a0 * baseKS^j) + <A[i][a0][j], s>  mod qKS.
+ * A [N*baseKS*dKS][n] (the sampled vectors, part of the key as they are), e [rows], s [n] (LWE secret), sN_q [N]. */
+void orc_keygen_ksk_mklwe(const orc_ctx* c, const uint32_t* A, const uint32_t* e, const uint32_t* s, const uint32_t* sN_q,
+                          uint32_t* Bout) {
+    const uint32_t N = c->p.N, n = c->p.n, d = c->p.dKS, q = c->p.qKS, base = c->p.baseKS;
+    for (uint32_t i = 0; i < N; ++i)
+        for (uint32_t a0 = 0; a0 < base; ++a0) {
+            uint32_t pw = 1;
+            for (uint32_t j = 0; j < d; ++j) {
+                const size_t row = ((size_t)i * base + a0) * d + j;
+                uint32_t b = addmod(e[row] % q, mulmod(sN_q[i] % q, mulmod(a0 % q, pw, q), q), q);
+                for (uint32_t x = 0; x < n; ++x) b = addmod(b, mulmod(A[row * n + x] % q, s[x] % q, q), q);
+                Bout[row] = b;
+                pw = mulmod(pw, base % q, q);
+            }
+        }
+}
+
 int orc_decrypt(const orc_ctx* c, const uint32_t* sk, const uint32_t* ct, uint32_t b) {
     const uint32_t k = c->p.k, n = c->p.n, q = c->p.q, p = 4;
     uint32_t inner = 0;

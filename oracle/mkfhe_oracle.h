@@ -73,6 +73,10 @@ int orc_decrypt(const orc_ctx* c, const uint32_t* sk, const uint32_t* ct, uint32
 void orc_keygen_evk(const orc_ctx* c, const uint32_t* sinv, const uint32_t* crs, const uint32_t* r, const uint32_t* e, int m,
                     int kdm, uint32_t* out);
 void orc_keygen_pkey(const orc_ctx* c, const uint32_t* s, const uint32_t* crs, const uint32_t* e, uint32_t* out);
+/* key-switch key generation, one party (mntru-pke.cpp:624-760 digit-1 slice; mklwe-pke.cpp:176-256) */
+void orc_keygen_ksk_mntru(const orc_ctx* c, const uint32_t* s_q, const uint32_t* e, const uint32_t* finv, uint32_t* out);
+void orc_keygen_ksk_mklwe(const orc_ctx* c, const uint32_t* A, const uint32_t* e, const uint32_t* s, const uint32_t* sN_q,
+                          uint32_t* Bout);
 
 /* CPU baseline helper: run `gates` NAND bootstraps over `threads` pthreads (same inputs each), return wall seconds */
 double orc_bench_gates(const orc_ctx* c, const uint32_t* bk, const uint32_t* pkey, const uint32_t* kskA, const uint32_t* kskB,

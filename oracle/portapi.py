@@ -63,6 +63,8 @@ def lib():
         L.orc_decrypt.argtypes = [C.c_void_p, U32P, U32P, C.c_uint32]
         L.orc_keygen_evk.argtypes = [C.c_void_p, U32P, U32P, U32P, U32P, C.c_int, C.c_int, U32P]
         L.orc_keygen_pkey.argtypes = [C.c_void_p, U32P, U32P, U32P, U32P]
+        L.orc_keygen_ksk_mntru.argtypes = [C.c_void_p, U32P, U32P, U32P, U32P]
+        L.orc_keygen_ksk_mklwe.argtypes = [C.c_void_p, U32P, U32P, U32P, U32P, U32P]
         L.orc_bench_gates.restype = C.c_double
         L.orc_bench_gates.argtypes = [C.c_void_p, U32P, U32P, U32P, U32P, U32P, U32P, C.c_uint32, U32P, C.c_uint32,
                                       C.c_uint32, C.c_uint32]
@@ -163,6 +165,18 @@ class Oracle:
     def keygen_pkey(self, s, crs, e):
         out = np.zeros((self.ell, self.N), dtype=np.uint32)
         self.L.orc_keygen_pkey(self.h, _p(_c(s)), _p(_c(crs)), _p(_c(e)), _p(out))
+        return out
+
+    def keygen_ksk_mntru(self, s_q, e, finv):
+        """one party: s_q [N], e [N*dKS][n], finv [n][n] (all mod qKS) -> KSK digit-1 slice [N*dKS][n]"""
+        out = np.zeros((self.N * self.params.dKS, self.n), dtype=np.uint32)
+        self.L.orc_keygen_ksk_mntru(self.h, _p(_c(s_q)), _p(_c(e)), _p(_c(finv)), _p(out))
+        return out
+
+    def keygen_ksk_mklwe(self, A, e, s, sN_q):
+        """one party: A [N*baseKS*dKS][n], e [rows], s [n], sN_q [N] -> B [rows]"""
+        out = np.zeros(self.N * self.params.baseKS * self.params.dKS, dtype=np.uint32)
+        self.L.orc_keygen_ksk_mklwe(self.h, _p(_c(A)), _p(_c(e)), _p(_c(s)), _p(_c(sN_q)), _p(out))
         return out
 
     def bench_gates(self, bk, pkey, kskA, kskB, ctnand, ct1, b1, ct2, b2, gates, threads) -> float:

@@ -264,6 +264,23 @@ int ref_export_unienc_sk(void* h, uint32_t* out) {
         for (uint32_t u = 0; u < c->k; ++u) put(out + size_t(u) * c->N, c->ek.f[u]);
     });
 }
+// f_u in COEFFICIENT form [k][N] mod Q (UniEncBTKey::fvec): the secret the key-switch keys encrypt
+int ref_export_unienc_sk_coef(void* h, uint32_t* out) {
+    auto* c = static_cast<RefCtx*>(h);
+    return guarded(c, [&] {
+        for (uint32_t u = 0; u < c->k; ++u) put(out + size_t(u) * c->N, c->ek.fvec[u]);
+    });
+}
+// MNTRU secret matrices [k][n][n] mod qKS, row-major as stored (mntru-privatekey.h:52,104): inverse = 0 -> F, 1 -> F^-1
+int ref_export_mntru_F(void* h, uint32_t* out, int inverse) {
+    auto* c = static_cast<RefCtx*>(h);
+    return guarded(c, [&] {
+        if (c->scheme != 0) throw std::runtime_error("not an MNTRU context");
+        const auto& F = inverse ? c->skN->GetF_inv() : c->skN->GetF();
+        for (uint32_t u = 0; u < c->k; ++u)
+            for (uint32_t l = 0; l < c->n; ++l) put(out + (size_t(u) * c->n + l) * c->n, F[u][l]);
+    });
+}
 int ref_export_crs(void* h, uint32_t* out) {
     auto* c = static_cast<RefCtx*>(h);
     return guarded(c, [&] {

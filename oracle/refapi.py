@@ -41,8 +41,9 @@ def lib():
         L.ref_keygen.argtypes = [C.c_void_p]
         L.ref_bk_words.restype = C.c_uint64
         L.ref_bk_words.argtypes = [C.c_void_p]
-        for name in ("ref_export_bk", "ref_export_pkey", "ref_export_ctnand", "ref_export_sk", "ref_export_unienc_sk", "ref_export_crs"):
+        for name in ("ref_export_bk", "ref_export_pkey", "ref_export_ctnand", "ref_export_sk", "ref_export_unienc_sk", "ref_export_crs", "ref_export_unienc_sk_coef"):
             getattr(L, name).argtypes = [C.c_void_p, U32P]
+        L.ref_export_mntru_F.argtypes = [C.c_void_p, U32P, C.c_int]
         L.ref_export_ksk_mntru.argtypes = [C.c_void_p, U32P, C.POINTER(C.c_uint64)]
         L.ref_export_ksk_mklwe.argtypes = [C.c_void_p, U32P, U32P]
         L.ref_encrypt.argtypes = [C.c_void_p, C.c_int, U32P, U32P]
@@ -170,6 +171,18 @@ class Ref:
         a = np.zeros(self.p.k * self.p.N, dtype=np.uint32)
         self._ck(self.L.ref_export_unienc_sk(self.h, _p(a)), "ref_export_unienc_sk")
         return a.reshape(self.p.k, self.p.N)
+
+    def unienc_sk_coef(self) -> np.ndarray:
+        """f_u in COEFFICIENT form mod Q, [k][N] (UniEncBTKey::fvec)."""
+        a = np.zeros(self.p.k * self.p.N, dtype=np.uint32)
+        self._ck(self.L.ref_export_unienc_sk_coef(self.h, _p(a)), "ref_export_unienc_sk_coef")
+        return a.reshape(self.p.k, self.p.N)
+
+    def mntru_F(self, inverse: bool) -> np.ndarray:
+        """MNTRU secret matrices F (or F^-1) mod qKS, [k][n][n]."""
+        a = np.zeros(self.p.k * self.p.n * self.p.n, dtype=np.uint32)
+        self._ck(self.L.ref_export_mntru_F(self.h, _p(a), int(inverse)), "ref_export_mntru_F")
+        return a.reshape(self.p.k, self.p.n, self.p.n)
 
     def crs(self) -> np.ndarray:
         """CRS in EVALUATION form, [ell][N]."""

@@ -97,3 +97,48 @@ def expected_messages(p, sk):
         m[e] = int(v == 1) if s == 0 else int(v == p.qKS - 1)
     m[E - 1] = 1
     return m
+
+
+# ---- key-switch keys ----
+def _cen(x, q):
+    x = np.asarray(x).astype(np.int64) % q
+    return np.where(x > q // 2, x - q, x)
+
+
+def switch_modulus(f_coef, Q, q):
+    """NativeVector::SwitchModulus(qKS) of the uni-encryption secret coefficients: centred lift, then mod q."""
+    return (_cen(f_coef, Q) % q).astype(np.uint32)
+
+
+def extract_ksk_mntru_noise(p, ksk, F, s_q, small=64):
+    """KSK = centred(E + gadget(s)) x centred(F^-1)  =>  E = KSK x F - gadget(s)  (mntru-pke.cpp:624-760).  Returns E
+    [k][N*dKS][n] mod qKS; the reference fills it with copies of one sampled row per party (:646)."""
+    q, N, n, d, k = p.qKS, p.N, p.n, p.dKS, p.k
+    ksk = np.asarray(ksk).reshape(k, N * d, n).astype(np.int64)
+    out = np.zeros((k, N * d, n), np.uint32)
+    for u in range(k):
+        G = (ksk[u] @ np.asarray(F[u]).astype(np.int64)) % q
+        for j in range(d):
+            G[j::d, 0] = (G[j::d, 0] - s_q[u].astype(np.int64) * pow(p.baseKS, j, q)) % q
+        E = _cen(G, q)
+        assert np.abs(E).max() < small and (E == E[0]).all()
+        out[u] = (E % q).astype(np.uint32)
+    return out
+
+
+def extract_ksk_mklwe_noise(p, A, B, s, sN_q, small=64):
+    """e = B - <A, s> - sN_i a0 baseKS^j  (mklwe-pke.cpp:220-235).  Returns e [k][N*baseKS*dKS] mod qKS."""
+    q, N, n, d, k, base = p.qKS, p.N, p.n, p.dKS, p.k, p.baseKS
+    A = np.asarray(A).reshape(k, N, base, d, n).astype(np.int64)
+    B = np.asarray(B).reshape(k, N, base, d).astype(np.int64)
+    s = np.asarray(s).reshape(k, n).astype(np.int64)
+    out = np.zeros((k, N * base * d), np.uint32)
+    for u in range(k):
+        msg = np.zeros((N, base, d), np.int64)
+        for a0 in range(base):
+            for j in range(d):
+                msg[:, a0, j] = sN_q[u].astype(np.int64) * (a0 * pow(base, j, q) % q) % q
+        e = _cen(B[u] - A[u] @ s[u] - msg, q)
+        assert np.abs(e).max() < small
+        out[u] = (e.reshape(-1) % q).astype(np.uint32)
+    return out

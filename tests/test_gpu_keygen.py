@@ -75,3 +75,67 @@ def test_keygen_full_size_and_bootstraps():
     assert r.decrypt(o3, ob3) == 1    # NAND(NAND(1,0), NAND(1,1)) = NAND(1, 0) = 1
     ctx.close()
     r.close()
+
+
+def test_ksk_keygen_reproduces_reference_keys():
+    """Key-switch key generation at toy size, both schemes: the GPU fed with the noise recovered from the
+    reference's keys returns the reference's key bytes; with perturbed (non-replicated) noise it matches the C oracle."""
+    from gpu_util import ctx_from_params
+    from keygen_util import extract_ksk_mklwe_noise, extract_ksk_mntru_noise, switch_modulus
+
+    r = refapi.Ref(*TOY["mkntru_k2_N256"])
+    r.keygen()
+    p = params_from_ref(r.p)
+    o, ctx = make_oracle(p), ctx_from_params(p)
+    ksk, bad = r.ksk_mntru()
+    F, Fi = r.mntru_F(False), r.mntru_F(True)
+    s_q = switch_modulus(r.unienc_sk_coef(), p.Q, p.qKS)
+    E = extract_ksk_mntru_noise(p, ksk, F, s_q)
+    assert (ctx.KeySwitchGen2(s_q, E, Fi) == ksk).all()
+    E2 = np.random.default_rng(3).integers(0, p.qKS, size=E.shape, dtype=np.uint32)
+    got = ctx.KeySwitchGen2(s_q, E2, Fi).reshape(p.k, -1, p.n)
+    assert (got[1] == o.keygen_ksk_mntru(s_q[1], E2[1], Fi[1])).all()
+    ctx.close()
+    r.close()
+
+    r = refapi.Ref(*TOY["mklwe_k3_N64_B7"])
+    r.keygen()
+    p = params_from_ref(r.p)
+    o, ctx = make_oracle(p), ctx_from_params(p)
+    A, B = r.ksk_mklwe()
+    s = r.sk().reshape(p.k, p.n)
+    sN_q = switch_modulus(r.unienc_sk_coef(), p.Q, p.qKS)
+    e = extract_ksk_mklwe_noise(p, A, B, s, sN_q)
+    assert (ctx.KeySwitchGenLWE(A, e, s, sN_q) == B).all()
+    A2 = np.random.default_rng(4).integers(0, p.qKS, size=A.shape, dtype=np.uint32)
+    rows = p.N * p.baseKS * p.dKS
+    got = ctx.KeySwitchGenLWE(A2, e, s, sN_q).reshape(p.k, rows)
+    assert (got[2] == o.keygen_ksk_mklwe(A2.reshape(p.k, rows, p.n)[2], e[2], s[2], sN_q[2])).all()
+    ctx.close()
+    r.close()
+
+
+def test_ksk_keygen_full_size_mntru():
+    """boolean-mkntru (STD100_MKNTRU): the 2 x 8192 x 560 digit-1 slice regenerated on the GPU = the reference's; installed with
+    load=True next to the reference's other keys it bootstraps to the reference's EvalBinGate output."""
+    from gpu_util import ctx_from_params
+    from keygen_util import extract_ksk_mntru_noise, switch_modulus
+
+    r = refapi.Ref.from_paramset("STD100_MKNTRU")
+    r.keygen()
+    p = params_from_ref(r.p)
+    ctx = ctx_from_params(p)
+    ksk, bad = r.ksk_mntru()
+    assert bad == 0
+    F, Fi = r.mntru_F(False), r.mntru_F(True)
+    s_q = switch_modulus(r.unienc_sk_coef(), p.Q, p.qKS)
+    E = extract_ksk_mntru_noise(p, ksk, F, s_q)
+    ctx.LoadKeys(r.bk(), r.pkey(), ksk=np.zeros_like(ksk), ctnand=r.ctnand())  # a wrong key-switch key first
+    assert (ctx.KeySwitchGen2(s_q, E, Fi, load=True) == ksk).all()
+    c1, _ = r.encrypt(1)
+    c2, _ = r.encrypt(1)
+    eo, _ = r.eval_gate(c1, 0, c2, 0)
+    out = ctx.EvalBinGate("NAND", c1.reshape(1, p.k, p.n), c2.reshape(1, p.k, p.n))
+    assert (np.asarray(out).ravel() == eo).all() and r.decrypt(eo, 0) == 0
+    ctx.close()
+    r.close()

@@ -157,3 +157,38 @@ def test_oracle_keygen_reproduces_reference_keys(scheme):
         assert ((a[j, 1] - b[j, 1]) % p.Q == g * R % p.Q * inv[0].astype(np.int64) % p.Q).all()
         assert ((a[j, 0] - b[j, 0]) % p.Q == R[j] * crs[j].astype(np.int64) % p.Q).all()
     r.close()
+
+
+@pytest.mark.skipif(not refapi.available(), reason="oracle/_ref/libmkfhe_ref.so not present")
+def test_oracle_ksk_keygen_reproduces_reference_keys():
+    """Key-switch key generation: noise recovered from the reference's keys and secrets, fed to the
+    oracle's restatement of KeySwitchGen2 (digit-1 slice) / MKLWE KeySwitchGen, gives the reference's key bytes back."""
+    from keygen_util import extract_ksk_mklwe_noise, extract_ksk_mntru_noise, switch_modulus
+
+    r = refapi.Ref(0, 2, 27, 512, 8, 45181, 45181, 0.75, 32, 1 << 9, 32)
+    r.keygen()
+    p = params_from_ref(r.p)
+    o = make_oracle(p)
+    ksk, bad = r.ksk_mntru()
+    assert bad == 0
+    F, Fi = r.mntru_F(False), r.mntru_F(True)
+    s_q = switch_modulus(r.unienc_sk_coef(), p.Q, p.qKS)
+    E = extract_ksk_mntru_noise(p, ksk, F, s_q)
+    ksk = ksk.reshape(p.k, p.N * p.dKS, p.n)
+    for u in range(p.k):
+        assert (o.keygen_ksk_mntru(s_q[u], E[u], Fi[u]) == ksk[u]).all()
+    r.close()
+
+    r = refapi.Ref(1, 3, 27, 128, 6, 32749, 32749, 1.9, 32, 1 << 7, 2)
+    r.keygen()
+    p = params_from_ref(r.p)
+    o = make_oracle(p)
+    A, B = r.ksk_mklwe()
+    s = r.sk().reshape(p.k, p.n)
+    sN_q = switch_modulus(r.unienc_sk_coef(), p.Q, p.qKS)
+    e = extract_ksk_mklwe_noise(p, A, B, s, sN_q)
+    rows = p.N * p.baseKS * p.dKS
+    A, B = A.reshape(p.k, rows, p.n), B.reshape(p.k, rows)
+    for u in range(p.k):
+        assert (o.keygen_ksk_mklwe(A[u], e[u], s[u], sN_q[u]) == B[u]).all()
+    r.close()
