@@ -183,6 +183,18 @@ int mkfhe_keygen_ksk_mntru(mkfhe_ctx* ctx, const uint32_t* s_q, const uint32_t* 
 int mkfhe_keygen_ksk_mklwe(mkfhe_ctx* ctx, const uint32_t* A, const uint32_t* e, const uint32_t* s, const uint32_t* sN_q,
                            uint32_t* B_out, int load);
 
+/* Binary key file: the flattened layouts above, one checksummed section per key (format: mkfhe_b200/csrc/keyfile.h).
+ * Replaces, for the GPU path, the reference's cereal save/load of the key object graphs (mk-acckey.h, mk-evalkey.h,
+ * mntru-keyswitchkey2.h, mklwe-keyswitchkey.h; UniEncBTKey has no serializer of its own).  Host buffers; a NULL / zero-length
+ * key is not written.  kskA = the MNTRU digit-1 slice (kskB, ctnand: MKLWE B column / MNTRU ctNAND).
+ * mkfhe_keyfile_info: parameters and section sizes (words_by_tag[7], index 1 bk, 2 pkey, 3 ksk, 4 kskA, 5 kskB, 6 ctnand),
+ * verifying every checksum -- needs no GPU.  mkfhe_keyfile_load: the file must match the context's parameter set. */
+int mkfhe_keyfile_write(const char* path, const mkfhe_params* p, const uint32_t* bk, uint64_t bk_words, const uint32_t* pkey,
+                        uint64_t pkey_words, const uint32_t* kskA, uint64_t kskA_words, const uint32_t* kskB, uint64_t kskB_words,
+                        const uint32_t* ctnand, uint64_t ctnand_words);
+int mkfhe_keyfile_info(const char* path, mkfhe_params* p, uint64_t* words_by_tag);
+int mkfhe_keyfile_load(mkfhe_ctx* ctx, const char* path);
+
 const char* mkfhe_version(void);
 /* INT32 pipe micro-benchmark (dependent IMAD chains on every SM): returns thread-level IMAD/s in *imad_per_s.
  * Used by bench.py as the denominator of the integer roofline (SURVEY.md section 8d asks for a measured peak). */

@@ -9,6 +9,7 @@ derivation of Q and psi (binfhecontext.cpp:157-158), which is host-side paramete
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass
 from math import ceil, log
 
@@ -364,3 +365,31 @@ class BinFHEContext:
         self._ck(self._L.mkfhe_keygen_ksk_mklwe(self._h, _ptr(A)[0], _ptr(e)[0], _ptr(s)[0], _ptr(sN_q)[0], _ptr(out)[0],
                                                 int(load)), "mkfhe_keygen_ksk_mklwe")
         return out
+
+    # -- binary key file (mkfhe_b200/csrc/keyfile.h): the flattened layouts, checksummed; replaces the reference's cereal
+    #    serialisation of the key object graphs for the GPU path
+    def LoadKeyFile(self, path: str):
+        self._ck(self._L.mkfhe_keyfile_load(self._h, os.fsencode(path)), "mkfhe_keyfile_load")
+
+
+def SaveKeyFile(path: str, params: Params, bk, pkey, ksk=None, kskA=None, kskB=None, ctnand=None):
+    """Write a key file for `params` (no GPU needed).  MNTRU: ksk (digit-1 slice) + ctnand; MKNTRU_LWE: kskA + kskB."""
+    L = _lib.load()
+    a = kskA if kskA is not None else ksk
+    args = []
+    for x in (bk, pkey, a, kskB, ctnand):
+        p, n = _ptr(None if x is None else np.ascontiguousarray(x, dtype=np.uint32))
+        args += [p, n]
+    if L.mkfhe_keyfile_write(os.fsencode(path), C.byref(params), *args) != 0:
+        raise _lib.MkfheError(-1, "mkfhe_keyfile_write", f"cannot write {path}")
+
+
+def KeyFileInfo(path: str):
+    """(Params, {section name: words}) of a key file, verifying every checksum (no GPU needed)."""
+    L = _lib.load()
+    p = Params()
+    w = (C.c_uint64 * 7)()
+    if L.mkfhe_keyfile_info(os.fsencode(path), C.byref(p), w) != 0:
+        raise _lib.MkfheError(-1, "mkfhe_keyfile_info", f"{path}: unreadable, not a key file, or checksum mismatch")
+    names = {1: "bk", 2: "pkey", 3: "ksk", 4: "kskA", 5: "kskB", 6: "ctnand"}
+    return p, {names[i]: int(w[i]) for i in names if w[i]}

@@ -16,6 +16,7 @@
 #include "../../include/mkfhe_b200.h"
 #include "fast_kernels.cuh"
 #include "generic_kernels.cuh"
+#include "keyfile.h"
 
 using namespace mkfhe;
 
@@ -741,6 +742,67 @@ int mkfhe_keygen_ksk_mklwe(mkfhe_ctx* ctx, const uint32_t* A, const uint32_t* e,
     CU(cudaStreamSynchronize(ctx->stream));
     if (load) return mkfhe_load_ksk_mklwe(ctx, d_A, wordsA, d_B, rows);
     return MKFHE_OK;
+}
+
+// ---- binary key file (format in keyfile.h) ----
+int mkfhe_keyfile_write(const char* path, const mkfhe_params* p, const uint32_t* bk, uint64_t bk_words, const uint32_t* pkey,
+                        uint64_t pkey_words, const uint32_t* kskA, uint64_t kskA_words, const uint32_t* kskB, uint64_t kskB_words,
+                        const uint32_t* ctnand, uint64_t ctnand_words) {
+    if (!path || !p) return MKFHE_EINVAL;
+    using namespace mkfhe_keyfile;
+    Writer w;
+    if (!w.open(path, *p)) return MKFHE_EINVAL;
+    const bool lwe = p->scheme == MKFHE_SCHEME_MKLWE;
+    bool ok = w.section(BK, bk, bk_words) && w.section(PKEY, pkey, pkey_words) && w.section(lwe ? KSKA : KSK, kskA, kskA_words) &&
+              (!lwe || w.section(KSKB, kskB, kskB_words)) && (lwe || w.section(CTNAND, ctnand, ctnand_words));
+    ok = w.close() && ok;
+    return ok ? MKFHE_OK : MKFHE_EINVAL;
+}
+
+int mkfhe_keyfile_info(const char* path, mkfhe_params* p, uint64_t* words_by_tag /* [7], index = section tag */) {
+    if (!path) return MKFHE_EINVAL;
+    uint64_t w[mkfhe_keyfile::TAG_MAX + 1];
+    const int rc = mkfhe_keyfile::read(path, p, &w, [](uint32_t, const uint32_t*, uint64_t) { return 0; });
+    if (words_by_tag) memcpy(words_by_tag, w, sizeof w);
+    return rc ? MKFHE_EINVAL : MKFHE_OK;
+}
+
+int mkfhe_keyfile_load(mkfhe_ctx* ctx, const char* path) {
+    if (!ctx || !path) return MKFHE_EINVAL;
+    using namespace mkfhe_keyfile;
+    // first pass: header only -- the file must describe this context's parameter set
+    mkfhe_params fp{};
+    std::vector<uint32_t> kskA;  // MKLWE: A is held until B arrives (mkfhe_load_ksk_mklwe takes both)
+    bool params_checked = false;
+    int inner = MKFHE_OK;
+    const int rc = read(path, &fp, nullptr, [&](uint32_t tag, const uint32_t* data, uint64_t words) -> int {
+        if (!params_checked) {
+            uint32_t a[13], b[13];
+            params_to_words(fp, a);
+            params_to_words(ctx->p, b);
+            if (memcmp(a, b, sizeof a) != 0) return -5;
+            params_checked = true;
+        }
+        switch (tag) {
+            case BK: inner = mkfhe_load_bk(ctx, data, words); break;
+            case PKEY: inner = mkfhe_load_pkey(ctx, data, words); break;
+            case KSK: inner = mkfhe_load_ksk_mntru(ctx, data, words); break;
+            case KSKA: kskA.assign(data, data + words); break;
+            case KSKB: inner = kskA.empty() ? MKFHE_EINVAL : mkfhe_load_ksk_mklwe(ctx, kskA.data(), kskA.size(), data, words); break;
+            case CTNAND: inner = mkfhe_load_ctnand(ctx, data, words); break;
+            default: return -4;
+        }
+        return inner ? -6 : 0;
+    });
+    switch (rc) {
+        case 0: return MKFHE_OK;
+        case -1: return fail(ctx, MKFHE_EINVAL, "mkfhe_keyfile_load: cannot read %s", path);
+        case -2: return fail(ctx, MKFHE_EINVAL, "mkfhe_keyfile_load: %s is not a version-%u key file", path, VERSION);
+        case -3: return fail(ctx, MKFHE_EINVAL, "mkfhe_keyfile_load: checksum mismatch in %s", path);
+        case -5: return fail(ctx, MKFHE_EINVAL, "mkfhe_keyfile_load: %s was written for a different parameter set", path);
+        case -6: return inner;  // mkfhe_load_* already recorded the reason
+        default: return fail(ctx, MKFHE_EINVAL, "mkfhe_keyfile_load: malformed section in %s", path);
+    }
 }
 
 int mkfhe_measure_butterfly_peak(mkfhe_ctx* ctx, double* bfly_per_s) {

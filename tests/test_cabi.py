@@ -50,3 +50,30 @@ def test_parameter_derivation_matches_reference_constants():
     assert mk.derive_params(mk.PARAMSETS["STD128_MKNTRU_4"], mk.MKNTRU).digitsG == 6
     with pytest.raises(mk.config_error):
         mk.derive_params(mk.PARAMSETS["STD100_MKNTRU"], "GINX")
+
+
+def test_keyfile_write_info_roundtrip_and_corruption(tmp_path):
+    """The binary key file needs no GPU to write or to verify: sizes and parameters come back, a flipped
+    payload byte is caught by the section checksum, a foreign file is rejected."""
+    import numpy as np
+
+    import mkfhe_b200 as mk
+    from util import load_golden
+
+    g = load_golden("toy_mkntru_k4_N256")
+    p = g["p"]
+    P = mk.Params(k=p.k, N=p.N, Q=p.Q, psi=p.psi, q=p.q, qKS=p.qKS, n=p.n, baseG_log2=p.baseG_log2, digitsG=p.digitsG,
+                  baseKS=p.baseKS, dKS=p.dKS, variant=p.variant, scheme=p.scheme, device=-1)
+    path = str(tmp_path / "keys.mkfhe")
+    mk.SaveKeyFile(path, P, g["bk"], g["pkey"], ksk=g["ksk"], ctnand=g["ctnand"])
+    Pr, sizes = mk.KeyFileInfo(path)
+    assert (Pr.k, Pr.N, Pr.Q, Pr.n, Pr.scheme, Pr.variant) == (p.k, p.N, p.Q, p.n, p.scheme, p.variant)
+    assert sizes == {"bk": np.size(g["bk"]), "pkey": np.size(g["pkey"]), "ksk": np.size(g["ksk"]), "ctnand": np.size(g["ctnand"])}
+    raw = bytearray(open(path, "rb").read())
+    raw[len(raw) // 2] ^= 1
+    open(path, "wb").write(raw)
+    with pytest.raises(mk.MkfheError):
+        mk.KeyFileInfo(path)
+    open(path, "wb").write(b"not a key file at all, just some bytes" * 4)
+    with pytest.raises(mk.MkfheError):
+        mk.KeyFileInfo(path)

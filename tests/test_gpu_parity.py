@@ -129,3 +129,34 @@ def test_unfused_key_switch_path(name, monkeypatch):
             assert (out == g["g_out"]).all() and (bout == g["g_bout"]).all()
     finally:
         ctx.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["toy_mkntru_k4_N256", "toy_mklwe_k2_N128"])
+def test_keyfile_load_gives_the_same_gates(name, tmp_path):
+    """Keys written to the binary key file and loaded with mkfhe_keyfile_load bootstrap exactly like keys loaded from
+    memory (= the reference's golden outputs); a file for another parameter set is refused."""
+    import mkfhe_b200 as mk
+    from gpu_util import ctx_from_params
+
+    g = load_golden(name)
+    p = g["p"]
+    ctx = ctx_from_params(p)
+    path = str(tmp_path / "keys.mkfhe")
+    if p.scheme == 0:
+        mk.SaveKeyFile(path, ctx.params, g["bk"], g["pkey"], ksk=g["ksk"], ctnand=g["ctnand"])
+    else:
+        mk.SaveKeyFile(path, ctx.params, g["bk"], g["pkey"], kskA=g["kskA"], kskB=g["kskB"])
+    ctx.LoadKeyFile(path)
+    if p.scheme == 0:
+        out = ctx.EvalBinGate("NAND", g["g_ct1"], g["g_ct2"])
+        assert (out == g["g_out"]).all()
+    else:
+        out, bout = ctx.EvalBinGate("NAND", g["g_ct1"], g["g_ct2"], g["g_b1"], g["g_b2"])
+        assert (out == g["g_out"]).all() and (bout == g["g_bout"]).all()
+    ctx.close()
+    other = load_golden("toy_mklwe_k2_N128" if p.scheme == 0 else "toy_mkntru_k4_N256")
+    ctx2 = ctx_from_params(other["p"])
+    with pytest.raises(mk.MkfheError):
+        ctx2.LoadKeyFile(path)
+    ctx2.close()
