@@ -183,6 +183,17 @@ int mkfhe_keygen_ksk_mntru(mkfhe_ctx* ctx, const uint32_t* s_q, const uint32_t* 
 int mkfhe_keygen_ksk_mklwe(mkfhe_ctx* ctx, const uint32_t* A, const uint32_t* e, const uint32_t* s, const uint32_t* sN_q,
                            uint32_t* B_out, int load);
 
+/* Batched Encrypt on the GPU with the noise supplied by the caller (host or device pointers; residues mod q).
+ * MNTRU: replaces MNTRUEncryptionScheme::Encrypt (mntru-pke.cpp:158-205) for a batch:
+ *   ct[b][u] = (e[b][u] + [u == 0] (m[b] mod pmod) (q / pmod) at index 0) x F_u^-1 mod q;  finv [k][n][n] = sk->GetF_inv(),
+ *   row-major; e [B][k][n]; m [B] bytes; ct_out [B][k][n].
+ * MKLWE: replaces MKLWEEncryptionScheme::Encrypt (mklwe-pke.cpp:36-64): b[g] = (m mod pmod)(q / pmod) + err[g] + sum_u <a[g][u], s_u>;
+ *   the a vectors [B][k][n] are the caller's samples (the ciphertext's a part as they are); s [k][n]; err [B]; b_out [B]. */
+int mkfhe_encrypt_mntru(mkfhe_ctx* ctx, const uint32_t* finv, const uint32_t* e, const uint8_t* m, uint32_t pmod, uint32_t* ct_out,
+                        uint64_t batch);
+int mkfhe_encrypt_mklwe(mkfhe_ctx* ctx, const uint32_t* s, const uint32_t* a, const uint32_t* err, const uint8_t* m, uint32_t pmod,
+                        uint32_t* b_out, uint64_t batch);
+
 /* Binary key file: the flattened layouts above, one checksummed section per key (format: mkfhe_b200/csrc/keyfile.h).
  * Replaces, for the GPU path, the reference's cereal save/load of the key object graphs (mk-acckey.h, mk-evalkey.h,
  * mntru-keyswitchkey2.h, mklwe-keyswitchkey.h; UniEncBTKey has no serializer of its own).  Host buffers; a NULL / zero-length

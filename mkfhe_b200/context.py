@@ -393,3 +393,30 @@ def KeyFileInfo(path: str):
         raise _lib.MkfheError(-1, "mkfhe_keyfile_info", f"{path}: unreadable, not a key file, or checksum mismatch")
     names = {1: "bk", 2: "pkey", 3: "ksk", 4: "kskA", 5: "kskB", 6: "ctnand"}
     return p, {names[i]: int(w[i]) for i in names if w[i]}
+
+
+def _encrypt_methods():
+    # -- batched Encrypt with caller-supplied noise (mntru-pke.cpp:158-205, mklwe-pke.cpp:36-64)
+    def EncryptBatch(self, m, noise, secret, a=None, pmod: int = 4):
+        """MNTRU: noise = e [B][k][n], secret = F^-1 [k][n][n] -> ct [B][k][n].
+        MKNTRU_LWE: a [B][k][n] (the sampled vectors = the ciphertext's a part), noise = err [B], secret = s [k][n] -> b [B]."""
+        P = self.params
+        m = np.ascontiguousarray(m, dtype=np.uint8).reshape(-1)
+        B = m.size
+        u32 = lambda x, shape: np.ascontiguousarray(x, dtype=np.uint32).reshape(shape)
+        mp = C.c_void_p(m.ctypes.data)
+        if not self.is_lwe:
+            e, finv = u32(noise, (B, P.k, P.n)), u32(secret, (P.k, P.n, P.n))
+            out = np.empty((B, P.k, P.n), dtype=np.uint32)
+            self._ck(self._L.mkfhe_encrypt_mntru(self._h, _ptr(finv)[0], _ptr(e)[0], mp, pmod, _ptr(out)[0], B), "mkfhe_encrypt_mntru")
+            return out
+        a, err, s = u32(a, (B, P.k, P.n)), u32(noise, (B,)), u32(secret, (P.k, P.n))
+        out = np.empty(B, dtype=np.uint32)
+        self._ck(self._L.mkfhe_encrypt_mklwe(self._h, _ptr(s)[0], _ptr(a)[0], _ptr(err)[0], mp, pmod, _ptr(out)[0], B),
+                 "mkfhe_encrypt_mklwe")
+        return out
+
+    BinFHEContext.EncryptBatch = EncryptBatch
+
+
+_encrypt_methods()

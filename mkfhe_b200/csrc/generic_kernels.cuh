@@ -713,6 +713,74 @@ __global__ void __launch_bounds__(256) keygen_ksk_mklwe_kernel(const DevCtx P, c
     }
 }
 
+// ---- batched Encrypt with caller-supplied noise ----
+// MNTRU Encrypt (mntru-pke.cpp:158-205): c[b][u] = (e[b][u] + [u == 0] (m mod p)(q/p) delta_0) x F_u^-1 mod q -- a row vector
+// times the party's n x n matrix; batched: a [B x n] x [n x n] product per party, exact in 64 bits.  Same tiling as the
+// key-switch key generator.  e [B][k][n], m [B], out [B][k][n].
+__global__ void __launch_bounds__(256) encrypt_mntru_kernel(const DevCtx P, const uint32_t* __restrict__ finv, const uint32_t* __restrict__ e,
+                                                            const uint8_t* __restrict__ m, uint32_t pmod, uint32_t* __restrict__ out,
+                                                            uint32_t B) {
+    __shared__ uint32_t Es[32][64 + 1];  // [x][gate]
+    __shared__ uint32_t Fs[32][64];      // [x][col]
+    const uint32_t u = blockIdx.z, b0 = blockIdx.y * 64, y0 = blockIdx.x * 64;
+    const uint32_t tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    const uint32_t n = P.n, q = P.q, k = P.k;
+    unsigned long long acc[4][4] = {};
+    for (uint32_t x0 = 0; x0 < n; x0 += 32) {
+        for (uint32_t t = threadIdx.x; t < 32 * 64; t += 256) {
+            const uint32_t bl = t >> 5, xl = t & 31, b = b0 + bl, x = x0 + xl;
+            uint32_t v = 0;
+            if (b < B && x < n) {
+                v = e[(size_t(b) * k + u) * n + x] % q;
+                if (u == 0 && x == 0) v = addmod(v, uint32_t((uint64_t(m[b] % pmod) * (q / pmod)) % q), q);
+            }
+            Es[xl][bl] = v;
+        }
+        for (uint32_t t = threadIdx.x; t < 32 * 64; t += 256) {
+            const uint32_t xl = t >> 6, yl = t & 63, x = x0 + xl, y = y0 + yl;
+            Fs[xl][yl] = (x < n && y < n) ? finv[(size_t(u) * n + x) * n + y] % q : 0u;
+        }
+        __syncthreads();
+#pragma unroll 8
+        for (uint32_t xl = 0; xl < 32; ++xl) {
+            uint32_t ev[4], fv[4];
+#pragma unroll
+            for (int a = 0; a < 4; ++a) ev[a] = Es[xl][ty * 4 + a];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) fv[c] = Fs[xl][tx * 4 + c];
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) acc[a][c] += static_cast<unsigned long long>(ev[a]) * fv[c];
+        }
+        __syncthreads();
+    }
+    for (int a = 0; a < 4; ++a)
+        for (int c = 0; c < 4; ++c) {
+            const uint32_t b = b0 + ty * 4 + a, y = y0 + tx * 4 + c;
+            if (b < B && y < n) out[(size_t(b) * k + u) * n + y] = static_cast<uint32_t>(acc[a][c] % q);
+        }
+}
+// MKLWE Encrypt (mklwe-pke.cpp:36-64): b = (m mod p)(q/p) + err + sum_u <a_u, s_u> mod q; the a vectors are the caller's
+// samples and stay as they are.  One warp per ciphertext.
+__global__ void __launch_bounds__(256) encrypt_mklwe_kernel(const DevCtx P, const uint32_t* __restrict__ s, const uint32_t* __restrict__ a,
+                                                            const uint32_t* __restrict__ err, const uint8_t* __restrict__ m, uint32_t pmod,
+                                                            uint32_t* __restrict__ bout, uint64_t B) {
+    const uint64_t g = (blockIdx.x * uint64_t(blockDim.x) + threadIdx.x) >> 5;
+    if (g >= B) return;
+    const uint32_t lane = threadIdx.x & 31, kn = P.k * P.n, q = P.q;
+    const uint32_t* c = a + g * kn;
+    unsigned long long acc = 0;
+    for (uint32_t x = lane; x < kn; x += 32) acc += static_cast<unsigned long long>(c[x] % q) * (s[x] % q);
+    uint32_t r = static_cast<uint32_t>(acc % q);
+#pragma unroll
+    for (int o = 16; o; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);
+    if (lane == 0) {
+        const uint32_t msg = uint32_t((uint64_t(m[g] % pmod) * (q / pmod)) % q);
+        bout[g] = addmod(addmod(msg, err[g] % q, q), r % q, q);
+    }
+}
+
 // ---- INT32 pipe micro-benchmark: 8 independent dependent-IMAD chains per thread ----
 __global__ void int32_peak_kernel(uint32_t* sink, uint32_t iters, uint32_t seed) {
     uint32_t a0 = seed + threadIdx.x, a1 = a0 ^ 0x9e3779b9u, a2 = a0 * 3u, a3 = a0 + 17u;

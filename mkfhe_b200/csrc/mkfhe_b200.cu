@@ -744,6 +744,63 @@ int mkfhe_keygen_ksk_mklwe(mkfhe_ctx* ctx, const uint32_t* A, const uint32_t* e,
     return MKFHE_OK;
 }
 
+// ---- batched Encrypt with caller-supplied noise ----
+int mkfhe_encrypt_mntru(mkfhe_ctx* ctx, const uint32_t* finv, const uint32_t* e, const uint8_t* m, uint32_t pmod, uint32_t* ct_out,
+                        uint64_t batch) {
+    if (!ctx || !finv || !e || !m || !ct_out || pmod == 0) return MKFHE_EINVAL;
+    const mkfhe_params& p = ctx->p;
+    if (p.scheme != MKFHE_SCHEME_MNTRU) return fail(ctx, MKFHE_EINVAL, "context is not MNTRU");
+    if (batch == 0) return MKFHE_OK;
+    if (batch > 0x3fffffull) return fail(ctx, MKFHE_EINVAL, "batch too large");
+    const size_t words = size_t(batch) * p.k * p.n;
+    CU(cudaSetDevice(ctx->device));
+    TmpBuf tmp;
+    uint32_t *d_f, *d_e, *d_out;
+    uint8_t* d_m;
+    CU(tmp.get(&d_f, size_t(p.k) * p.n * p.n));
+    CU(tmp.get(&d_e, words));
+    CU(tmp.get(&d_out, words));
+    CU(tmp.get(&d_m, size_t(batch)));
+    CU(cudaMemcpyAsync(d_f, finv, size_t(p.k) * p.n * p.n * 4, cudaMemcpyDefault, ctx->stream));
+    CU(cudaMemcpyAsync(d_e, e, words * 4, cudaMemcpyDefault, ctx->stream));
+    CU(cudaMemcpyAsync(d_m, m, size_t(batch), cudaMemcpyDefault, ctx->stream));
+    const dim3 grid((p.n + 63) / 64, unsigned((batch + 63) / 64), p.k);
+    encrypt_mntru_kernel<<<grid, 256, 0, ctx->stream>>>(ctx->d, d_f, d_e, d_m, pmod, d_out, uint32_t(batch));
+    ctx->launches++;
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(ct_out, d_out, words * 4, cudaMemcpyDefault, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return MKFHE_OK;
+}
+
+int mkfhe_encrypt_mklwe(mkfhe_ctx* ctx, const uint32_t* s, const uint32_t* a, const uint32_t* err, const uint8_t* m, uint32_t pmod,
+                        uint32_t* b_out, uint64_t batch) {
+    if (!ctx || !s || !a || !err || !m || !b_out || pmod == 0) return MKFHE_EINVAL;
+    const mkfhe_params& p = ctx->p;
+    if (p.scheme != MKFHE_SCHEME_MKLWE) return fail(ctx, MKFHE_EINVAL, "context is not MKLWE");
+    if (batch == 0) return MKFHE_OK;
+    const size_t words = size_t(batch) * p.k * p.n;
+    CU(cudaSetDevice(ctx->device));
+    TmpBuf tmp;
+    uint32_t *d_s, *d_a, *d_err, *d_b;
+    uint8_t* d_m;
+    CU(tmp.get(&d_s, size_t(p.k) * p.n));
+    CU(tmp.get(&d_a, words));
+    CU(tmp.get(&d_err, size_t(batch)));
+    CU(tmp.get(&d_b, size_t(batch)));
+    CU(tmp.get(&d_m, size_t(batch)));
+    CU(cudaMemcpyAsync(d_s, s, size_t(p.k) * p.n * 4, cudaMemcpyDefault, ctx->stream));
+    CU(cudaMemcpyAsync(d_a, a, words * 4, cudaMemcpyDefault, ctx->stream));
+    CU(cudaMemcpyAsync(d_err, err, size_t(batch) * 4, cudaMemcpyDefault, ctx->stream));
+    CU(cudaMemcpyAsync(d_m, m, size_t(batch), cudaMemcpyDefault, ctx->stream));
+    encrypt_mklwe_kernel<<<unsigned((batch * 32 + 255) / 256), 256, 0, ctx->stream>>>(ctx->d, d_s, d_a, d_err, d_m, pmod, d_b, batch);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    CU(cudaMemcpyAsync(b_out, d_b, size_t(batch) * 4, cudaMemcpyDefault, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return MKFHE_OK;
+}
+
 // ---- binary key file (format in keyfile.h) ----
 int mkfhe_keyfile_write(const char* path, const mkfhe_params* p, const uint32_t* bk, uint64_t bk_words, const uint32_t* pkey,
                         uint64_t pkey_words, const uint32_t* kskA, uint64_t kskA_words, const uint32_t* kskB, uint64_t kskB_words,

@@ -142,3 +142,21 @@ def extract_ksk_mklwe_noise(p, A, B, s, sN_q, small=64):
         assert np.abs(e).max() < small
         out[u] = (e.reshape(-1) % q).astype(np.uint32)
     return out
+
+
+# ---- Encrypt: numpy restatements, the checker for the GPU's batched Encrypt ----
+def encrypt_mntru_np(p, finv, e, m, pmod=4):
+    """mntru-pke.cpp:158-205: c[u] = (e[u] + [u == 0] (m mod p)(q/p) e_0) x F_u^-1 mod q.  e [B][k][n], m [B]."""
+    q = p.q
+    e = np.asarray(e, dtype=np.int64).reshape(-1, p.k, p.n) % q
+    e[:, 0, 0] = (e[:, 0, 0] + (np.asarray(m, dtype=np.int64) % pmod) * (q // pmod)) % q
+    finv = np.asarray(finv, dtype=np.int64).reshape(p.k, p.n, p.n) % q
+    return np.stack([(e[:, u, :] @ finv[u]) % q for u in range(p.k)], axis=1).astype(np.uint32)
+
+
+def encrypt_mklwe_np(p, s, a, err, m, pmod=4):
+    """mklwe-pke.cpp:36-64: b = (m mod p)(q/p) + err + sum_u <a_u, s_u> mod q.  a [B][k][n], err [B], m [B]."""
+    q = p.q
+    a = np.asarray(a, dtype=np.int64).reshape(-1, p.k * p.n) % q
+    s = np.asarray(s, dtype=np.int64).reshape(p.k * p.n) % q
+    return (((np.asarray(m, dtype=np.int64) % pmod) * (q // pmod) + np.asarray(err, dtype=np.int64) + a @ s) % q).astype(np.uint32)

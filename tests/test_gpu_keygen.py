@@ -139,3 +139,44 @@ def test_ksk_keygen_full_size_mntru():
     assert (np.asarray(out).ravel() == eo).all() and r.decrypt(eo, 0) == 0
     ctx.close()
     r.close()
+
+
+@pytest.mark.parametrize("name", sorted(TOY))
+def test_encrypt_batch_reproduces_reference_ciphertexts(name):
+    """Batched Encrypt: the noise of ciphertexts the reference encrypted is recovered with the secret
+    (MNTRU: e = c x F - message; MKLWE: err = b - message - <a, s>), and the GPU fed with it returns the reference's
+    ciphertexts; random noise is checked against the numpy restatement."""
+    from gpu_util import ctx_from_params
+    from keygen_util import _cen, encrypt_mklwe_np, encrypt_mntru_np
+
+    r = refapi.Ref(*TOY[name])
+    r.keygen()
+    p = params_from_ref(r.p)
+    ctx = ctx_from_params(p)
+    q = p.q
+    bits = np.array([0, 1, 1, 0, 1, 0, 0, 1, 1], dtype=np.uint8)
+    cts = [r.encrypt(int(b)) for b in bits]
+    ct = np.array([c for c, _ in cts], dtype=np.uint32).reshape(len(bits), p.k, p.n)
+    bs = np.array([b for _, b in cts], dtype=np.uint32)
+    rng = np.random.default_rng(12)
+    if p.scheme == 0:
+        F, Fi = r.mntru_F(False).astype(np.int64), r.mntru_F(True)
+        e = np.stack([(ct[:, u, :].astype(np.int64) @ F[u]) % q for u in range(p.k)], axis=1)
+        e[:, 0, 0] = (e[:, 0, 0] - bits.astype(np.int64) * (q // 4)) % q
+        assert np.abs(_cen(e, q)).max() < 16
+        assert (ctx.EncryptBatch(bits, e, Fi) == ct).all()
+        e2 = rng.integers(0, q, size=(70, p.k, p.n), dtype=np.uint32)
+        m2 = rng.integers(0, 2, size=70, dtype=np.uint8)
+        assert (ctx.EncryptBatch(m2, e2, Fi) == encrypt_mntru_np(p, Fi, e2, m2)).all()
+    else:
+        s = r.sk().reshape(p.k, p.n)
+        err = (bs.astype(np.int64) - bits.astype(np.int64) * (q // 4)
+               - ct.reshape(len(bits), -1).astype(np.int64) @ s.reshape(-1).astype(np.int64)) % q
+        assert np.abs(_cen(err, q)).max() < 16
+        assert (ctx.EncryptBatch(bits, err, s, a=ct) == bs).all()
+        a2 = rng.integers(0, q, size=(70, p.k, p.n), dtype=np.uint32)
+        err2 = rng.integers(0, q, size=70, dtype=np.uint32)
+        m2 = rng.integers(0, 2, size=70, dtype=np.uint8)
+        assert (ctx.EncryptBatch(m2, err2, s, a=a2) == encrypt_mklwe_np(p, s, a2, err2, m2)).all()
+    ctx.close()
+    r.close()
