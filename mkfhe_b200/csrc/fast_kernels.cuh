@@ -320,11 +320,11 @@ __device__ __forceinline__ uint4 key4(const uint32_t* ev1, const uint32_t* ev2, 
     return a;
 }
 
-// Shared memory of one gate: a[k][N] | E1[2][FNP] | E2[FNP] (absent when ALIAS) | crot[k*n] (u16).
+// Shared memory of one gate: a[k][N] | E1[2][FNP] | E2[FNP] (absent when ALIAS) | Ms[N] (XZW: Q - X^-c per slot) | crot[k*n] (u16).
 // ALIAS: the inverse transform exchanges through E1[0] instead of its own buffer (one more block barrier per iteration);
 // chosen by the host only when the separate buffer does not fit (see fast_use_alias).
-__host__ __device__ inline size_t fast_smem_bytes(uint32_t k, uint32_t n, bool alias) {
-    return (size_t(k) * FN + (alias ? 2 : 3) * FNP) * 4 + ((size_t(k) * n * 2 + 15) & ~size_t(15));
+__host__ __device__ inline size_t fast_smem_bytes(uint32_t k, uint32_t n, bool alias, bool xzw) {
+    return (size_t(k) * FN + (alias ? 2 : 3) * FNP + (xzw ? FN : 0)) * 4 + ((size_t(k) * n * 2 + 15) & ~size_t(15));
 }
 
 // psi^e for the 4 slots 8 tid + 4 ch + q of X^x (x = c or -c mod 2N): slot j evaluates X at psi^(2 bitrev(j) + 1), and
@@ -343,7 +343,7 @@ __device__ __forceinline__ void monomial4(const uint32_t* psipow, uint32_t e0, u
 template <bool XZW, bool FIRST>
 __device__ __forceinline__ void key_mac4(const DevCtx& P, const uint32_t* k1p, const uint32_t* k2p, const uint32_t* evsp, uint32_t c,
                                          uint32_t cneg, uint32_t e0p, uint32_t e0n, int ch, const uint32_t (&D)[2][8],
-                                         uint32_t (&x4)[4]) {
+                                         uint32_t (&x4)[4], const uint32_t* Ms = nullptr) {
     constexpr uint32_t N = FN, KCH = FN / 2;  // key polynomials are stored in register order: chunk ch of thread t at
                                               // words KCH ch + 4 t .. + 3 (fast_permute_keys), so a warp load is 512 contiguous bytes
     const uint32_t Q = P.mod.Q;
@@ -374,8 +374,17 @@ __device__ __forceinline__ void key_mac4(const DevCtx& P, const uint32_t* k1p, c
         // sum_j D_j (ev1_j - ev2_j X^-c) = sum_j D_j ev1_j + (Q - X^-c) * redc(sum_j D_j ev2_j): two 64-bit sums,
         // two reductions, five wide products per slot (mk-acc-xzw.cpp:322-325 assembles the key first: 2 more
         // reductions and the conditional subtractions)
-        uint32_t mn[4];
-        monomial4(P.psipow, e0n, cneg, ch, mn);
+        // Q - X^-c at the 4 slots: from the per-step staging in shared memory (Ms: this thread's own 8 values, written once
+        // per step by fast_step), else gathered from the power table
+        uint32_t mq[4];
+        if (Ms != nullptr) {
+            const uint4 v = *reinterpret_cast<const uint4*>(Ms + KCH * ch);
+            mq[0] = v.x; mq[1] = v.y; mq[2] = v.z; mq[3] = v.w;
+        } else {
+            monomial4(P.psipow, e0n, cneg, ch, mq);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) mq[q] = Q - mq[q];
+        }
         const uint4 a0 = ldg4_stream(k1p + KCH * ch), a1 = ldg4_stream(k1p + 2 * N + KCH * ch);
         const uint4 b0 = ldg4_stream(k2p + KCH * ch), b1 = ldg4_stream(k2p + 2 * N + KCH * ch);
         const uint32_t a0v[4] = {a0.x, a0.y, a0.z, a0.w}, a1v[4] = {a1.x, a1.y, a1.z, a1.w};
@@ -387,7 +396,7 @@ __device__ __forceinline__ void key_mac4(const DevCtx& P, const uint32_t* k1p, c
             const uint32_t q2 = static_cast<uint32_t>(s2) * P.mod.qinv_neg;
             const uint32_t r2 = static_cast<uint32_t>((s2 + static_cast<uint64_t>(q2) * Q) >> 32);  // < 3Q
             const uint64_t s1 = static_cast<uint64_t>(d0) * a0v[q] + static_cast<uint64_t>(d1) * a1v[q] +
-                                static_cast<uint64_t>(r2) * (Q - mn[q]);  // < 51 Q^2 < 2^60
+                                static_cast<uint64_t>(r2) * mq[q];  // < 51 Q^2 < 2^60
             const uint32_t q1 = static_cast<uint32_t>(s1) * P.mod.qinv_neg;
             x4[q] = static_cast<uint32_t>((s1 + static_cast<uint64_t>(q1) * Q) >> 32);  // < 3Q
         }
@@ -405,8 +414,8 @@ __device__ __forceinline__ void key_mac4(const DevCtx& P, const uint32_t* k1p, c
 // the result REPLACES it.  Runs once per gate, so it is a separate instantiation instead of selects in the hot loop.
 // Entry: a[] visible to all threads, nobody still reading E1 / E2.  Exit: as entry (ends with a block barrier).
 template <bool XZW, bool FIRST, bool ALIAS>
-__device__ __forceinline__ void fast_step(const DevCtx& P, const FastTables& T, uint32_t* a, uint32_t* E1, uint32_t* E2, uint32_t s,
-                                          uint32_t c, uint32_t tid) {
+__device__ __forceinline__ void fast_step(const DevCtx& P, const FastTables& T, uint32_t* a, uint32_t* E1, uint32_t* E2, uint32_t* Ms,
+                                          uint32_t s, uint32_t c, uint32_t tid) {
     constexpr uint32_t N = FN, M = 2 * FN;
     const uint32_t Q = P.mod.Q, k = P.k, n = P.n, g = P.gbits;
     const uint32_t u = FIRST ? 0u : s / n, i = FIRST ? 0u : s - u * n;
@@ -419,6 +428,19 @@ __device__ __forceinline__ void fast_step(const DevCtx& P, const FastTables& T, 
     const uint32_t e0n = cneg * (2 * brv8 + 1), e0p = c * (2 * brv8 + 1);
     uint32_t keep[8];  // V while parties are processed, then X of the key owner
     uint32_t y[8];
+    // XZW: Q - X^-c at this thread's 8 slots is the same in all k + 1 iterations of the step.  Gathering it from the power
+    // table costs 8 scattered 4-byte loads per iteration (up to 32 L1 wavefronts each: as much LSU traffic as everything
+    // else in the iteration); it is gathered once per step instead and parked in shared memory at this thread's own words
+    // (register order, so it comes back as two 128-bit loads; no barrier: nobody else reads them).
+    uint32_t* Mt = Ms + 4 * tid;
+    if (XZW && !FIRST) {
+#pragma unroll
+        for (int ch = 0; ch < 2; ++ch) {
+            uint32_t mq[4];
+            monomial4(P.psipow, e0n, cneg, ch, mq);
+            *reinterpret_cast<uint4*>(Mt + (N / 2) * ch) = make_uint4(Q - mq[0], Q - mq[1], Q - mq[2], Q - mq[3]);
+        }
+    }
 #pragma unroll 1
     for (uint32_t it = 0; it <= k; ++it) {
         uint32_t D[2][8];
@@ -441,7 +463,7 @@ __device__ __forceinline__ void fast_step(const DevCtx& P, const FastTables& T, 
 #pragma unroll
         for (int ch = 0; ch < 2; ++ch) {
             uint32_t x4[4];  // <D, key> at slots 8 tid + 4 ch + q, < 3Q
-            key_mac4<XZW, FIRST>(P, k1p, k2p, evs + col * N, c, cneg, e0p, e0n, ch, D, x4);
+            key_mac4<XZW, FIRST>(P, k1p, k2p, evs + col * N, c, cneg, e0p, e0n, ch, D, x4, (XZW && !FIRST) ? Mt : nullptr);
             if (it < k) {
                 const uint4 q0 = ldg4(pk + (N / 2) * ch), q1 = ldg4(pk + N + (N / 2) * ch);
                 const uint32_t pp0[4] = {q0.x, q0.y, q0.z, q0.w}, pp1[4] = {q1.x, q1.y, q1.z, q1.w};
@@ -497,14 +519,15 @@ __global__ void __launch_bounds__(FT, MINB) blind_rotate_fast(const DevCtx P, co
     uint32_t* a = sm;
     uint32_t* E1 = a + k * N;
     uint32_t* E2 = E1 + 2 * FNP;
-    uint16_t* crot = reinterpret_cast<uint16_t*>(ALIAS ? E2 : E2 + FNP);
+    uint32_t* Ms = ALIAS ? E2 : E2 + FNP;
+    uint16_t* crot = reinterpret_cast<uint16_t*>(XZW ? Ms + N : Ms);
 
     rotate_prologue<GATE>(P, io, blockIdx.x, a, crot);
-    fast_step<XZW, true, ALIAS>(P, T, a, E1, E2, 0, crot[0], tid);
+    fast_step<XZW, true, ALIAS>(P, T, a, E1, E2, Ms, 0, crot[0], tid);
     for (uint32_t s = 1; s < k * n; ++s) {
         const uint32_t c = crot[s];
         if (c == 0) continue;  // X^0 - 1 = 0: the step leaves acc unchanged
-        fast_step<XZW, false, ALIAS>(P, T, a, E1, E2, s, c, tid);
+        fast_step<XZW, false, ALIAS>(P, T, a, E1, E2, Ms, s, c, tid);
     }
     rotate_epilogue<GATE>(P, io, blockIdx.x, a, E1);
 }
@@ -734,7 +757,7 @@ struct FastState {
 
 inline bool fast_supported(const DevCtx& d) {
     return d.N == FN && d.ell == 2 && d.mod.Q < (1u << 27) && d.gbits >= 2 && d.gbits <= 16 &&
-           fast_smem_bytes(d.k, d.n, true) <= 227 * 1024;
+           fast_smem_bytes(d.k, d.n, true, d.variant == 0) <= 227 * 1024;
 }
 
 // N = 1024 with a modulus the lazy butterflies can take: the batched transform (mkfhe_ntt, config 5) runs on the HALF path
@@ -841,7 +864,7 @@ inline int fast_gates_per_sm(size_t smem) { return int(std::min<size_t>(4, (227 
 // the fallback for party counts whose separate buffer does not fit shared memory at all.
 inline bool fast_use_alias(const DevCtx& d) {
     if (const char* e = getenv("MKFHE_FAST_ALIAS")) return e[0] == '1';
-    return fast_smem_bytes(d.k, d.n, false) > 227 * 1024;
+    return fast_smem_bytes(d.k, d.n, false, d.variant == 0) > 227 * 1024;
 }
 
 // party-parallel groups per gate, overridable for experiments with MKFHE_GROUPS.  Measured on B200 (profiles/r1_s17_*):
@@ -861,7 +884,7 @@ inline cudaError_t fast_blind_rotate(FastState& F, const DevCtx& d, bool gate, c
     const bool xzw = d.variant == 0;
     const uint32_t G = fast_groups(d);
     const bool alias = G > 1 ? grouped_smem_bytes(d.k, d.n, G, false) > 227 * 1024 : fast_use_alias(d);
-    const size_t smem = G > 1 ? grouped_smem_bytes(d.k, d.n, G, alias) : fast_smem_bytes(d.k, d.n, alias);
+    const size_t smem = G > 1 ? grouped_smem_bytes(d.k, d.n, G, alias) : fast_smem_bytes(d.k, d.n, alias, xzw);
     auto launch = [&](auto kern) -> cudaError_t {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
         if (e != cudaSuccess) return e;
@@ -871,6 +894,9 @@ inline cudaError_t fast_blind_rotate(FastState& F, const DevCtx& d, bool gate, c
     cudaError_t e;
     const int sel = (gate ? 4 : 0) | (xzw ? 2 : 0) | (alias ? 1 : 0);
     int minb = G > 1 ? 1 : std::max(2, fast_gates_per_sm(smem));
+    // XZW at 64 registers spills in the step loop; 3 gates per SM with 80 registers measured 3% faster than 4 with 64
+    // (16.66k vs 16.17k gates/s, boolean-mkntru k = 2, profiles/r1_s28_xzw_quick.txt); XZW_B measured equal, stays at 4
+    if (xzw && minb > 3) minb = 3;
     if (const char* ev = getenv("MKFHE_MINB")) minb = std::min(4, std::max(2, atoi(ev)));
     if (alias) minb = 4;  // the fallback layout is built for the 64-register budget only
     if (G > 1) {
