@@ -38,6 +38,9 @@ struct FastTables {
     const uint2* tw2;     // [N]  forward twiddles, OpenFHE order: psi^i at bitrev(i), as Shoup pairs (w, floor(w 2^32 / Q))
     const uint2* itw2;    // [N]  cyclic inverse (DIT) twiddles: itw2[t + m] = omega^(-m N / 2t), m < t, t = 1, 2, .., N/2
     const uint2* scale2;  // [N]  psi^-i / N  (the twist and the 1/N of the inverse, folded into one Shoup multiply)
+    const uint4* tw4;     // [3][256] the six twiddles of thread t in the last forward pass, as three 128-bit words:
+                          // (tw2[512+2t], tw2[513+2t]) | (tw2[1024+4t], tw2[1025+4t]) | (tw2[1026+4t], tw2[1027+4t]) -- one
+                          // coalesced load each (16-byte lane stride) instead of six 8-byte loads at 16/32-byte stride
     uint2 twA[8];         // tw2[0..7]: the first forward pass uses the same twiddles in every thread -> kernel-parameter constants
     uint2 itwA[4];        // itw2[0..3]
     uint32_t zero;        // 0, opaque to the compiler: makes "u + t" a three-input add, which ptxas maps to IADD3 (alu pipe)
@@ -175,16 +178,20 @@ __device__ __forceinline__ void fwd_ntt_regs(uint32_t (&x)[NP][8], uint32_t* E, 
             x[p][4 * c + 0] = v.x; x[p][4 * c + 1] = v.y; x[p][4 * c + 2] = v.z; x[p][4 * c + 3] = v.w;
         }
     // pass 4: t = 2, 1  (m = 512, 1024; block = (tid << (s + 1)) + (i >> (2 - s)))
-#pragma unroll
-    for (int s = 0; s < 2; ++s) {
-        const int h = 2 >> s;
-        const uint2* tws = T.tw2 + (512 << s) + (tid << (s + 1));
+    {
+        const uint4 wa = __ldg(T.tw4 + tid), wb = __ldg(T.tw4 + 256 + tid), wc = __ldg(T.tw4 + 512 + tid);
+        const uint2 w0[2] = {make_uint2(wa.x, wa.y), make_uint2(wa.z, wa.w)};
+        const uint2 w1[4] = {make_uint2(wb.x, wb.y), make_uint2(wb.z, wb.w), make_uint2(wc.x, wc.y), make_uint2(wc.z, wc.w)};
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-            if (i & h) continue;
-            const uint2 w = __ldg(tws + (i >> (2 - s)));
+            if (i & 2) continue;
 #pragma unroll
-            for (int p = 0; p < NP; ++p) MKFHE_BFLY(x[p][i], x[p][i + h], w);
+            for (int p = 0; p < NP; ++p) MKFHE_BFLY(x[p][i], x[p][i + 2], w0[i >> 2]);
+        }
+#pragma unroll
+        for (int i = 0; i < 8; i += 2) {
+#pragma unroll
+            for (int p = 0; p < NP; ++p) MKFHE_BFLY(x[p][i], x[p][i + 1], w1[i >> 1]);
         }
     }
 }
@@ -750,6 +757,7 @@ __global__ void __launch_bounds__(256) butterfly_peak_kernel(uint32_t* sink, uin
 struct FastState {
     FastTables T{};
     uint2 *d_tw2{nullptr}, *d_itw2{nullptr}, *d_scale2{nullptr};
+    uint4* d_tw4{nullptr};
     uint2 one2{};
     int sms{148};
     bool half{false};  // tables for N = 1024 (two polynomials per 2048-word pass): only the batched transform uses them
@@ -817,8 +825,18 @@ inline cudaError_t fast_init(FastState& F, const DevCtx& d, uint32_t psi, cudaSt
         *dev_bytes += N * sizeof(uint2);
         if ((e = cudaMemcpyAsync(*pr.first, pr.second->data(), N * sizeof(uint2), cudaMemcpyHostToDevice, st)) != cudaSuccess) return e;
     }
+    std::vector<uint4> t4(3 * 256);
+    for (uint32_t t = 0; t < 256; ++t) {
+        auto q4 = [&](uint32_t i) { return make_uint4(tw[i].x, tw[i].y, tw[i + 1].x, tw[i + 1].y); };
+        t4[t] = q4(512 + 2 * t);
+        t4[256 + t] = q4(1024 + 4 * t);
+        t4[512 + t] = q4(1026 + 4 * t);
+    }
+    if ((e = cudaMalloc(reinterpret_cast<void**>(&F.d_tw4), t4.size() * sizeof(uint4))) != cudaSuccess) return e;
+    *dev_bytes += t4.size() * sizeof(uint4);
+    if ((e = cudaMemcpyAsync(F.d_tw4, t4.data(), t4.size() * sizeof(uint4), cudaMemcpyHostToDevice, st)) != cudaSuccess) return e;
     if ((e = cudaStreamSynchronize(st)) != cudaSuccess) return e;
-    F.T.tw2 = F.d_tw2; F.T.itw2 = F.d_itw2; F.T.scale2 = F.d_scale2;
+    F.T.tw2 = F.d_tw2; F.T.itw2 = F.d_itw2; F.T.scale2 = F.d_scale2; F.T.tw4 = F.d_tw4;
     for (int i = 0; i < 8; ++i) F.T.twA[i] = tw[i];
     for (int i = 0; i < 4; ++i) F.T.itwA[i] = itw[i];
     F.T.zero = 0;
@@ -832,6 +850,7 @@ inline cudaError_t fast_init(FastState& F, const DevCtx& d, uint32_t psi, cudaSt
 inline void fast_destroy(FastState& F) {
     for (uint2* p : {F.d_tw2, F.d_itw2, F.d_scale2})
         if (p) cudaFree(p);
+    if (F.d_tw4) cudaFree(F.d_tw4);
     F = FastState{};
 }
 // Key polynomials -> register order, in place, one CTA per polynomial: thread t of a gate holds the slots 8t .. 8t+7 after
