@@ -43,6 +43,8 @@ struct FastTables {
                           // coalesced load each (16-byte lane stride) instead of six 8-byte loads at 16/32-byte stride
     uint2 twA[8];         // tw2[0..7]: the first forward pass uses the same twiddles in every thread -> kernel-parameter constants
     uint2 itwA[4];        // itw2[0..3]
+    uint2 twB[64];        // tw2[0..63]: the second forward pass indexes them by warp number (uniform: constant-bank loads, off the LSU)
+    uint2 itwB[32];       // itw2[0..31]: the second inverse pass (4 distinct addresses per warp)
     uint32_t zero;        // 0, opaque to the compiler: makes "u + t" a three-input add, which ptxas maps to IADD3 (alu pipe)
                           // instead of IMAD.IADD (fma pipe, the saturated one: profiles/r1_fast_v2_blind_rotate.txt)
 };
@@ -131,11 +133,11 @@ __device__ __forceinline__ void fwd_ntt_regs(uint32_t (&x)[NP][8], uint32_t* E, 
 #pragma unroll
     for (int s = 0; s < 3; ++s) {
         const int h = 4 >> s;
-        const uint2* tws = T.tw2 + (8 << s) + (wrp << s);
+        const uint32_t twi = (8 << s) + (wrp << s);
 #pragma unroll
         for (int r = 0; r < 8; ++r) {
             if (r & h) continue;
-            const uint2 w = __ldg(tws + (r >> (3 - s)));
+            const uint2 w = T.twB[twi + (r >> (3 - s))];
 #pragma unroll
             for (int p = 0; p < NP; ++p) MKFHE_BFLY(x[p][r], x[p][r + h], w);
         }
@@ -233,11 +235,11 @@ __device__ __forceinline__ void inv_ntt_regs(uint32_t (&x)[8], uint32_t* E, cons
 #pragma unroll
     for (int s = 0; s < 3; ++s) {
         const int h = 1 << s;
-        const uint2* tws = T.itw2 + 4 * h + lo2;
+        const uint32_t twi = 4 * h + lo2;
 #pragma unroll
         for (int r = 0; r < 8; ++r) {
             if (r & h) continue;
-            const uint2 w = __ldg(tws + 4 * (r & (h - 1)));
+            const uint2 w = T.itwB[twi + 4 * (r & (h - 1))];
             MKFHE_BFLY(x[r], x[r + h], w);
         }
     }
@@ -839,6 +841,8 @@ inline cudaError_t fast_init(FastState& F, const DevCtx& d, uint32_t psi, cudaSt
     F.T.tw2 = F.d_tw2; F.T.itw2 = F.d_itw2; F.T.scale2 = F.d_scale2; F.T.tw4 = F.d_tw4;
     for (int i = 0; i < 8; ++i) F.T.twA[i] = tw[i];
     for (int i = 0; i < 4; ++i) F.T.itwA[i] = itw[i];
+    for (int i = 0; i < 64; ++i) F.T.twB[i] = tw[i];
+    for (int i = 0; i < 32; ++i) F.T.itwB[i] = itw[i];
     F.T.zero = 0;
     F.one2 = pair(1);
     F.half = half;
