@@ -755,6 +755,73 @@ __global__ void __launch_bounds__(256) butterfly_peak_kernel(uint32_t* sink, uin
     if (r == 0x12345678u) sink[0] = r;
 }
 
+// ---- bootstrapping-key generation on the register-resident transforms (N = 2048; semantics of keygen_bk_kernel) ----------
+// One CTA per evk: NTT(r), then per digit NTT(e0_j), NTT(e1_j) as one two-polynomial transform, canonicalised, and the
+// pointwise assembly on the 8 slots the thread holds; the evk leaves as 128-bit stores.  R[j] (slot j of NTT(r), the
+// reference's scalar "skrPoly[i]") is published through shared memory by thread 0, which holds slots 0..7.
+__global__ void __launch_bounds__(FT, 2) keygen_bk_fast(const DevCtx P, const FastTables T, const uint2 one2, const GadgetPow G,
+                                                        const uint32_t* __restrict__ sinv_m, const uint32_t* __restrict__ crs_m,
+                                                        const uint32_t* __restrict__ r, const uint32_t* __restrict__ e,
+                                                        const uint8_t* __restrict__ m, uint32_t* __restrict__ out) {
+    __shared__ __align__(16) uint32_t E[2 * FNP];
+    __shared__ uint32_t Rlow[8];
+    constexpr uint32_t N = FN;
+    const uint32_t Q = P.mod.Q, ell = P.ell, n = P.n, tid = threadIdx.x;
+    const uint32_t ev = blockIdx.x, last = gridDim.x - 1;
+    uint32_t u = 0;
+    bool kdm = true;
+    if (ev != last) {
+        u = ev / (P.S * n);
+        kdm = (u == 0 && (ev - u * P.S * n) % n == 0);
+    }
+    const bool msg = m[ev] != 0;
+    uint32_t R[1][8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q) R[0][q] = r[size_t(ev) * N + tid + 256 * q];
+    fwd_ntt_regs<1>(R, E, T, Q, tid);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) R[0][i] = fold1(shoup_lazy(R[0][i], one2, Q), Q);
+    if (tid == 0) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) Rlow[i] = R[0][i];
+    }
+    uint32_t sv[8];
+    {
+        const uint4 a = ldg4(sinv_m + size_t(u) * N + 8 * tid), b = ldg4(sinv_m + size_t(u) * N + 8 * tid + 4);
+        sv[0] = a.x; sv[1] = a.y; sv[2] = a.z; sv[3] = a.w; sv[4] = b.x; sv[5] = b.y; sv[6] = b.z; sv[7] = b.w;
+    }
+    __syncthreads();  // Rlow visible; E free again
+    for (uint32_t j = 0; j < ell; ++j) {
+        uint32_t X[2][8];
+        const uint32_t* ee = e + (size_t(ev) * ell + j) * 2 * N;
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            X[0][q] = ee[tid + 256 * q];
+            X[1][q] = ee[N + tid + 256 * q];
+        }
+        fwd_ntt_regs<2>(X, E, T, Q, tid);
+        const uint32_t Rj = Rlow[j];
+        const uint32_t* cj = crs_m + size_t(j) * N + 8 * tid;
+        const uint4 c0 = ldg4(cj), c1 = ldg4(cj + 4);
+        const uint32_t cv[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+        uint32_t d[8], f[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const uint32_t e0 = fold1(shoup_lazy(X[0][i], one2, Q), Q), e1 = fold1(shoup_lazy(X[1][i], one2, Q), Q);
+            f[i] = montmul(addmod(e1, montmul(R[0][i], G.mont[j], P.mod), Q), sv[i], P.mod);
+            uint32_t dd = e0;
+            if (msg) dd = addmod(dd, kdm ? montmul(G.plain[j], sv[i], P.mod) : G.plain[j], Q);
+            d[i] = addmod(dd, montmul(Rj, cv[i], P.mod), Q);
+        }
+        uint32_t* o = out + (size_t(ev) * ell + j) * 2 * N + 8 * tid;
+        *reinterpret_cast<uint4*>(o) = make_uint4(d[0], d[1], d[2], d[3]);
+        *reinterpret_cast<uint4*>(o + 4) = make_uint4(d[4], d[5], d[6], d[7]);
+        *reinterpret_cast<uint4*>(o + N) = make_uint4(f[0], f[1], f[2], f[3]);
+        *reinterpret_cast<uint4*>(o + N + 4) = make_uint4(f[4], f[5], f[6], f[7]);
+        __syncthreads();  // E is reused by the next digit's transform
+    }
+}
+
 // ---- host side ------------------------------------------------------------------------------------------------------
 struct FastState {
     FastTables T{};
@@ -953,6 +1020,14 @@ inline cudaError_t fast_blind_rotate(FastState& F, const DevCtx& d, bool gate, c
 #undef MKFHE_LAUNCH_MINB
     }
     if (e != cudaSuccess) return e;
+    ++*launches;
+    return cudaGetLastError();
+}
+
+inline cudaError_t fast_keygen_bk(FastState& F, const DevCtx& d, const GadgetPow& G, const uint32_t* sinv_m, const uint32_t* crs_m,
+                                  const uint32_t* r, const uint32_t* e, const uint8_t* m, uint32_t* out, uint32_t evks, cudaStream_t st,
+                                  uint64_t* launches) {
+    keygen_bk_fast<<<evks, FT, 0, st>>>(d, F.T, F.one2, G, sinv_m, crs_m, r, e, m, out);
     ++*launches;
     return cudaGetLastError();
 }

@@ -655,9 +655,15 @@ int mkfhe_keygen_bk(mkfhe_ctx* ctx, const uint32_t* sinv, const uint32_t* crs, c
         G.plain[j] = g;
         G.mont[j] = h_mulmod(g, R, Q);
     }
-    CU(cudaFuncSetAttribute(keygen_bk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
-    keygen_bk_kernel<<<unsigned(E), 256, smem, ctx->stream>>>(ctx->d, G, d_sinv, d_crs, d_r, d_e, d_m, d_out);
-    ctx->launches += 3;
+    if (ctx->use_fast) {  // N = 2048: register-resident transforms
+        cudaError_t ce = fast_keygen_bk(ctx->fast, ctx->d, G, d_sinv, d_crs, d_r, d_e, d_m, d_out, unsigned(E), ctx->stream, &ctx->launches);
+        if (ce != cudaSuccess) return fail(ctx, MKFHE_ECUDA, "fast_keygen_bk: %s", cudaGetErrorString(ce));
+    } else {
+        CU(cudaFuncSetAttribute(keygen_bk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem)));
+        keygen_bk_kernel<<<unsigned(E), 256, smem, ctx->stream>>>(ctx->d, G, d_sinv, d_crs, d_r, d_e, d_m, d_out);
+        ctx->launches++;
+    }
+    ctx->launches += 2;
     CU(cudaGetLastError());
     if (bk_out) CU(cudaMemcpyAsync(bk_out, d_out, words * 4, cudaMemcpyDefault, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
