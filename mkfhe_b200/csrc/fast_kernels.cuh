@@ -548,14 +548,17 @@ __global__ void __launch_bounds__(FT, MINB) blind_rotate_fast(const DevCtx P, co
 // independent except for sumV, which the groups accumulate in shared memory with atomic adds (sums of canonical residues:
 // k Q < 2^32).  Then one group runs the sumV term (:273-289) while the others wait: a step takes ceil(k / G) + 1 transform
 // rounds instead of k + 1.  Group barriers are named barriers (1 + group); block barriers separate the phases.
-// Shared memory: a[k][N] | per group E1[2][FNP] | E2[FNP] (absent when ALIAS) | Vs[N] | crot[k*n] (u16).
+// Shared memory: a[k][N] | per group E1[2][FNP] | E2[FNP] (absent when ALIAS) | Vs[N] | Ms[N] (XZW: Q - X^-c per slot, shared by
+// the groups).  The rotation amounts are not kept on chip (k = 16 needs the space): rotation_amount() re-derives the step's
+// amount from the gate's inputs.
 __host__ __device__ inline size_t grouped_smem_bytes(uint32_t k, uint32_t n, uint32_t G, bool alias) {
-    return (size_t(k) * FN + size_t(G) * (alias ? 2 : 3) * FNP + FN) * 4 + ((size_t(k) * n * 2 + 15) & ~size_t(15));
+    (void)n;
+    return (size_t(k) * FN + size_t(G) * (alias ? 2 : 3) * FNP + 2 * FN) * 4;
 }
 
 template <bool XZW, bool FIRST, bool ALIAS>
 __device__ __forceinline__ void grouped_step(const DevCtx& P, const FastTables& T, uint32_t* a, uint32_t* E1, uint32_t* E2, uint32_t* Vs,
-                                             uint32_t s, uint32_t c, uint32_t tid, uint32_t grp, uint32_t G) {
+                                             uint32_t* Ms, uint32_t s, uint32_t c, uint32_t tid, uint32_t grp, uint32_t G) {
     constexpr uint32_t N = FN, M = 2 * FN;
     const uint32_t Q = P.mod.Q, k = P.k, n = P.n, g = P.gbits, bar = 1 + grp;
     const uint32_t u = FIRST ? 0u : s / n, i = FIRST ? 0u : s - u * n;
@@ -567,6 +570,17 @@ __device__ __forceinline__ void grouped_step(const DevCtx& P, const FastTables& 
     const uint32_t brv8 = __brev(tid) >> 24;
     const uint32_t e0n = cneg * (2 * brv8 + 1), e0p = c * (2 * brv8 + 1);
     uint32_t y[8];
+    // XZW: Q - X^-c per slot, once per step (see fast_step).  Every group writes the same values to the same words (slot =
+    // f(tid) only), each thread reads back the words it wrote itself; steps are separated by block barriers.
+    uint32_t* Mt = Ms + 4 * tid;
+    if (XZW && !FIRST) {
+#pragma unroll
+        for (int ch = 0; ch < 2; ++ch) {
+            uint32_t mq[4];
+            monomial4(P.psipow, e0n, cneg, ch, mq);
+            *reinterpret_cast<uint4*>(Mt + (N / 2) * ch) = make_uint4(Q - mq[0], Q - mq[1], Q - mq[2], Q - mq[3]);
+        }
+    }
     // ---- phase 1: the parties, round-robin over the groups (order index k - 1 = the key owner).  The owner's <D_u, d> is
     // transformed back and added to a_u like everybody else's (one more inverse transform per step than the sequential
     // schedule, which adds it to <g^-1(sumV), f> in the evaluation domain: same sum, and no registers held across phases) ----
@@ -582,7 +596,7 @@ __device__ __forceinline__ void grouped_step(const DevCtx& P, const FastTables& 
 #pragma unroll
         for (int ch = 0; ch < 2; ++ch) {
             uint32_t x4[4];
-            key_mac4<XZW, FIRST>(P, ev1, ev2, evs, c, cneg, e0p, e0n, ch, D, x4);
+            key_mac4<XZW, FIRST>(P, ev1, ev2, evs, c, cneg, e0p, e0n, ch, D, x4, (XZW && !FIRST) ? Mt : nullptr);
             const uint4 q0 = ldg4(pk + (N / 2) * ch), q1 = ldg4(pk + N + (N / 2) * ch);
             const uint32_t pp0[4] = {q0.x, q0.y, q0.z, q0.w}, pp1[4] = {q1.x, q1.y, q1.z, q1.w};
 #pragma unroll
@@ -628,7 +642,7 @@ __device__ __forceinline__ void grouped_step(const DevCtx& P, const FastTables& 
 #pragma unroll
         for (int ch = 0; ch < 2; ++ch) {
             uint32_t x4[4];
-            key_mac4<XZW, FIRST>(P, ev1 + N, ev2 + N, evs + N, c, cneg, e0p, e0n, ch, D, x4);  // the "f" column
+            key_mac4<XZW, FIRST>(P, ev1 + N, ev2 + N, evs + N, c, cneg, e0p, e0n, ch, D, x4, (XZW && !FIRST) ? Mt : nullptr);  // "f" column
 #pragma unroll
             for (int q = 0; q < 4; ++q) y[4 * ch + q] = x4[q];  // < 3Q
         }
@@ -644,8 +658,8 @@ __device__ __forceinline__ void grouped_step(const DevCtx& P, const FastTables& 
     __syncthreads();  // a[] complete (and every group past its last exchange) before the next step
 }
 
-template <bool GATE, bool XZW, bool ALIAS>
-__global__ void __launch_bounds__(1024, 1) blind_rotate_grouped(const DevCtx P, const FastTables T, const GateIO io) {
+template <bool GATE, bool XZW, bool ALIAS, int MAXT>  // MAXT = 256 G: 2 groups get 128 registers per thread, 4 groups 64
+__global__ void __launch_bounds__(MAXT, 1) blind_rotate_grouped(const DevCtx P, const FastTables T, const GateIO io) {
     extern __shared__ __align__(16) uint32_t sm[];
     const uint32_t k = P.k, n = P.n, G = blockDim.x >> 8, grp = threadIdx.x >> 8, tid = threadIdx.x & 255;
     constexpr uint32_t N = FN;
@@ -654,15 +668,15 @@ __global__ void __launch_bounds__(1024, 1) blind_rotate_grouped(const DevCtx P, 
     uint32_t* E1 = a + k * N + grp * EW;
     uint32_t* E2 = E1 + 2 * FNP;
     uint32_t* Vs = a + k * N + G * EW;
-    uint16_t* crot = reinterpret_cast<uint16_t*>(Vs + N);
+    uint32_t* Ms = Vs + N;
 
     for (uint32_t e = threadIdx.x; e < N; e += blockDim.x) Vs[e] = 0;
-    rotate_prologue<GATE>(P, io, blockIdx.x, a, crot);  // ends with a block barrier
-    grouped_step<XZW, true, ALIAS>(P, T, a, E1, E2, Vs, 0, crot[0], tid, grp, G);
+    rotate_prologue<GATE>(P, io, blockIdx.x, a, nullptr);  // ends with a block barrier
+    grouped_step<XZW, true, ALIAS>(P, T, a, E1, E2, Vs, Ms, 0, rotation_amount<GATE>(P, io, blockIdx.x, 0), tid, grp, G);
     for (uint32_t s = 1; s < k * n; ++s) {
-        const uint32_t c = crot[s];
+        const uint32_t c = rotation_amount<GATE>(P, io, blockIdx.x, s);
         if (c == 0) continue;
-        grouped_step<XZW, false, ALIAS>(P, T, a, E1, E2, Vs, s, c, tid, grp, G);
+        grouped_step<XZW, false, ALIAS>(P, T, a, E1, E2, Vs, Ms, s, c, tid, grp, G);
     }
     rotate_epilogue<GATE>(P, io, blockIdx.x, a, a + k * N);  // scratch: group 0's exchange buffer
 }
@@ -957,12 +971,13 @@ inline bool fast_use_alias(const DevCtx& d) {
     return fast_smem_bytes(d.k, d.n, false, d.variant == 0) > 227 * 1024;
 }
 
-// party-parallel groups per gate, overridable for experiments with MKFHE_GROUPS.  Measured on B200 (profiles/r1_s17_*):
-// k = 16: 4 groups 235 gates/s vs 200 for one group (1 gate per SM either way: 32 warps instead of 8);  k = 8: 866 vs 957,
-// k = 4 (2 groups): 3013 vs 4246 -- where several gates fit an SM anyway, the idle groups of the sumV phase cost more than
-// the shorter step brings.  So: grouped from k = 16 on.
+// party-parallel groups per gate, overridable for experiments with MKFHE_GROUPS.  Measured on B200, gates/s
+// (profiles/r1_s34_k16_groups.txt, r1_s17_grouped_quick.txt):   k = 16: 1 group 281, 2 groups 350, 4 groups 306 (1 gate per SM
+// in all three: 8 / 16 / 32 warps, 128 / 128 / 64 registers);   k = 8: 1398 vs 1252 (2 groups);   k = 4: 4246 vs 3013 -- where
+// several gates fit an SM anyway, the idle groups of the sumV phase cost more than the shorter step brings.
+// So: two groups from k = 16 on.
 inline uint32_t fast_groups(const DevCtx& d) {
-    uint32_t G = d.k >= 16 ? 4 : 1;
+    uint32_t G = d.k >= 16 ? 2 : 1;
     if (const char* e = getenv("MKFHE_GROUPS")) G = uint32_t(atoi(e));
     if (G != 2 && G != 4) return 1;
     if (d.k > 16 || d.k < G) return 1;
@@ -990,16 +1005,18 @@ inline cudaError_t fast_blind_rotate(FastState& F, const DevCtx& d, bool gate, c
     if (const char* ev = getenv("MKFHE_MINB")) minb = std::min(4, std::max(2, atoi(ev)));
     if (alias) minb = 4;  // the fallback layout is built for the 64-register budget only
     if (G > 1) {
+#define MKFHE_LAUNCH_G(G_, X_, A_) (G == 2 ? launch(blind_rotate_grouped<G_, X_, A_, 512>) : launch(blind_rotate_grouped<G_, X_, A_, 1024>))
         switch (sel) {
-            case 0: e = launch(blind_rotate_grouped<false, false, false>); break;
-            case 1: e = launch(blind_rotate_grouped<false, false, true>); break;
-            case 2: e = launch(blind_rotate_grouped<false, true, false>); break;
-            case 3: e = launch(blind_rotate_grouped<false, true, true>); break;
-            case 4: e = launch(blind_rotate_grouped<true, false, false>); break;
-            case 5: e = launch(blind_rotate_grouped<true, false, true>); break;
-            case 6: e = launch(blind_rotate_grouped<true, true, false>); break;
-            default: e = launch(blind_rotate_grouped<true, true, true>); break;
+            case 0: e = MKFHE_LAUNCH_G(false, false, false); break;
+            case 1: e = MKFHE_LAUNCH_G(false, false, true); break;
+            case 2: e = MKFHE_LAUNCH_G(false, true, false); break;
+            case 3: e = MKFHE_LAUNCH_G(false, true, true); break;
+            case 4: e = MKFHE_LAUNCH_G(true, false, false); break;
+            case 5: e = MKFHE_LAUNCH_G(true, false, true); break;
+            case 6: e = MKFHE_LAUNCH_G(true, true, false); break;
+            default: e = MKFHE_LAUNCH_G(true, true, true); break;
         }
+#undef MKFHE_LAUNCH_G
     } else if (alias) {
         switch (sel >> 1) {
             case 0: e = launch(blind_rotate_fast<false, false, true, 4>); break;

@@ -125,7 +125,26 @@ struct GateIO {
 // ---- the three parts of one gate's blind rotation, shared by the generic kernel and (prologue, first step, epilogue) by the
 // specialised one in fast_kernels.cuh.  All threads of the CTA call them; g = gate index. ----
 
-// inputs -> rotation amounts crot[k*n] and the initial accumulator a[k][N] in COEFFICIENT form.  Ends with a barrier.
+// rotation amount of step s of gate g: the prologue's formulas for one entry, for kernels that do not keep crot[] in shared
+// memory (the party-parallel kernel at k = 16 needs the space) and re-derive it from the inputs once per step
+template <bool GATE>
+__device__ __forceinline__ uint32_t rotation_amount(const DevCtx& P, const GateIO& io, uint32_t g, uint32_t s) {
+    const uint32_t M = 2 * P.N;
+    const size_t at = size_t(g) * P.k * P.n + s;
+    if (!GATE) {
+        const uint32_t v = io.rot[at];
+        return P.variant == 0 ? ((v * M) / io.rot_mod) % M : v % M;
+    }
+    if (P.scheme == 0) {
+        const uint32_t r = submod(__ldg(io.ctnand + s), addmod(io.ct1[at], io.ct2[at], P.q), P.q);
+        return (r * M) / P.q;
+    }
+    const uint32_t av = submod(0u, addmod(io.ct1[at], io.ct2[at], P.q), P.q);
+    return (M - round_qQ(av, M, P.q)) & (M - 1);
+}
+
+// inputs -> rotation amounts crot[k*n] (skipped when crot is null) and the initial accumulator a[k][N] in COEFFICIENT form.
+// Ends with a barrier.
 template <bool GATE>
 __device__ __forceinline__ void rotate_prologue(const DevCtx& P, const GateIO& io, uint32_t g, uint32_t* a, uint16_t* crot) {
     const uint32_t N = P.N, Q = P.mod.Q, k = P.k, n = P.n, M = 2 * N;
@@ -137,13 +156,13 @@ __device__ __forceinline__ void rotate_prologue(const DevCtx& P, const GateIO& i
         uint32_t b_hat = 0;
         if (P.scheme == 0) {
             // ct_temp = ctNAND - (ct1 + ct2) mod q (binfhe-base-scheme.cpp:485-490); c = ct*2N/q (mk-acc-xzw.cpp:110)
-            for (uint32_t s = tid; s < k * n; s += T) {
+            for (uint32_t s = tid; crot != nullptr && s < k * n; s += T) {
                 const uint32_t r = submod(__ldg(io.ctnand + s), addmod(c1[s], c2[s], P.q), P.q);
                 crot[s] = static_cast<uint16_t>((r * M) / P.q);
             }
         } else {
             // ct_temp = (0, 5q/8) - (ct1 + ct2); ModSwitch to 2N; GetAneg (binfhe-base-scheme.cpp:393-406, mklwe-ciphertext.h:86-96)
-            for (uint32_t s = tid; s < k * n; s += T) {
+            for (uint32_t s = tid; crot != nullptr && s < k * n; s += T) {
                 const uint32_t av = submod(0u, addmod(c1[s], c2[s], P.q), P.q);
                 const uint32_t ams = round_qQ(av, M, P.q);
                 crot[s] = static_cast<uint16_t>((M - ams) & (M - 1));
@@ -170,7 +189,7 @@ __device__ __forceinline__ void rotate_prologue(const DevCtx& P, const GateIO& i
         __syncthreads();
     } else {
         const uint32_t* r = io.rot + size_t(g) * k * n;
-        for (uint32_t s = tid; s < k * n; s += T) {
+        for (uint32_t s = tid; crot != nullptr && s < k * n; s += T) {
             const uint32_t v = r[s];
             crot[s] = static_cast<uint16_t>(P.variant == 0 ? ((v * M) / io.rot_mod) % M : v % M);
         }
