@@ -769,6 +769,177 @@ __global__ void __launch_bounds__(256) butterfly_peak_kernel(uint32_t* sink, uin
     if (r == 0x12345678u) sink[0] = r;
 }
 
+// ---- 16 coefficients per thread: the batched transform with TWO exchanges instead of three ------------------------------
+// 128 threads per polynomial, passes of 4 + 4 + 3 radix-2 stages (forward; 3 + 4 + 4 inverse).  One exchange crosses warps,
+// the other stays inside a warp (warp w owns [512 w, 512 w + 512) on both sides).  Exchange index: pad16(j) = j + 4 (j >> 5)
+// + 8 (j >> 8), which makes the three access patterns "base + immediate" and bank-conflict free:
+//   A  j = tid + 128 r           -> (tid + 4 (tid >> 5)) + 152 r + 8 (r >> 1) ... consecutive lanes, consecutive words
+//   B  j = 128 h + 8 r + l3      -> h = tid >> 3, l3 = tid & 7: banks 16 h + 8 (h >> 1) + l3 (mod 32): {0,16,8,24} + l3
+//   C  j = 16 tid + r (128-bit)  -> a quarter warp covers 8 distinct 16-byte bank groups
+// Used by the NTT micro-benchmark entry (mkfhe_ntt, N = 2048); the gate kernel keeps the 8-coefficient transforms this round.
+constexpr uint32_t FT16 = 128, FNP16 = 2368;
+__device__ __forceinline__ constexpr uint32_t pad16(uint32_t j) { return j + 4 * (j >> 5) + 8 * (j >> 8); }
+struct ExIdx16 {
+    uint32_t a, b, c;
+    __device__ __forceinline__ explicit ExIdx16(uint32_t tid)
+        : a(tid + 4 * (tid >> 5)), b(pad16(128 * (tid >> 3)) + (tid & 7)), c(pad16(16 * tid)) {}
+    // A: j = tid + 128 r: j >> 5 = (tid >> 5) + 4 r, j >> 8 = r >> 1
+    __device__ __forceinline__ uint32_t A(int r) const { return a + 128 * r + 16 * r + 8 * (r >> 1); }
+    // B: j = 128 h + 8 r + l3: j >> 5 = 4 h + (r >> 2), j >> 8 = h >> 1 (in the base)
+    __device__ __forceinline__ uint32_t B(int r) const { return b + 8 * r + 4 * (r >> 2); }
+    // C: j = 16 tid + r: j >> 5 = tid >> 1, j >> 8 = tid >> 4 (both in the base)
+    __device__ __forceinline__ uint32_t C(int r) const { return c + r; }
+};
+
+// forward: in x[r] = coefficient tid + 128 r (< 2Q), out x[r] = slot 16 tid + r (< 24Q).  E: FNP16 words.
+__device__ __forceinline__ void fwd_ntt16(uint32_t (&x)[16], uint32_t* E, const FastTables& T, uint32_t Q, uint32_t tid) {
+    const uint32_t twoQ = 2 * Q;
+    const ExIdx16 ex(tid);
+    const uint32_t h4 = tid >> 3;
+    // pass 1: t = 1024, 512, 256, 128; block of coefficient tid + 128 r at stage s is r >> (4 - s): the same in every thread
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+        const int h = 8 >> s;
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+            if (r & h) continue;
+            MKFHE_BFLY(x[r], x[r + h], T.twB[(1 << s) + (r >> (4 - s))]);
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < 16; ++r) E[ex.A(r)] = x[r];
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < 16; ++r) x[r] = E[ex.B(r)];
+    // pass 2: t = 64, 32, 16, 8 (m = 16 << s); block = (h4 << s) + (r >> (4 - s))
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+        const int h = 8 >> s;
+        const uint2* tws = T.tw2 + (16 << s) + (h4 << s);
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+            if (r & h) continue;
+            const uint2 w = __ldg(tws + (r >> (4 - s)));
+            MKFHE_BFLY(x[r], x[r + h], w);
+        }
+    }
+    __syncwarp();
+#pragma unroll
+    for (int r = 0; r < 16; ++r) E[ex.B(r)] = x[r];
+    __syncwarp();
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        const uint4 v = *reinterpret_cast<const uint4*>(E + ex.C(4 * c));
+        x[4 * c] = v.x; x[4 * c + 1] = v.y; x[4 * c + 2] = v.z; x[4 * c + 3] = v.w;
+    }
+    // pass 3: t = 4, 2, 1 (m = 256 << s); block = (tid << (1 + s)) + (r >> (3 - s)): contiguous per thread
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+        const int h = 4 >> s;
+        const uint2* tws = T.tw2 + (256 << s) + (tid << (1 + s));
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+            if (r & h) continue;
+            const uint2 w = __ldg(tws + (r >> (3 - s)));
+            MKFHE_BFLY(x[r], x[r + h], w);
+        }
+    }
+}
+
+// inverse: in x[r] = slot 16 tid + r (< 6Q), out x[r] = coefficient tid + 128 r in [0, 2Q).  Same ring map as inv_ntt_regs.
+__device__ __forceinline__ void inv_ntt16(uint32_t (&x)[16], uint32_t* E, const FastTables& T, uint32_t Q, uint32_t tid) {
+    const uint32_t twoQ = 2 * Q, sixQ = 6 * Q;
+    const ExIdx16 ex(tid);
+    const uint32_t l3 = tid & 7;
+    // pass 1: t = 1 (twiddle 1), 2, 4: twiddle itw[t + (r mod t)], the same in every thread
+#pragma unroll
+    for (int r = 0; r < 16; r += 2) {
+        const uint32_t u = x[r], v = x[r + 1];
+        x[r] = u + v;
+        x[r + 1] = u + sixQ - v;
+    }
+#pragma unroll
+    for (int s = 1; s < 3; ++s) {
+        const int h = 1 << s;
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+            if (r & h) continue;
+            MKFHE_BFLY(x[r], x[r + h], T.itwB[h + (r & (h - 1))]);
+        }
+    }
+    __syncwarp();
+#pragma unroll
+    for (int c = 0; c < 4; ++c) *reinterpret_cast<uint4*>(E + ex.C(4 * c)) = make_uint4(x[4 * c], x[4 * c + 1], x[4 * c + 2], x[4 * c + 3]);
+    __syncwarp();
+#pragma unroll
+    for (int r = 0; r < 16; ++r) x[r] = E[ex.B(r)];
+    // pass 2: t = 8, 16, 32, 64 (h = t / 8 in register units); m = (j mod t) = 8 (r mod h) + l3
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+        const int h = 1 << s;
+        const uint2* tws = T.itw2 + 8 * h + l3;
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+            if (r & h) continue;
+            const uint2 w = __ldg(tws + 8 * (r & (h - 1)));
+            MKFHE_BFLY(x[r], x[r + h], w);
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < 16; ++r) E[ex.B(r)] = x[r];
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < 16; ++r) x[r] = E[ex.A(r)];
+    // pass 3: t = 128, 256, 512, 1024 (h = t / 128); m = 128 (r mod h) + tid
+#pragma unroll
+    for (int s = 0; s < 4; ++s) {
+        const int h = 1 << s;
+        const uint2* tws = T.itw2 + 128 * h + tid;
+#pragma unroll
+        for (int r = 0; r < 16; ++r) {
+            if (r & h) continue;
+            const uint2 w = __ldg(tws + 128 * (r & (h - 1)));
+            MKFHE_BFLY(x[r], x[r + h], w);
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < 16; ++r) x[r] = shoup_lazy(x[r], __ldg(T.scale2 + tid + 128 * r), Q);
+}
+
+__global__ void __launch_bounds__(FT16, 4) ntt_batch_fast16(const FastTables T, const uint32_t Q, const uint2 one2, uint32_t* polys,
+                                                           const uint64_t batch, const int inverse) {
+    __shared__ __align__(16) uint32_t E[FNP16];
+    const uint32_t tid = threadIdx.x;
+    for (uint64_t b = blockIdx.x; b < batch; b += gridDim.x) {
+        uint32_t* p = polys + b * FN;
+        uint32_t x[16];
+        if (!inverse) {
+#pragma unroll
+            for (int r = 0; r < 16; ++r) x[r] = __ldcs(p + tid + 128 * r);
+            fwd_ntt16(x, E, T, Q, tid);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                uint4 v;
+                v.x = fold1(shoup_lazy(x[4 * c + 0], one2, Q), Q);
+                v.y = fold1(shoup_lazy(x[4 * c + 1], one2, Q), Q);
+                v.z = fold1(shoup_lazy(x[4 * c + 2], one2, Q), Q);
+                v.w = fold1(shoup_lazy(x[4 * c + 3], one2, Q), Q);
+                __stcs(reinterpret_cast<uint4*>(p + 16 * tid + 4 * c), v);
+            }
+        } else {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const uint4 v = __ldcs(reinterpret_cast<const uint4*>(p + 16 * tid + 4 * c));
+                x[4 * c] = v.x; x[4 * c + 1] = v.y; x[4 * c + 2] = v.z; x[4 * c + 3] = v.w;
+            }
+            inv_ntt16(x, E, T, Q, tid);
+#pragma unroll
+            for (int r = 0; r < 16; ++r) __stcs(p + tid + 128 * r, fold1(x[r], Q));
+        }
+        __syncthreads();  // E is reused by the next polynomial
+    }
+}
+
 // ---- bootstrapping-key generation on the register-resident transforms (N = 2048; semantics of keygen_bk_kernel) ----------
 // One CTA per evk: NTT(r), then per digit NTT(e0_j), NTT(e1_j) as one two-polynomial transform, canonicalised, and the
 // pointwise assembly on the 8 slots the thread holds; the evk leaves as 128-bit stores.  R[j] (slot j of NTT(r), the
@@ -1053,7 +1224,10 @@ inline cudaError_t fast_ntt(FastState& F, const DevCtx& d, uint32_t* polys, uint
                             uint64_t* launches) {
     // HALF: batch counts PAIRS of size-1024 polynomials (the caller sends an odd last one through the generic kernel)
     const unsigned grid = unsigned(std::min<uint64_t>(batch, uint64_t(F.sms) * 4));
-    if (F.half) ntt_batch_fast<true><<<grid, FT, 0, st>>>(F.T, d.mod.Q, F.one2, polys, batch, inverse);
+    if (!F.half && getenv("MKFHE_NTT16")) {  // experimental: 16 coefficients per thread, two exchanges
+        const unsigned g16 = unsigned(std::min<uint64_t>(batch, uint64_t(F.sms) * 8));
+        ntt_batch_fast16<<<g16, FT16, 0, st>>>(F.T, d.mod.Q, F.one2, polys, batch, inverse);
+    } else if (F.half) ntt_batch_fast<true><<<grid, FT, 0, st>>>(F.T, d.mod.Q, F.one2, polys, batch, inverse);
     else ntt_batch_fast<false><<<grid, FT, 0, st>>>(F.T, d.mod.Q, F.one2, polys, batch, inverse);
     ++*launches;
     return cudaGetLastError();
