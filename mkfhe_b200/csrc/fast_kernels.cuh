@@ -38,6 +38,8 @@ struct FastTables {
     const uint2* tw2;     // [N]  forward twiddles, OpenFHE order: psi^i at bitrev(i), as Shoup pairs (w, floor(w 2^32 / Q))
     const uint2* itw2;    // [N]  cyclic inverse (DIT) twiddles: itw2[t + m] = omega^(-m N / 2t), m < t, t = 1, 2, .., N/2
     const uint2* scale2;  // [N]  psi^-i / N  (the twist and the 1/N of the inverse, folded into one Shoup multiply)
+    const uint4* tw16;    // [7][128] the 14 twiddles of thread t in the last forward pass of the 16-coefficient transform:
+                          // word 0: tw2[256+2t..], words 1-2: tw2[512+4t..], words 3-6: tw2[1024+8t..], two twiddles per word
     const uint4* tw4;     // [3][256] the six twiddles of thread t in the last forward pass, as three 128-bit words:
                           // (tw2[512+2t], tw2[513+2t]) | (tw2[1024+4t], tw2[1025+4t]) | (tw2[1026+4t], tw2[1027+4t]) -- one
                           // coalesced load each (16-byte lane stride) instead of six 8-byte loads at 16/32-byte stride
@@ -832,16 +834,22 @@ __device__ __forceinline__ void fwd_ntt16(uint32_t (&x)[16], uint32_t* E, const 
         const uint4 v = *reinterpret_cast<const uint4*>(E + ex.C(4 * c));
         x[4 * c] = v.x; x[4 * c + 1] = v.y; x[4 * c + 2] = v.z; x[4 * c + 3] = v.w;
     }
-    // pass 3: t = 4, 2, 1 (m = 256 << s); block = (tid << (1 + s)) + (r >> (3 - s)): contiguous per thread
+    // pass 3: t = 4, 2, 1 (m = 256 << s); block = (tid << (1 + s)) + (r >> (3 - s)): 2 + 4 + 8 twiddles, contiguous per thread,
+    // read as seven coalesced 128-bit words from the packed table
+    uint2 w[14];
+#pragma unroll
+    for (int i = 0; i < 7; ++i) {
+        const uint4 v = __ldg(T.tw16 + 128 * i + tid);
+        w[2 * i] = make_uint2(v.x, v.y);
+        w[2 * i + 1] = make_uint2(v.z, v.w);
+    }
 #pragma unroll
     for (int s = 0; s < 3; ++s) {
         const int h = 4 >> s;
-        const uint2* tws = T.tw2 + (256 << s) + (tid << (1 + s));
 #pragma unroll
         for (int r = 0; r < 16; ++r) {
             if (r & h) continue;
-            const uint2 w = __ldg(tws + (r >> (3 - s)));
-            MKFHE_BFLY(x[r], x[r + h], w);
+            MKFHE_BFLY(x[r], x[r + h], w[(2 << s) - 2 + (r >> (3 - s))]);
         }
     }
 }
@@ -910,12 +918,28 @@ __global__ void __launch_bounds__(FT16, 4) ntt_batch_fast16(const FastTables T, 
                                                            const uint64_t batch, const int inverse) {
     __shared__ __align__(16) uint32_t E[FNP16];
     const uint32_t tid = threadIdx.x;
+    uint32_t nx[16];  // the next polynomial, fetched while the current one is transformed
+    auto fetch = [&](uint64_t b) {
+        const uint32_t* p = polys + b * FN;
+        if (!inverse) {
+#pragma unroll
+            for (int r = 0; r < 16; ++r) nx[r] = __ldcs(p + tid + 128 * r);
+        } else {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const uint4 v = __ldcs(reinterpret_cast<const uint4*>(p + 16 * tid + 4 * c));
+                nx[4 * c] = v.x; nx[4 * c + 1] = v.y; nx[4 * c + 2] = v.z; nx[4 * c + 3] = v.w;
+            }
+        }
+    };
+    if (blockIdx.x < batch) fetch(blockIdx.x);
     for (uint64_t b = blockIdx.x; b < batch; b += gridDim.x) {
         uint32_t* p = polys + b * FN;
         uint32_t x[16];
-        if (!inverse) {
 #pragma unroll
-            for (int r = 0; r < 16; ++r) x[r] = __ldcs(p + tid + 128 * r);
+        for (int r = 0; r < 16; ++r) x[r] = nx[r];
+        if (b + gridDim.x < batch) fetch(b + gridDim.x);
+        if (!inverse) {
             fwd_ntt16(x, E, T, Q, tid);
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
@@ -927,11 +951,6 @@ __global__ void __launch_bounds__(FT16, 4) ntt_batch_fast16(const FastTables T, 
                 __stcs(reinterpret_cast<uint4*>(p + 16 * tid + 4 * c), v);
             }
         } else {
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                const uint4 v = __ldcs(reinterpret_cast<const uint4*>(p + 16 * tid + 4 * c));
-                x[4 * c] = v.x; x[4 * c + 1] = v.y; x[4 * c + 2] = v.z; x[4 * c + 3] = v.w;
-            }
             inv_ntt16(x, E, T, Q, tid);
 #pragma unroll
             for (int r = 0; r < 16; ++r) __stcs(p + tid + 128 * r, fold1(x[r], Q));
@@ -1012,6 +1031,7 @@ struct FastState {
     FastTables T{};
     uint2 *d_tw2{nullptr}, *d_itw2{nullptr}, *d_scale2{nullptr};
     uint4* d_tw4{nullptr};
+    uint4* d_tw16{nullptr};
     uint2 one2{};
     int sms{148};
     bool half{false};  // tables for N = 1024 (two polynomials per 2048-word pass): only the batched transform uses them
@@ -1089,7 +1109,18 @@ inline cudaError_t fast_init(FastState& F, const DevCtx& d, uint32_t psi, cudaSt
     if ((e = cudaMalloc(reinterpret_cast<void**>(&F.d_tw4), t4.size() * sizeof(uint4))) != cudaSuccess) return e;
     *dev_bytes += t4.size() * sizeof(uint4);
     if ((e = cudaMemcpyAsync(F.d_tw4, t4.data(), t4.size() * sizeof(uint4), cudaMemcpyHostToDevice, st)) != cudaSuccess) return e;
+    std::vector<uint4> t16(7 * 128);
+    for (uint32_t t = 0; t < 128; ++t) {
+        auto q4 = [&](uint32_t i) { return make_uint4(tw[i].x, tw[i].y, tw[i + 1].x, tw[i + 1].y); };
+        t16[t] = q4(256 + 2 * t);
+        for (uint32_t i = 0; i < 2; ++i) t16[128 * (1 + i) + t] = q4(512 + 4 * t + 2 * i);
+        for (uint32_t i = 0; i < 4; ++i) t16[128 * (3 + i) + t] = q4(1024 + 8 * t + 2 * i);
+    }
+    if ((e = cudaMalloc(reinterpret_cast<void**>(&F.d_tw16), t16.size() * sizeof(uint4))) != cudaSuccess) return e;
+    *dev_bytes += t16.size() * sizeof(uint4);
+    if ((e = cudaMemcpyAsync(F.d_tw16, t16.data(), t16.size() * sizeof(uint4), cudaMemcpyHostToDevice, st)) != cudaSuccess) return e;
     if ((e = cudaStreamSynchronize(st)) != cudaSuccess) return e;
+    F.T.tw16 = F.d_tw16;
     F.T.tw2 = F.d_tw2; F.T.itw2 = F.d_itw2; F.T.scale2 = F.d_scale2; F.T.tw4 = F.d_tw4;
     for (int i = 0; i < 8; ++i) F.T.twA[i] = tw[i];
     for (int i = 0; i < 4; ++i) F.T.itwA[i] = itw[i];
@@ -1107,6 +1138,7 @@ inline void fast_destroy(FastState& F) {
     for (uint2* p : {F.d_tw2, F.d_itw2, F.d_scale2})
         if (p) cudaFree(p);
     if (F.d_tw4) cudaFree(F.d_tw4);
+    if (F.d_tw16) cudaFree(F.d_tw16);
     F = FastState{};
 }
 // Key polynomials -> register order, in place, one CTA per polynomial: thread t of a gate holds the slots 8t .. 8t+7 after

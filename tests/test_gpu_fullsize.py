@@ -80,6 +80,17 @@ def test_ntt_full_size(full):
     assert (ctx.NTT(f, inverse=True) == x).all()
 
 
+def test_ntt_16_coefficient_variant(full, monkeypatch):
+    """The experimental two-exchange transform (16 coefficients per thread, MKFHE_NTT16=1) against the reference."""
+    r, p, ctx, keys = full
+    monkeypatch.setenv("MKFHE_NTT16", "1")
+    x = np.random.default_rng(6).integers(0, p.Q, size=(33, p.N), dtype=np.uint32)
+    f = ctx.NTT(x)
+    assert (f[:4] == r.ntt(x[:4], False)).all()
+    assert (ctx.NTT(x, inverse=True)[:4] == r.ntt(x[:4], True)).all()
+    assert (ctx.NTT(f, inverse=True) == x).all()
+
+
 def test_drop_in_accumulator_through_reference_api(full):
     """The reference's unmodified BinFHEScheme::EvalBinGate with UniEncAccumulatorB200 plugged into UniEncACCscheme."""
     from mkfhe_b200.lib import LIB_PATH
