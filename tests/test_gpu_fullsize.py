@@ -80,6 +80,31 @@ def test_ntt_full_size(full):
     assert (ctx.NTT(f, inverse=True) == x).all()
 
 
+def test_identical_gates_give_identical_outputs(full):
+    """Race / scheduling check (compute-sanitizer is closed on the GPU pool): 1200 copies of one refreshed gate -- more than two
+    waves of resident CTAs, so copies run at different times, on different SMs and next to different neighbours -- must give
+    1200 identical refreshed ciphertexts, equal to the reference's."""
+    r, p, ctx, keys = full
+    c1, b1 = r.encrypt(1)
+    c2, b2 = r.encrypt(0)
+    c3, b3 = r.encrypt(1)
+    c4, b4 = r.encrypt(1)
+    x, bx = r.eval_gate(c1, b1, c2, b2)   # refreshed inputs: dense rotation amounts
+    y, by = r.eval_gate(c3, b3, c4, b4)
+    eo, eb = r.eval_gate(x, bx, y, by)
+    B = 1200
+    X = np.tile(np.asarray(x, dtype=np.uint32).reshape(1, p.k, p.n), (B, 1, 1))
+    Y = np.tile(np.asarray(y, dtype=np.uint32).reshape(1, p.k, p.n), (B, 1, 1))
+    if p.scheme == 1:
+        out, bout = ctx.EvalBinGate("NAND", X, Y, np.full(B, bx, np.uint32), np.full(B, by, np.uint32))
+        assert (bout == eb).all()
+    else:
+        out = ctx.EvalBinGate("NAND", X, Y)
+    out = np.asarray(out).reshape(B, -1)
+    assert (out == out[0]).all()
+    assert (out[0] == eo).all()
+
+
 def test_ntt_16_coefficient_variant(full, monkeypatch):
     """The experimental two-exchange transform (16 coefficients per thread, MKFHE_NTT16=1) against the reference."""
     r, p, ctx, keys = full

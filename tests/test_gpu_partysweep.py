@@ -49,6 +49,8 @@ def test_large_party_counts_vs_oracle(paramset, env, gates, pick, monkeypatch):
     ct2 = rng.integers(0, P.q, size=(gates, P.k, P.n), dtype=np.uint32)
     b1 = rng.integers(0, P.q, size=gates, dtype=np.uint32)
     b2 = rng.integers(0, P.q, size=gates, dtype=np.uint32)
+    dup = (pick + 1) % gates  # a copy of the checked gate elsewhere in the batch must come out identical
+    ct1[dup], ct2[dup], b1[dup], b2[dup] = ct1[pick], ct2[pick], b1[pick], b2[pick]
     if lwe:
         out, bout = ctx.EvalBinGate("NAND", ct1, ct2, b1, b2)
     else:
@@ -56,4 +58,5 @@ def test_large_party_counts_vs_oracle(paramset, env, gates, pick, monkeypatch):
     o = make_oracle(P)
     eo, eb = o.eval_nand(bk, pkey, kskA, kskB, ctnand, ct1[pick].ravel(), int(b1[pick]), ct2[pick].ravel(), int(b2[pick]))
     assert (np.asarray(out)[pick].ravel() == eo).all() and (not lwe or int(bout[pick]) == eb)
+    assert (np.asarray(out)[dup] == np.asarray(out)[pick]).all() and int(bout[dup]) == int(bout[pick])
     ctx.close()
