@@ -50,6 +50,9 @@ struct mkfhe_ctx {
     bool ntt_half{false};  // N = 1024: batched transforms on the two-polynomials-per-pass path of fast_kernels.cuh
     cudaEvent_t ev[3]{nullptr, nullptr, nullptr};  // before blind rotation | after it | after key switch (last gate batch)
     bool ev_valid{false};
+    // stream-ordered pool behind the per-call scratch of mkfhe_keygen_* / mkfhe_encrypt_* (TmpBuf): repeated calls reuse the same
+    // device memory instead of paying cudaMalloc + cudaFree (about 2 ms a call, more than the kernels take)
+    cudaMemPool_t pool{nullptr};
 };
 
 static thread_local std::string g_create_error;
@@ -163,12 +166,23 @@ static int upload_ksk16(mkfhe_ctx* ctx, const uint32_t* src, uint64_t words, con
 }
 
 namespace {
-struct TmpBuf {  // device scratch of one call, freed on every exit path
+struct TmpBuf {  // device scratch of one call, returned to the context's pool (in stream order) on every exit path
+    mkfhe_ctx* ctx;
     std::vector<void*> p;
-    ~TmpBuf() { for (void* x : p) cudaFree(x); }
+    explicit TmpBuf(mkfhe_ctx* c) : ctx(c) {}
+    TmpBuf(const TmpBuf&) = delete;
+    TmpBuf& operator=(const TmpBuf&) = delete;
+    ~TmpBuf() {
+        for (void* x : p) {
+            if (ctx->pool) cudaFreeAsync(x, ctx->stream);
+            else cudaFree(x);
+        }
+    }
     template <class T>
     cudaError_t get(T** out, size_t count) {
-        cudaError_t e = cudaMalloc(reinterpret_cast<void**>(out), count * sizeof(T));
+        const size_t bytes = std::max<size_t>(count, 1) * sizeof(T);
+        cudaError_t e = ctx->pool ? cudaMallocFromPoolAsync(reinterpret_cast<void**>(out), bytes, ctx->pool, ctx->stream)
+                                  : cudaMalloc(reinterpret_cast<void**>(out), bytes);
         if (e == cudaSuccess) p.push_back(*out);
         return e;
     }
@@ -219,6 +233,20 @@ int mkfhe_ctx_create(const mkfhe_params* p, mkfhe_ctx** out) {
     ctx->stream = ctx->own_stream;
     for (auto& e : ctx->ev)
         if (cudaEventCreate(&e) != cudaSuccess) return bail(fail(ctx, MKFHE_ECUDA, "cudaEventCreate failed"));
+    if (!getenv("MKFHE_NO_POOL")) {  // scratch pool: keeps up to 512 MiB between calls; without one TmpBuf uses cudaMalloc
+        cudaMemPoolProps pp{};
+        pp.allocType = cudaMemAllocationTypePinned;
+        pp.handleTypes = cudaMemHandleTypeNone;
+        pp.location.type = cudaMemLocationTypeDevice;
+        pp.location.id = ctx->device;
+        uint64_t keep = 512ull << 20;
+        if (cudaMemPoolCreate(&ctx->pool, &pp) != cudaSuccess ||
+            cudaMemPoolSetAttribute(ctx->pool, cudaMemPoolAttrReleaseThreshold, &keep) != cudaSuccess) {
+            if (ctx->pool) cudaMemPoolDestroy(ctx->pool);
+            ctx->pool = nullptr;
+            cudaGetLastError();
+        }
+    }
 
     const uint32_t N = p->N, Q = p->Q;
     uint32_t logN = 0;
@@ -296,6 +324,7 @@ void mkfhe_ctx_destroy(mkfhe_ctx* ctx) {
     if (ctx->ksk16) cudaFree(ctx->ksk16);
     for (auto& e : ctx->ev)
         if (e) cudaEventDestroy(e);
+    if (ctx->pool) cudaMemPoolDestroy(ctx->pool);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     delete ctx;
 }
@@ -631,7 +660,7 @@ int mkfhe_keygen_bk(mkfhe_ctx* ctx, const uint32_t* sinv, const uint32_t* crs, c
     const size_t S = p.variant == MKFHE_VARIANT_XZW ? 2 : 1, E = size_t(p.k) * S * p.n + 1, words = bk_words(p);
     const size_t smem = size_t(1 + 2 * ell) * N * 4;
     CU(cudaSetDevice(ctx->device));
-    TmpBuf tmp;
+    TmpBuf tmp(ctx);
     uint32_t *d_sinv, *d_crs, *d_r, *d_e, *d_out;
     uint8_t* d_m;
     CU(tmp.get(&d_sinv, size_t(p.k) * N));
@@ -677,7 +706,7 @@ int mkfhe_keygen_pkey(mkfhe_ctx* ctx, const uint32_t* s, const uint32_t* crs, co
     const uint32_t N = p.N, ell = p.digitsG - 1;
     const size_t words = size_t(p.k) * ell * N, smem = size_t(ell) * N * 4;
     CU(cudaSetDevice(ctx->device));
-    TmpBuf tmp;
+    TmpBuf tmp(ctx);
     uint32_t *d_s, *d_crs, *d_e, *d_out;
     CU(tmp.get(&d_s, size_t(p.k) * N));
     CU(tmp.get(&d_crs, size_t(ell) * N));
@@ -704,7 +733,7 @@ int mkfhe_keygen_ksk_mntru(mkfhe_ctx* ctx, const uint32_t* s_q, const uint32_t* 
     if (p.scheme != MKFHE_SCHEME_MNTRU) return fail(ctx, MKFHE_EINVAL, "context is not MNTRU");
     const size_t L = size_t(p.N) * p.dKS, words = size_t(p.k) * L * p.n;
     CU(cudaSetDevice(ctx->device));
-    TmpBuf tmp;
+    TmpBuf tmp(ctx);
     uint32_t *d_s, *d_e, *d_f, *d_out;
     CU(tmp.get(&d_s, size_t(p.k) * p.N));
     CU(tmp.get(&d_e, words));
@@ -730,7 +759,7 @@ int mkfhe_keygen_ksk_mklwe(mkfhe_ctx* ctx, const uint32_t* A, const uint32_t* e,
     if (p.scheme != MKFHE_SCHEME_MKLWE) return fail(ctx, MKFHE_EINVAL, "context is not MKLWE");
     const size_t rows = size_t(p.k) * p.N * p.baseKS * p.dKS, wordsA = rows * p.n;
     CU(cudaSetDevice(ctx->device));
-    TmpBuf tmp;
+    TmpBuf tmp(ctx);
     uint32_t *d_A, *d_e, *d_s, *d_sN, *d_B;
     CU(tmp.get(&d_A, wordsA));
     CU(tmp.get(&d_e, rows));
@@ -760,7 +789,7 @@ int mkfhe_encrypt_mntru(mkfhe_ctx* ctx, const uint32_t* finv, const uint32_t* e,
     if (batch > 0x3fffffull) return fail(ctx, MKFHE_EINVAL, "batch too large");
     const size_t words = size_t(batch) * p.k * p.n;
     CU(cudaSetDevice(ctx->device));
-    TmpBuf tmp;
+    TmpBuf tmp(ctx);
     uint32_t *d_f, *d_e, *d_out;
     uint8_t* d_m;
     CU(tmp.get(&d_f, size_t(p.k) * p.n * p.n));
@@ -787,7 +816,7 @@ int mkfhe_encrypt_mklwe(mkfhe_ctx* ctx, const uint32_t* s, const uint32_t* a, co
     if (batch == 0) return MKFHE_OK;
     const size_t words = size_t(batch) * p.k * p.n;
     CU(cudaSetDevice(ctx->device));
-    TmpBuf tmp;
+    TmpBuf tmp(ctx);
     uint32_t *d_s, *d_a, *d_err, *d_b;
     uint8_t* d_m;
     CU(tmp.get(&d_s, size_t(p.k) * p.n));
