@@ -12,6 +12,8 @@
 //   plug-in surface include/mk-acc.h:54-80 (UniEncAccumulator) -- ref_use_accumulator_b200() swaps in the
 //                   drop-in class from integration/unienc_acc_b200.h so the reference's own EvalBinGate runs
 //                   on the GPU library.
+//   batched entry   ref_batch_b200_* drive integration/binfhe_batch_b200.h (EvalBinGateBatch over the reference's ciphertext
+//                   and key objects) and decrypt its outputs with the reference's Decrypt.
 #include <atomic>
 #include <chrono>
 #include <cstdint>
@@ -22,6 +24,7 @@
 #include <vector>
 
 #include "binfhecontext.h"
+#include "binfhe_batch_b200.h"
 #include "unienc_acc_b200.h"
 
 using namespace lbcrypto;
@@ -49,6 +52,7 @@ struct RefCtx {
     MKLWEPrivateKey skL;
     UniEncBTKey ek{};
     MNTRUCiphertext ctNAND;
+    std::shared_ptr<BinFHEBatchB200> batch;  // integration/binfhe_batch_b200.h, created by ref_batch_b200_load
     std::string err;
 };
 
@@ -445,6 +449,92 @@ int ref_use_accumulator_b200(void* h, const char* lib, int restore) {
             lib, c->scheme == 0 ? UniEncAccumulatorB200::XZW : UniEncAccumulatorB200::XZW_B);
         acc->LoadKeys(c->unienc, c->ek.BSkey, c->ek.Pkey, c->n, c->q);
         c->sch->Acc() = acc;
+    });
+}
+
+// ---- the batched entry a maintainer adds (integration/binfhe_batch_b200.h), driven with the reference's own objects ----
+
+// Create the batch evaluator on `lib` (path of libmkfhe_b200.so) and upload this context's keys from the UniEncBTKey the
+// reference generated (and ctNAND for MKNTRU).
+int ref_batch_b200_load(void* h, const char* lib) {
+    auto* c = static_cast<RefCtx*>(h);
+    return guarded(c, [&] {
+        c->batch = std::make_shared<BinFHEBatchB200>(lib);
+        c->batch->LoadKeys(c->params, c->method, c->ek);
+        if (c->scheme == 0) c->batch->LoadGateCiphertext(c->ctNAND);
+    });
+}
+
+// EvalBinGateBatch(NAND) on B gates given as flat arrays (wrapped into reference ciphertext objects first); the outputs are
+// exported flat and, when `dec` is not null, decrypted with the reference's Decrypt.
+int ref_batch_b200_gates(void* h, const uint32_t* ct1, const uint32_t* b1, const uint32_t* ct2, const uint32_t* b2, uint32_t* out,
+                         uint32_t* bout, uint64_t B, int* dec) {
+    auto* c = static_cast<RefCtx*>(h);
+    return guarded(c, [&] {
+        if (!c->batch) throw std::runtime_error("ref_batch_b200_load has not been called");
+        const size_t kn = size_t(c->k) * c->n;
+        if (c->scheme == 0) {
+            std::vector<MNTRUCiphertext> x1, x2;
+            for (uint64_t g = 0; g < B; ++g) {
+                x1.push_back(mk_mntru_ct(c, ct1 + g * kn, c->q));
+                x2.push_back(mk_mntru_ct(c, ct2 + g * kn, c->q));
+            }
+            auto r = c->batch->EvalBinGateBatch(NAND, x1, x2);
+            for (uint64_t g = 0; g < B; ++g) {
+                for (uint32_t u = 0; u < c->k; ++u) put(out + g * kn + size_t(u) * c->n, r[g]->GetElements()[u]);
+                if (dec) {
+                    MNTRUPlaintext m = 0;
+                    ConstMNTRUCiphertext x = r[g];
+                    c->sch->MNTRU()->Decrypt(c->mntru, c->skN, x, &m, 4);
+                    dec[g] = int(m);
+                }
+            }
+        }
+        else {
+            std::vector<MKLWECiphertext> x1, x2;
+            for (uint64_t g = 0; g < B; ++g) {
+                x1.push_back(mk_mklwe_ct(c, ct1 + g * kn, b1[g], c->q));
+                x2.push_back(mk_mklwe_ct(c, ct2 + g * kn, b2[g], c->q));
+            }
+            auto r = c->batch->EvalBinGateBatch(NAND, x1, x2);
+            for (uint64_t g = 0; g < B; ++g) {
+                for (uint32_t u = 0; u < c->k; ++u) put(out + g * kn + size_t(u) * c->n, r[g]->GetA()[u]);
+                bout[g] = r[g]->GetB().ConvertToInt<uint32_t>();
+                if (dec) {
+                    MKLWEPlaintext m = 0;
+                    ConstMKLWECiphertext x = r[g];
+                    c->sch->MKLWE()->Decrypt(c->mklwe, c->skL, x, &m, 4);
+                    dec[g] = int(m);
+                }
+            }
+        }
+    });
+}
+
+// Argument checks of EvalBinGateBatch: returns a bit mask of the cases that threw the reference's config_error
+// (1: gate other than NAND, 2: the same ciphertext object on both sides, 4: input vectors of different length).
+int ref_batch_b200_errors(void* h, int* mask) {
+    auto* c = static_cast<RefCtx*>(h);
+    return guarded(c, [&] {
+        if (!c->batch) throw std::runtime_error("ref_batch_b200_load has not been called");
+        *mask = 0;
+        std::vector<uint32_t> z(size_t(c->k) * c->n, 1u);
+        auto probe = [&](int bit, auto&& f) {
+            try { f(); }
+            catch (const config_error&) { *mask |= bit; }
+        };
+        if (c->scheme == 0) {
+            MNTRUCiphertext a = mk_mntru_ct(c, z.data(), c->q), b = mk_mntru_ct(c, z.data(), c->q);
+            probe(1, [&] { c->batch->EvalBinGateBatch(AND, std::vector<MNTRUCiphertext>{a}, std::vector<MNTRUCiphertext>{b}); });
+            probe(2, [&] { c->batch->EvalBinGateBatch(NAND, std::vector<MNTRUCiphertext>{a}, std::vector<MNTRUCiphertext>{a}); });
+            probe(4, [&] { c->batch->EvalBinGateBatch(NAND, std::vector<MNTRUCiphertext>{a, b}, std::vector<MNTRUCiphertext>{b}); });
+        }
+        else {
+            MKLWECiphertext a = mk_mklwe_ct(c, z.data(), 1, c->q), b = mk_mklwe_ct(c, z.data(), 1, c->q);
+            probe(1, [&] { c->batch->EvalBinGateBatch(AND, std::vector<MKLWECiphertext>{a}, std::vector<MKLWECiphertext>{b}); });
+            probe(2, [&] { c->batch->EvalBinGateBatch(NAND, std::vector<MKLWECiphertext>{a}, std::vector<MKLWECiphertext>{a}); });
+            probe(4, [&] { c->batch->EvalBinGateBatch(NAND, std::vector<MKLWECiphertext>{a, b}, std::vector<MKLWECiphertext>{b}); });
+        }
     });
 }
 

@@ -54,6 +54,9 @@ def lib():
         L.ref_decompose.argtypes = [C.c_void_p, U32P, U32P]
         L.ref_bench_gates.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_double)]
         L.ref_use_accumulator_b200.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
+        L.ref_batch_b200_load.argtypes = [C.c_void_p, C.c_char_p]
+        L.ref_batch_b200_gates.argtypes = [C.c_void_p, U32P, U32P, U32P, U32P, U32P, U32P, C.c_uint64, C.POINTER(C.c_int)]
+        L.ref_batch_b200_errors.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
         _lib = L
     return _lib
 
@@ -236,3 +239,26 @@ class Ref:
 
     def use_accumulator_b200(self, libpath: str, restore: bool = False):
         self._ck(self.L.ref_use_accumulator_b200(self.h, libpath.encode(), 1 if restore else 0), "ref_use_accumulator_b200")
+
+    # ---- integration/binfhe_batch_b200.h: EvalBinGateBatch over the reference's own key and ciphertext objects ----
+    def batch_b200_load(self, libpath: str):
+        self._ck(self.L.ref_batch_b200_load(self.h, libpath.encode()), "ref_batch_b200_load")
+
+    def batch_b200_gates(self, ct1, b1, ct2, b2):
+        """ct1, ct2: [B][k][n]; b1, b2: [B] (MK-LWE; ignored for matrix-NTRU).  Returns (out [B][k][n], bout [B], the reference's
+        Decrypt of every output)."""
+        ct1 = np.ascontiguousarray(ct1, dtype=np.uint32)
+        ct2 = np.ascontiguousarray(ct2, dtype=np.uint32)
+        B = ct1.shape[0]
+        b1 = np.ascontiguousarray(b1 if b1 is not None else np.zeros(B), dtype=np.uint32)
+        b2 = np.ascontiguousarray(b2 if b2 is not None else np.zeros(B), dtype=np.uint32)
+        out = np.zeros_like(ct1)
+        bout = np.zeros(B, dtype=np.uint32)
+        dec = (C.c_int * B)()
+        self._ck(self.L.ref_batch_b200_gates(self.h, _p(ct1), _p(b1), _p(ct2), _p(b2), _p(out), _p(bout), B, dec), "ref_batch_b200_gates")
+        return out, bout, np.array(list(dec), dtype=np.int64)
+
+    def batch_b200_errors(self) -> int:
+        m = C.c_int(0)
+        self._ck(self.L.ref_batch_b200_errors(self.h, C.byref(m)), "ref_batch_b200_errors")
+        return int(m.value)

@@ -133,6 +133,29 @@ def test_drop_in_accumulator_through_reference_api(full):
     assert r.decrypt(gpu_out, gpu_b) == 0
 
 
+def test_batched_gate_class_over_reference_objects(full):
+    """integration/binfhe_batch_b200.h: the C++ EvalBinGateBatch a maintainer adds, compiled against the unmodified reference.
+    It takes the reference's BinFHECryptoParams + UniEncBTKey (+ ctNAND), flattens and uploads them itself, takes vectors of
+    the reference's ciphertext objects and returns ciphertext objects: every output equals the reference's own EvalBinGate on
+    the same pair, the reference's Decrypt gives NAND, and the argument checks throw the reference's config_error."""
+    from mkfhe_b200.lib import LIB_PATH
+
+    r, p, ctx, keys = full
+    bits = [(0, 0), (0, 1), (1, 0), (1, 1), (1, 1), (0, 1)]
+    enc = [(r.encrypt(x), r.encrypt(y)) for x, y in bits]
+    ct1 = np.stack([e[0][0] for e in enc]).reshape(len(bits), p.k, p.n)
+    ct2 = np.stack([e[1][0] for e in enc]).reshape(len(bits), p.k, p.n)
+    b1 = np.array([e[0][1] for e in enc], dtype=np.uint32)
+    b2 = np.array([e[1][1] for e in enc], dtype=np.uint32)
+    r.batch_b200_load(LIB_PATH)
+    out, bout, dec = r.batch_b200_gates(ct1, b1, ct2, b2)
+    assert list(dec) == [1 - (x & y) for x, y in bits]
+    for g in (0, 3, 5):  # the reference takes 1-2 s a gate
+        eo, eb = r.eval_gate(ct1[g].ravel(), int(b1[g]), ct2[g].ravel(), int(b2[g]))
+        assert (out[g].ravel() == eo).all() and int(bout[g]) == int(eb)
+    assert r.batch_b200_errors() == 7
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("batch", [1, 2, 7, 64])
 def test_ntt_n1024_vs_oracle(batch):
