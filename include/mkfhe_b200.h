@@ -129,6 +129,27 @@ int mkfhe_eval_nand(mkfhe_ctx* ctx, const uint32_t* ct1, const uint32_t* b1, con
 int mkfhe_eval_nand_dev(mkfhe_ctx* ctx, const uint32_t* d_ct1, const uint32_t* d_b1, const uint32_t* d_ct2,
                         const uint32_t* d_b2, uint32_t* d_out, uint32_t* d_bout, uint64_t batch);
 
+/* A circuit of NAND gates on a table of wires ("gate circuits on the batch API").  The reference has no
+ * circuit entry: a caller loops over BinFHEContext::EvalBinGate (binfhecontext.cpp:415-419), one gate at a time, which on a GPU
+ * would leave all but one SM idle.  Here gate g computes wires[out[g]] = NAND(wires[in1[g]], wires[in2[g]]); the library
+ * levelises the netlist (level of a gate = 1 + the deepest gate feeding it) and runs every level as ONE batch of
+ * mkfhe_eval_nand_dev, gathering and scattering ciphertext rows on the device.
+ *   wires   : [n_wires][k][n] mod q, in/out (primary inputs filled by the caller, gate outputs written by the call)
+ *   wires_b : [n_wires] (MKLWE; NULL for MNTRU)
+ *   in1, in2, out : [n_gates] wire indices, HOST arrays in both variants.  Gates must be in topological order; every wire is
+ *             written by at most one gate and never read before the gate that writes it; in1[g] != in2[g] (the reference
+ *             rejects a gate on one ciphertext object: binfhe-base-scheme.cpp:382-383, 471-472).  Violations: MKFHE_EINVAL.
+ *   n_levels: optional, receives the depth of the circuit = number of gate batches launched.
+ * mkfhe_eval_circuit: host wires, synchronous.  _dev: wires in device memory, asynchronous on the context's stream (the index
+ * arrays are consumed before the call returns).  mkfhe_circuit_levels: the levelisation alone (needs no GPU): level_of_gate
+ * [n_gates] receives 0-based levels; returns the number of levels, or MKFHE_EINVAL for a netlist the calls above would refuse. */
+int mkfhe_eval_circuit(mkfhe_ctx* ctx, uint32_t* wires, uint32_t* wires_b, uint64_t n_wires, const uint32_t* in1,
+                       const uint32_t* in2, const uint32_t* out, uint64_t n_gates, uint32_t* n_levels);
+int mkfhe_eval_circuit_dev(mkfhe_ctx* ctx, uint32_t* d_wires, uint32_t* d_wires_b, uint64_t n_wires, const uint32_t* in1,
+                           const uint32_t* in2, const uint32_t* out, uint64_t n_gates, uint32_t* n_levels);
+int64_t mkfhe_circuit_levels(uint64_t n_wires, const uint32_t* in1, const uint32_t* in2, const uint32_t* out, uint64_t n_gates,
+                             uint32_t* level_of_gate);
+
 /* MNTRUEncryptionScheme::Decrypt (mntru-pke.cpp:306-341) / MKLWEEncryptionScheme::Decrypt (mklwe-pke.cpp:66-97) for `batch`
  * ciphertexts: ct [batch][k][n] mod q, b [batch] (MKLWE; NULL for MNTRU), p = plaintext modulus (4 in both examples),
  * m [batch] receives the plaintexts.  Host pointers, synchronous; _dev: device pointers, asynchronous. */

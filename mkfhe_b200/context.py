@@ -238,6 +238,38 @@ class BinFHEContext:
         g = lambda t: None if t is None else C.c_void_p(t.data_ptr())
         self._ck(self._L.mkfhe_eval_nand_dev(self._h, g(ct1), g(b1), g(ct2), g(b2), g(out), g(bout), B), "mkfhe_eval_nand_dev")
 
+    # -- circuits of NAND gates: what a caller of the reference writes as a loop over EvalBinGate (binfhecontext.cpp:415-419)
+    def EvalCircuit(self, wires, gates, b=None):
+        """wires: uint32 [W, k, n] with the primary inputs filled in; gates: int [G, 3] rows (in1, in2, out) in topological order;
+        b: uint32 [W] for MKNTRU_LWE.  Gate g sets wires[out] = NAND(wires[in1], wires[in2]); every level of the netlist runs as
+        one batch.  Returns (wires, b, levels) -- new arrays, the inputs are not modified."""
+        P = self.params
+        w = np.ascontiguousarray(wires, dtype=np.uint32).reshape(-1, P.k, P.n).copy()
+        g = np.ascontiguousarray(gates, dtype=np.uint32).reshape(-1, 3)
+        i1, i2, o = (np.ascontiguousarray(g[:, j]) for j in range(3))
+        if len(g) and bool((i1 == i2).any()):
+            raise config_error("Input ciphertexts should be independant")  # binfhe-base-scheme.cpp:382-383,471-472
+        bb = None
+        if self.is_lwe:
+            if b is None:
+                raise config_error("MKLWE ciphertexts carry b")
+            bb = np.ascontiguousarray(b, dtype=np.uint32).reshape(w.shape[0]).copy()
+        lv = C.c_uint32(0)
+        self._ck(self._L.mkfhe_eval_circuit(self._h, _ptr(w)[0], _ptr(bb)[0], w.shape[0], _ptr(i1)[0], _ptr(i2)[0], _ptr(o)[0], len(g),
+                                            C.byref(lv)), "mkfhe_eval_circuit")
+        return w, bb, int(lv.value)
+
+    def EvalCircuitDevice(self, wires, gates, b=None) -> int:
+        """Same on CUDA tensors (int32 storage, [W, k, n] and [W]), in place and asynchronous; gates stays a host array."""
+        g = np.ascontiguousarray(gates, dtype=np.uint32).reshape(-1, 3)
+        i1, i2, o = (np.ascontiguousarray(g[:, j]) for j in range(3))
+        W = wires.numel() // (self.params.k * self.params.n)
+        lv = C.c_uint32(0)
+        dp = lambda t: None if t is None else C.c_void_p(t.data_ptr())
+        self._ck(self._L.mkfhe_eval_circuit_dev(self._h, dp(wires), dp(b), W, _ptr(i1)[0], _ptr(i2)[0], _ptr(o)[0], len(g), C.byref(lv)),
+                 "mkfhe_eval_circuit_dev")
+        return int(lv.value)
+
     # -- BinFHEContext::Decrypt (binfhecontext.h:318-338 -> mntru-pke.cpp:306-341 / mklwe-pke.cpp:66-97), batched
     def LoadSecretKey(self, sk):
         """sk: uint32 [k, n] -- MNTRUPrivateKey::GetF_col0() or MKLWEPrivateKey::GetElement() of the decrypting parties"""
@@ -393,6 +425,20 @@ def KeyFileInfo(path: str):
         raise _lib.MkfheError(-1, "mkfhe_keyfile_info", f"{path}: unreadable, not a key file, or checksum mismatch")
     names = {1: "bk", 2: "pkey", 3: "ksk", 4: "kskA", 5: "kskB", 6: "ctnand"}
     return p, {names[i]: int(w[i]) for i in names if w[i]}
+
+
+def CircuitLevels(n_wires: int, gates):
+    """Levelisation EvalCircuit applies (no GPU needed): gates int [G, 3] rows (in1, in2, out) -> (levels, level of each gate).
+    Raises config_error for a netlist EvalCircuit refuses (index out of range, in1 == in2, a wire written twice or read
+    before the gate that writes it)."""
+    L = _lib.load()
+    g = np.ascontiguousarray(gates, dtype=np.uint32).reshape(-1, 3)
+    i1, i2, o = (np.ascontiguousarray(g[:, j]) for j in range(3))
+    lev = np.zeros(len(g), dtype=np.uint32)
+    n = L.mkfhe_circuit_levels(int(n_wires), _ptr(i1)[0], _ptr(i2)[0], _ptr(o)[0], len(g), _ptr(lev)[0])
+    if n < 0:
+        raise config_error("not a levelisable NAND netlist")
+    return int(n), lev
 
 
 def _encrypt_methods():

@@ -165,6 +165,55 @@ static int upload_ksk16(mkfhe_ctx* ctx, const uint32_t* src, uint64_t words, con
     return MKFHE_OK;
 }
 
+// ---- circuits of gates: rows of the wire table <-> the contiguous batch of one level ----
+// One CTA per gate of the level; kn = k * n words per ciphertext.  HBM-bound copies of a few KB per gate next to a gate kernel
+// that works tens of milliseconds on each: their cost is the launch.
+__global__ void circuit_gather(const uint32_t* __restrict__ wires, const uint32_t* __restrict__ wb, const uint32_t* __restrict__ in1,
+                               const uint32_t* __restrict__ in2, uint32_t* __restrict__ c1, uint32_t* __restrict__ c2,
+                               uint32_t* __restrict__ b1, uint32_t* __restrict__ b2, uint32_t kn) {
+    const uint32_t g = blockIdx.x;
+    const uint32_t* s1 = wires + size_t(in1[g]) * kn;
+    const uint32_t* s2 = wires + size_t(in2[g]) * kn;
+    for (uint32_t e = threadIdx.x; e < kn; e += blockDim.x) {
+        c1[size_t(g) * kn + e] = s1[e];
+        c2[size_t(g) * kn + e] = s2[e];
+    }
+    if (wb != nullptr && threadIdx.x == 0) {
+        b1[g] = wb[in1[g]];
+        b2[g] = wb[in2[g]];
+    }
+}
+__global__ void circuit_scatter(uint32_t* __restrict__ wires, uint32_t* __restrict__ wb, const uint32_t* __restrict__ out,
+                                const uint32_t* __restrict__ c, const uint32_t* __restrict__ b, uint32_t kn) {
+    const uint32_t g = blockIdx.x;
+    uint32_t* d = wires + size_t(out[g]) * kn;
+    for (uint32_t e = threadIdx.x; e < kn; e += blockDim.x) d[e] = c[size_t(g) * kn + e];
+    if (wb != nullptr && threadIdx.x == 0) wb[out[g]] = b[g];
+}
+
+// Levelisation of a netlist (host).  level[g] = 0-based level of gate g; returns the number of levels or -1 with `why` set.
+static int64_t circuit_levelise(uint64_t n_wires, const uint32_t* in1, const uint32_t* in2, const uint32_t* out, uint64_t n_gates,
+                                std::vector<uint32_t>& level, const char** why) {
+    // depth[w]: 0 = primary input (never written so far), else 1 + level of the gate that wrote it; seen[w]: read already
+    std::vector<uint32_t> depth(n_wires, 0);
+    std::vector<uint8_t> seen(n_wires, 0);
+    level.assign(n_gates, 0);
+    uint32_t levels = 0;
+    for (uint64_t g = 0; g < n_gates; ++g) {
+        const uint32_t a = in1[g], b = in2[g], o = out[g];
+        if (a >= n_wires || b >= n_wires || o >= n_wires) { *why = "wire index out of range"; return -1; }
+        if (a == b) { *why = "Input ciphertexts should be independent (in1 == in2)"; return -1; }
+        if (depth[o] != 0) { *why = "a wire is written by two gates"; return -1; }
+        if (seen[o] || o == a || o == b) { *why = "a wire is read before the gate that writes it (gates must be in topological order)"; return -1; }
+        seen[a] = seen[b] = 1;
+        const uint32_t l = std::max(depth[a], depth[b]);
+        level[g] = l;
+        depth[o] = l + 1;
+        levels = std::max(levels, l + 1);
+    }
+    return levels;
+}
+
 namespace {
 struct TmpBuf {  // device scratch of one call, returned to the context's pool (in stream order) on every exit path
     mkfhe_ctx* ctx;
@@ -589,6 +638,101 @@ int mkfhe_eval_nand(mkfhe_ctx* ctx, const uint32_t* ct1, const uint32_t* b1, con
     if (rc) return rc;
     CU(cudaMemcpyAsync(out, dout, cw * 4, cudaMemcpyDeviceToHost, ctx->stream));
     if (lwe) CU(cudaMemcpyAsync(bout, dbo, batch * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    return MKFHE_OK;
+}
+
+// ---- circuits ----
+
+int64_t mkfhe_circuit_levels(uint64_t n_wires, const uint32_t* in1, const uint32_t* in2, const uint32_t* out, uint64_t n_gates,
+                             uint32_t* level_of_gate) {
+    if ((!in1 || !in2 || !out) && n_gates) return MKFHE_EINVAL;
+    std::vector<uint32_t> level;
+    const char* why = "";
+    const int64_t L = circuit_levelise(n_wires, in1, in2, out, n_gates, level, &why);
+    if (L < 0) return MKFHE_EINVAL;
+    if (level_of_gate) std::copy(level.begin(), level.end(), level_of_gate);
+    return L;
+}
+
+int mkfhe_eval_circuit_dev(mkfhe_ctx* ctx, uint32_t* d_wires, uint32_t* d_wires_b, uint64_t n_wires, const uint32_t* in1,
+                           const uint32_t* in2, const uint32_t* out, uint64_t n_gates, uint32_t* n_levels) {
+    if (!ctx || !d_wires || ((!in1 || !in2 || !out) && n_gates)) return MKFHE_EINVAL;
+    const mkfhe_params& p = ctx->p;
+    const bool lwe = p.scheme == MKFHE_SCHEME_MKLWE;
+    if (lwe && !d_wires_b) return fail(ctx, MKFHE_EINVAL, "MKLWE circuits need wires_b");
+    if (n_wires > 0xffffffffull || n_gates > 0x7fffffffull) return fail(ctx, MKFHE_EINVAL, "circuit too large");
+    std::vector<uint32_t> level;
+    const char* why = "";
+    const int64_t L = circuit_levelise(n_wires, in1, in2, out, n_gates, level, &why);
+    if (L < 0) return fail(ctx, MKFHE_EINVAL, "mkfhe_eval_circuit: %s", why);
+    if (n_levels) *n_levels = uint32_t(L);
+    if (n_gates == 0) return MKFHE_OK;
+    // counting sort of the gates by level (stable): start[l] .. start[l + 1] are the gates of level l
+    std::vector<uint64_t> start(size_t(L) + 1, 0);
+    for (uint64_t g = 0; g < n_gates; ++g) start[level[g] + 1]++;
+    uint64_t widest = 0;
+    for (int64_t l = 0; l < L; ++l) {
+        widest = std::max(widest, start[l + 1]);
+        start[l + 1] += start[l];
+    }
+    std::vector<uint32_t> idx(3 * n_gates);  // [in1 | in2 | out], each sorted by level
+    {
+        std::vector<uint64_t> at(start.begin(), start.end() - 1);
+        for (uint64_t g = 0; g < n_gates; ++g) {
+            const uint64_t pos = at[level[g]]++;
+            idx[pos] = in1[g];
+            idx[n_gates + pos] = in2[g];
+            idx[2 * n_gates + pos] = out[g];
+        }
+    }
+    CU(cudaSetDevice(ctx->device));
+    const uint32_t kn = p.k * p.n;
+    TmpBuf tmp(ctx);
+    uint32_t *d_idx, *c1, *c2, *co, *b1 = nullptr, *b2 = nullptr, *bo = nullptr;
+    CU(tmp.get(&d_idx, idx.size()));
+    CU(tmp.get(&c1, widest * kn));
+    CU(tmp.get(&c2, widest * kn));
+    CU(tmp.get(&co, widest * kn));
+    if (lwe) {
+        CU(tmp.get(&b1, widest));
+        CU(tmp.get(&b2, widest));
+        CU(tmp.get(&bo, widest));
+    }
+    // pageable source: the copy is staged before cudaMemcpyAsync returns, so `idx` may go out of scope
+    CU(cudaMemcpyAsync(d_idx, idx.data(), idx.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+    for (int64_t l = 0; l < L; ++l) {
+        const uint64_t s = start[l], B = start[l + 1] - s;
+        circuit_gather<<<unsigned(B), 256, 0, ctx->stream>>>(d_wires, lwe ? d_wires_b : nullptr, d_idx + s, d_idx + n_gates + s, c1, c2, b1,
+                                                           b2, kn);
+        CU(cudaGetLastError());
+        const int rc = mkfhe_eval_nand_dev(ctx, c1, b1, c2, b2, co, bo, B);
+        if (rc) return rc;
+        circuit_scatter<<<unsigned(B), 256, 0, ctx->stream>>>(d_wires, lwe ? d_wires_b : nullptr, d_idx + 2 * n_gates + s, co, bo, kn);
+        CU(cudaGetLastError());
+        ctx->launches += 2;
+    }
+    return MKFHE_OK;  // scratch returns to the pool in stream order (TmpBuf)
+}
+
+int mkfhe_eval_circuit(mkfhe_ctx* ctx, uint32_t* wires, uint32_t* wires_b, uint64_t n_wires, const uint32_t* in1, const uint32_t* in2,
+                       const uint32_t* out, uint64_t n_gates, uint32_t* n_levels) {
+    if (!ctx || !wires) return MKFHE_EINVAL;
+    const mkfhe_params& p = ctx->p;
+    const bool lwe = p.scheme == MKFHE_SCHEME_MKLWE;
+    if (lwe && !wires_b) return fail(ctx, MKFHE_EINVAL, "MKLWE circuits need wires_b");
+    CU(cudaSetDevice(ctx->device));
+    const size_t words = size_t(n_wires) * p.k * p.n;
+    TmpBuf tmp(ctx);
+    uint32_t *d_w, *d_b = nullptr;
+    CU(tmp.get(&d_w, words));
+    if (lwe) CU(tmp.get(&d_b, n_wires));
+    CU(cudaMemcpyAsync(d_w, wires, words * 4, cudaMemcpyHostToDevice, ctx->stream));
+    if (lwe) CU(cudaMemcpyAsync(d_b, wires_b, n_wires * 4, cudaMemcpyHostToDevice, ctx->stream));
+    const int rc = mkfhe_eval_circuit_dev(ctx, d_w, d_b, n_wires, in1, in2, out, n_gates, n_levels);
+    if (rc) return rc;
+    CU(cudaMemcpyAsync(wires, d_w, words * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (lwe) CU(cudaMemcpyAsync(wires_b, d_b, n_wires * 4, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
     return MKFHE_OK;
 }

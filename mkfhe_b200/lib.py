@@ -22,7 +22,7 @@ SYMBOLS = [
     "mkfhe_ctx_create", "mkfhe_ctx_destroy", "mkfhe_last_error", "mkfhe_ctx_set_stream", "mkfhe_ctx_synchronize",
     "mkfhe_load_bk", "mkfhe_load_pkey", "mkfhe_load_ksk_mntru", "mkfhe_load_ksk_mklwe", "mkfhe_load_ctnand",
     "mkfhe_eval_acc", "mkfhe_eval_acc_dev", "mkfhe_eval_nand", "mkfhe_eval_nand_dev", "mkfhe_ntt", "mkfhe_ntt_dev",
-    "mkfhe_load_sk", "mkfhe_decrypt", "mkfhe_decrypt_dev", "mkfhe_keygen_bk", "mkfhe_keygen_pkey", "mkfhe_keygen_ksk_mntru", "mkfhe_keygen_ksk_mklwe", "mkfhe_encrypt_mntru", "mkfhe_encrypt_mklwe", "mkfhe_keyfile_write", "mkfhe_keyfile_info", "mkfhe_keyfile_load",
+    "mkfhe_load_sk", "mkfhe_decrypt", "mkfhe_decrypt_dev", "mkfhe_eval_circuit", "mkfhe_eval_circuit_dev", "mkfhe_circuit_levels", "mkfhe_keygen_bk", "mkfhe_keygen_pkey", "mkfhe_keygen_ksk_mntru", "mkfhe_keygen_ksk_mklwe", "mkfhe_encrypt_mntru", "mkfhe_encrypt_mklwe", "mkfhe_keyfile_write", "mkfhe_keyfile_info", "mkfhe_keyfile_load",
     "mkfhe_decompose", "mkfhe_last_gate_timing", "mkfhe_launch_count", "mkfhe_device_bytes", "mkfhe_version", "mkfhe_measure_int32_peak", "mkfhe_measure_butterfly_peak",
 ]
 
@@ -65,6 +65,10 @@ def load():
     L.mkfhe_eval_acc_dev.argtypes = [vp, vp, vp, u32, vp, u64]
     L.mkfhe_eval_nand.argtypes = [vp, vp, vp, vp, vp, vp, vp, u64]
     L.mkfhe_eval_nand_dev.argtypes = [vp, vp, vp, vp, vp, vp, vp, u64]
+    L.mkfhe_eval_circuit.argtypes = [vp, vp, vp, u64, vp, vp, vp, u64, vp]
+    L.mkfhe_eval_circuit_dev.argtypes = [vp, vp, vp, u64, vp, vp, vp, u64, vp]
+    L.mkfhe_circuit_levels.argtypes = [u64, vp, vp, vp, u64, vp]
+    L.mkfhe_circuit_levels.restype = C.c_int64
     L.mkfhe_decrypt.argtypes = [vp, vp, vp, u32, vp, u64]
     L.mkfhe_decrypt_dev.argtypes = [vp, vp, vp, u32, vp, u64]
     L.mkfhe_keygen_bk.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32]

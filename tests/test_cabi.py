@@ -4,6 +4,7 @@ import ctypes
 import os
 import re
 
+import numpy as np
 import pytest
 
 import mkfhe_b200 as mk
@@ -77,3 +78,23 @@ def test_keyfile_write_info_roundtrip_and_corruption(tmp_path):
     open(path, "wb").write(b"not a key file at all, just some bytes" * 4)
     with pytest.raises(mk.MkfheError):
         mk.KeyFileInfo(path)
+
+
+def test_circuit_levelisation_needs_no_gpu():
+    """mkfhe_circuit_levels: the host-side levelisation behind mkfhe_eval_circuit (include/mkfhe_b200.h)."""
+    import mkfhe_b200 as mk
+
+    xor = [(0, 1, 2), (0, 2, 3), (1, 2, 4), (3, 4, 5)]
+    n, lev = mk.CircuitLevels(6, xor)
+    assert n == 3 and list(lev) == [0, 1, 1, 2]
+    # two independent chains interleave into shared levels
+    n, lev = mk.CircuitLevels(8, [(0, 1, 4), (2, 3, 5), (4, 5, 6), (0, 6, 7)])
+    assert n == 3 and list(lev) == [0, 0, 1, 2]
+    assert mk.CircuitLevels(3, np.zeros((0, 3), dtype=np.uint32))[0] == 0
+    for bad in ([(0, 0, 2)],              # one ciphertext on both inputs (binfhe-base-scheme.cpp:382-383)
+                [(0, 1, 6)],              # index out of range
+                [(0, 1, 2), (0, 1, 2)],   # a wire written twice
+                [(0, 2, 3), (0, 1, 2)],   # read before written
+                [(0, 1, 0)]):             # a gate overwriting its own input
+        with pytest.raises(mk.config_error):
+            mk.CircuitLevels(6, bad)

@@ -133,6 +133,68 @@ def test_drop_in_accumulator_through_reference_api(full):
     assert r.decrypt(gpu_out, gpu_b) == 0
 
 
+def _adder_netlist(bits, base_a, base_b, carry_in, first_free):
+    """Ripple-carry adder from NAND gates only: 9 per full adder.  Returns (gates, sum wires [bits + 1], next free wire)."""
+    gates, w = [], first_free
+
+    def nand(x, y):
+        nonlocal w
+        gates.append((x, y, w))
+        w += 1
+        return w - 1
+
+    sums, c = [], carry_in
+    for i in range(bits):
+        a, b = base_a + i, base_b + i
+        n1 = nand(a, b)
+        x = nand(nand(a, n1), nand(b, n1))       # a xor b
+        n4 = nand(x, c)
+        sums.append(nand(nand(x, n4), nand(c, n4)))  # x xor c
+        c = nand(n1, n4)                         # (a and b) or (x and c)
+    sums.append(c)
+    return gates, sums, w
+
+
+def test_adder_circuit_decrypts_to_the_sum(full):
+    """SURVEY 8f rank 4, "gate circuits on the batch API": 16 independent 4-bit ripple-carry adders (NAND only, 576 gates)
+    through mkfhe_eval_circuit -- one batch per level (12 launches of the gate kernel) instead of the reference's one
+    EvalBinGate per gate.  Every sum, decrypted by the reference's Decrypt, equals a + b (MK-LWE flavour); the first XOR
+    (4 gates, 3 levels) equals the reference's own EvalBinGate chain bit for bit (both flavours)."""
+    r, p, ctx, keys = full
+    rng = np.random.default_rng(17)
+    bits, inst = 4, 16
+    avals, bvals = rng.integers(0, 16, inst), rng.integers(0, 16, inst)
+    per = 2 * bits + 1  # a bits | b bits | carry-in (an encryption of 0)
+    gates, sums, w = [], [], per * inst
+    for t in range(inst):
+        gt, st, w = _adder_netlist(bits, per * t, per * t + bits, per * t + 2 * bits, w)
+        gates += gt
+        sums.append(st)
+    wires = np.zeros((w, p.k, p.n), dtype=np.uint32)
+    wb = np.zeros(w, dtype=np.uint32)
+    for t in range(inst):
+        plain = [(int(avals[t]) >> i) & 1 for i in range(bits)] + [(int(bvals[t]) >> i) & 1 for i in range(bits)] + [0]
+        for i, m in enumerate(plain):
+            ct, b = r.encrypt(m)
+            wires[per * t + i] = np.asarray(ct, dtype=np.uint32).reshape(p.k, p.n)
+            wb[per * t + i] = b
+    out, ob, levels = ctx.EvalCircuit(wires, np.array(gates, dtype=np.uint32), wb if p.scheme == 1 else None)
+    if ob is None:
+        ob = np.zeros(w, dtype=np.uint32)
+    assert levels == 2 * bits + 4  # the carry chain
+    # The reference's MKNTRU gate outputs do not compose: in the reference itself NAND(1, NAND(0, 1)) decrypts to 1 (checked on
+    # the CPU with its own Encrypt / EvalBinGate / Decrypt), so only the MK-LWE flavour has a meaningful sum.  Parity with the
+    # reference's chain (below) holds for both.
+    for t in range(inst if p.scheme == 1 else 0):
+        got = sum(r.decrypt(out[s].ravel(), int(ob[s])) << i for i, s in enumerate(sums[t]))
+        assert got == int(avals[t]) + int(bvals[t])
+    # the first adder's bit-0 XOR against the reference, gate by gate
+    ew = {0: (wires[0].ravel(), int(wb[0])), bits: (wires[bits].ravel(), int(wb[bits]))}
+    for i1, i2, o in gates[:4]:
+        ew[o] = r.eval_gate(ew[i1][0], ew[i1][1], ew[i2][0], ew[i2][1])
+        assert (out[o].ravel() == ew[o][0]).all() and int(ob[o]) == int(ew[o][1])
+
+
 def test_batched_gate_class_over_reference_objects(full):
     """integration/binfhe_batch_b200.h: the C++ EvalBinGateBatch a maintainer adds, compiled against the unmodified reference.
     It takes the reference's BinFHECryptoParams + UniEncBTKey (+ ctNAND), flattens and uploads them itself, takes vectors of

@@ -160,3 +160,54 @@ def test_keyfile_load_gives_the_same_gates(name, tmp_path):
     with pytest.raises(mk.MkfheError):
         ctx2.LoadKeyFile(path)
     ctx2.close()
+
+
+def _oracle_gate(o, g, x, bx, y, by):
+    return o.eval_nand(g["bk"], g["pkey"], g["kskA_any"], g["kskB_any"], g["ctnand_any"], x, bx, y, by)
+
+
+def test_circuit_matches_gate_by_gate_oracle(fx):
+    """mkfhe_eval_circuit: a NAND netlist (XOR of the first two gate inputs, then gates mixing every level) levelised and run
+    level by level on the device equals the same netlist evaluated gate by gate by the C oracle, bit for bit on every wire;
+    primary inputs stay untouched."""
+    g, ctx = fx
+    p = g["p"]
+    c1 = np.asarray(g["g_ct1"], dtype=np.uint32).reshape(-1, p.k, p.n)
+    c2 = np.asarray(g["g_ct2"], dtype=np.uint32).reshape(-1, p.k, p.n)
+    lwe = p.scheme == 1
+    b1 = np.asarray(g["g_b1"], dtype=np.uint32) if lwe else np.zeros(len(c1), np.uint32)
+    b2 = np.asarray(g["g_b2"], dtype=np.uint32) if lwe else np.zeros(len(c1), np.uint32)
+    # wires 0, 1: inputs; 2..5: XOR; 6: NAND(xor, w2) (levels 3); 7: NAND(w0, w6); 8: NAND(w3, w4) again (same as 5)
+    gates = np.array([(0, 1, 2), (0, 2, 3), (1, 2, 4), (3, 4, 5), (5, 2, 6), (0, 6, 7), (4, 3, 8)], dtype=np.uint32)
+    W = 9
+    wires = np.zeros((W, p.k, p.n), dtype=np.uint32)
+    wb = np.zeros(W, dtype=np.uint32)
+    wires[0], wires[1], wb[0], wb[1] = c1[0], c2[0], b1[0], b2[0]
+    out, ob, levels = ctx.EvalCircuit(wires, gates, wb if lwe else None)
+    assert levels == 5
+    assert (out[:2] == wires[:2]).all()
+    o = make_oracle(p)
+    ew, eb = wires.copy(), wb.copy()
+    for i1, i2, oo in gates:
+        r = _oracle_gate(o, g, ew[i1].ravel(), int(eb[i1]), ew[i2].ravel(), int(eb[i2]))
+        ew[oo], eb[oo] = np.asarray(r[0]).reshape(p.k, p.n), int(r[1])
+    assert (out == ew).all()
+    if lwe:
+        assert (ob == eb).all()
+    assert (out[8] == out[5]).all()  # commutativity of the input sum: NAND(w4, w3) == NAND(w3, w4)
+
+
+def test_circuit_argument_checks(fx):
+    import mkfhe_b200 as mk
+
+    g, ctx = fx
+    p = g["p"]
+    wires = np.zeros((4, p.k, p.n), dtype=np.uint32)
+    wb = np.zeros(4, dtype=np.uint32) if p.scheme == 1 else None
+    with pytest.raises(mk.config_error):
+        ctx.EvalCircuit(wires, [(0, 0, 2)], wb)
+    for bad in ([(0, 1, 4)], [(0, 1, 2), (0, 1, 2)], [(0, 2, 3), (0, 1, 2)]):
+        with pytest.raises(mk.MkfheError):
+            ctx.EvalCircuit(wires, bad, wb)
+    out, ob, levels = ctx.EvalCircuit(wires, np.zeros((0, 3), dtype=np.uint32), wb)  # empty netlist: nothing to do
+    assert levels == 0 and (out == wires).all()
