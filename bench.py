@@ -794,6 +794,121 @@ def run_keygen_arm(args):
     ctx.close()
 
 
+def run_circuit_arm(args):
+    """--workload circuit: --adders independent ripple-carry adders of --adder-bits bits as ONE NAND netlist through
+    mkfhe_eval_circuit: the library levelises it and runs one gate batch per level.  value = gates/s with
+    the wire table resident in HBM (mkfhe_eval_circuit_dev), e2e = the same through host buffers (whole wire table H2D and
+    D2H).  With oracle/_ref present the inputs are the reference's encryptions, a sample of sums is decrypted by the
+    reference's Decrypt and the first XOR is re-computed by the reference's EvalBinGate."""
+    import torch
+
+    import mkfhe_b200 as mk
+    from mkfhe_b200.netlist import ripple_carry_adders
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the GPU arm has no CPU fallback")
+    dev = torch.device("cuda", 0)
+    method = mk.MKNTRU_LWE if "LWE" in args.paramset else mk.MKNTRU
+    bits, inst = args.adder_bits, args.adders
+    P, keys, ct1, b1, ct2, b2, mbits, ref = make_workload(args.paramset, method, 64, seed=6)
+    P.device = 0
+    ctx = mk.BinFHEContext().GenerateFromParams(P)
+    lwe = ctx.is_lwe
+    ctx.LoadKeys(keys["bk"], keys["pkey"], ksk=keys.get("ksk"), kskA=keys.get("kskA"), kskB=keys.get("kskB"), ctnand=keys.get("ctnand"))
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    ctx.set_stream(stream.cuda_stream)
+    nl, sums = ripple_carry_adders(bits, inst)
+    gates, W, per = nl.array(), nl.n_wires, 2 * bits + 1
+    G = len(gates)
+    wires = np.zeros((W, P.k, P.n), dtype=np.uint32)
+    wb = np.zeros(W, dtype=np.uint32)
+    nu = len(ct1)
+    zero = ref.encrypt(0) if ref is not None else (ct1[0].ravel(), int(b1[0]))
+    avals, bvals = np.zeros(inst, dtype=np.int64), np.zeros(inst, dtype=np.int64)
+    for t in range(inst):
+        for i in range(bits):
+            j = (t * bits + i) % nu
+            wires[per * t + i], wb[per * t + i] = ct1[j], b1[j]
+            wires[per * t + bits + i], wb[per * t + bits + i] = ct2[j], b2[j]
+            if mbits is not None:
+                avals[t] |= int(mbits[0][j]) << i
+                bvals[t] |= int(mbits[1][j]) << i
+        wires[per * t + 2 * bits] = np.asarray(zero[0], dtype=np.uint32).reshape(P.k, P.n)
+        wb[per * t + 2 * bits] = zero[1]
+    d_w = torch.from_numpy(wires.view(np.int32)).to(dev)
+    d_b = torch.from_numpy(wb.view(np.int32)).to(dev) if lwe else None
+    levels = 0
+
+    def step_dev():
+        nonlocal levels
+        levels = ctx.EvalCircuitDevice(d_w, gates, d_b)
+
+    for _ in range(args.warmup):
+        step_dev()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(0)
+    sampler.start()
+    launches0 = ctx.launch_count()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    ev[0].record(stream)
+    for _ in range(args.steps):
+        step_dev()
+    ev[1].record(stream)
+    ev[1].synchronize()
+    dev_ms = ev[0].elapsed_time(ev[1])
+    launches = ctx.launch_count() - launches0
+    out, ob, _ = ctx.EvalCircuit(wires, gates, wb if lwe else None)  # warm the host path
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        out, ob, _ = ctx.EvalCircuit(wires, gates, wb if lwe else None)
+    e2e_s = time.perf_counter() - t0
+    clocks = sampler.stop()
+    assert (d_w.cpu().numpy().view(np.uint32).reshape(out.shape) == out).all(), "device-pointer and host-pointer paths disagree"
+    if ob is None:
+        ob = np.zeros(W, dtype=np.uint32)
+    checked = ref_gates = None
+    if ref is not None:
+        if lwe:  # the reference's MKNTRU gate outputs do not compose (DESIGN.md section 8), so only MK-LWE sums are meaningful
+            idx = list(range(0, inst, max(1, inst // 8)))[:8]
+            for t in idx:
+                got = sum(ref.decrypt(out[w].ravel(), int(ob[w])) << i for i, w in enumerate(sums[t]))
+                assert got == int(avals[t] + bvals[t]), "an adder does not decrypt to a + b"
+            checked = len(idx)
+        cur = {int(g[j]): (wires[g[j]].ravel(), int(wb[g[j]])) for g in gates[:2] for j in (0, 1) if g[j] < per * inst}
+        for i1, i2, o in gates[:4]:
+            cur[int(o)] = ref.eval_gate(cur[int(i1)][0], cur[int(i1)][1], cur[int(i2)][0], cur[int(i2)][1])
+            assert (out[o].ravel() == cur[int(o)][0]).all() and int(ob[o]) == int(cur[int(o)][1]), "circuit differs from the reference chain"
+        ref_gates = 4
+    wm = work_model(P)
+    step_s = dev_ms * 1e-3 / args.steps
+    bfly_peak = ctx.measure_butterfly_peak()
+    mm_ach = wm["modmul"] * G / step_s
+    line = {"metric": METRIC, "value": G / step_s, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": step_s * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u32",
+            "data": "synthetic circuit inputs: reference keygen + Encrypt (oracle/_ref)" if ref is not None else "synthetic (uniform residues)",
+            "config": {"workload": f"{args.paramset}: {inst} ripple-carry adders of {bits} bits as one NAND netlist ({G} gates, {levels} levels, "
+                                   f"{W} wires) through mkfhe_eval_circuit", "paramset": args.paramset, "gates": G, "levels": int(levels),
+                       "l2": f"wire table of {W * P.k * P.n * 4 >> 20} MiB, keys of {sum(np.asarray(v).size for v in keys.values()) * 4 >> 20} MiB per level"},
+            "e2e": {"value": G * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(W * (P.k * P.n + (1 if lwe else 0)) * 4),
+                    "d2h_bytes_per_step": int(W * (P.k * P.n + (1 if lwe else 0)) * 4)},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "int32", "kernel": "blind_rotate (one launch per level)", "achieved": mm_ach / 1e12,
+                         "peak": bfly_peak / 1e12, "unit": "Tmodmul/s", "frac": mm_ach / bfly_peak, "traffic": None,
+                         "model": "as --workload gates, over the whole step (all levels, gather/scatter included)",
+                         "modmul_per_gate": wm["modmul"]},
+            "clocks": clocks, "adders_checked": checked, "reference_gates_checked": ref_gates}
+    if not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        ng = cores * args.cpu_baseline_gates_per_thread
+        gps, kind, secs = cpu_gates_per_s(args.paramset, cores, ng, ref)
+        line["cpu_baseline"] = {"value": gps, "unit": UNIT, "cores": cores, "kind": kind,
+                                "sample": f"{ng} EvalBinGate(NAND) on {cores} threads in {secs:.1f}s, same paramset (the reference "
+                                          "runs a circuit as a loop of such calls)"}
+    emit(line)
+    ctx.close()
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -808,11 +923,13 @@ def main():
     ap.add_argument("--synthetic-keys", action="store_true", help="uniform random key residues instead of the reference keygen "
                     "(throughput does not depend on key values; the reference's keygen takes minutes at k >= 8)")
     ap.add_argument("--check-oracle", type=int, default=0, help="gates to re-compute on the CPU oracle after the run")
-    ap.add_argument("--workload", default="gates", choices=["gates", "sharded", "ntt", "keygen"],
+    ap.add_argument("--workload", default="gates", choices=["gates", "sharded", "ntt", "keygen", "circuit"],
                     help="gates: configs[1]/[2] (batch per GPU); sharded: configs[3] (--total-gates split over the GPUs, "
                          "counter-based inputs); ntt: configs[4] (batched transform micro-benchmark)")
     ap.add_argument("--total-gates", type=int, default=1 << 17)
     ap.add_argument("--chunk", type=int, default=16384, help="sharded: gates per launch")
+    ap.add_argument("--adders", type=int, default=512, help="circuit: independent adders in the netlist")
+    ap.add_argument("--adder-bits", type=int, default=8)
     ap.add_argument("--ntt-n", type=int, default=2048)
     ap.add_argument("--ntt-batch", type=int, default=1 << 18)
     args = ap.parse_args()
@@ -827,6 +944,8 @@ def main():
         run_ntt_arm(args)
     elif args.workload == "keygen":
         run_keygen_arm(args)
+    elif args.workload == "circuit":
+        run_circuit_arm(args)
     else:
         run_gpu_arm(args)
 

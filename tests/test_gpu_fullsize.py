@@ -133,28 +133,6 @@ def test_drop_in_accumulator_through_reference_api(full):
     assert r.decrypt(gpu_out, gpu_b) == 0
 
 
-def _adder_netlist(bits, base_a, base_b, carry_in, first_free):
-    """Ripple-carry adder from NAND gates only: 9 per full adder.  Returns (gates, sum wires [bits + 1], next free wire)."""
-    gates, w = [], first_free
-
-    def nand(x, y):
-        nonlocal w
-        gates.append((x, y, w))
-        w += 1
-        return w - 1
-
-    sums, c = [], carry_in
-    for i in range(bits):
-        a, b = base_a + i, base_b + i
-        n1 = nand(a, b)
-        x = nand(nand(a, n1), nand(b, n1))       # a xor b
-        n4 = nand(x, c)
-        sums.append(nand(nand(x, n4), nand(c, n4)))  # x xor c
-        c = nand(n1, n4)                         # (a and b) or (x and c)
-    sums.append(c)
-    return gates, sums, w
-
-
 def test_adder_circuit_decrypts_to_the_sum(full):
     """SURVEY 8f rank 4, "gate circuits on the batch API": 16 independent 4-bit ripple-carry adders (NAND only, 576 gates)
     through mkfhe_eval_circuit -- one batch per level (12 launches of the gate kernel) instead of the reference's one
@@ -164,12 +142,12 @@ def test_adder_circuit_decrypts_to_the_sum(full):
     rng = np.random.default_rng(17)
     bits, inst = 4, 16
     avals, bvals = rng.integers(0, 16, inst), rng.integers(0, 16, inst)
+    from mkfhe_b200.netlist import ripple_carry_adders
+
     per = 2 * bits + 1  # a bits | b bits | carry-in (an encryption of 0)
-    gates, sums, w = [], [], per * inst
-    for t in range(inst):
-        gt, st, w = _adder_netlist(bits, per * t, per * t + bits, per * t + 2 * bits, w)
-        gates += gt
-        sums.append(st)
+    nl, sums = ripple_carry_adders(bits, inst)
+    gates, w = nl.gates, nl.n_wires
+    assert len(gates) == 9 * bits * inst
     wires = np.zeros((w, p.k, p.n), dtype=np.uint32)
     wb = np.zeros(w, dtype=np.uint32)
     for t in range(inst):
