@@ -12,6 +12,7 @@
 //   gpu.LoadKeys(params, method, EK);            // once, after MKKeyGen (binfhe-base-scheme.cpp:198-338)
 //   gpu.LoadGateCiphertext(ctNAND);              // MKNTRU only: the ctGateGen output (binfhe-base-scheme.cpp:340-376)
 //   auto out = gpu.EvalBinGateBatch(NAND, ct1s, ct2s);
+//   gpu.EvalCircuit(wires, gates);               // a NAND netlist on a table of ciphertexts, one batch per level
 //
 // Compiled in this repository only as part of oracle/_ref (the reference built in place): ref_batch_b200_* in
 // oracle/ref_harness.cpp drive it, tests/test_gpu_fullsize.py compares its output objects with the reference's EvalBinGate.
@@ -48,6 +49,7 @@ public:
         bind(m_load_ksk_mklwe, "mkfhe_load_ksk_mklwe");
         bind(m_load_ctnand, "mkfhe_load_ctnand");
         bind(m_eval_nand, "mkfhe_eval_nand");
+        bind(m_eval_circuit, "mkfhe_eval_circuit");
     }
     BinFHEBatchB200(const BinFHEBatchB200&)            = delete;
     BinFHEBatchB200& operator=(const BinFHEBatchB200&) = delete;
@@ -199,7 +201,66 @@ public:
         return res;
     }
 
+    // A circuit of NAND gates: what a caller of the reference writes as a loop of EvalBinGate calls
+    // (binfhecontext.cpp:415-419).  `wires` holds the primary inputs (any entry a gate writes may be null on entry); gate g
+    // sets wires[gates[g][2]] = NAND(wires[gates[g][0]], wires[gates[g][1]]).  Gates in topological order; the library runs
+    // each level of the netlist as one batch.  Returns the number of levels.
+    struct Gate { uint32_t in1, in2, out; };
+    uint32_t EvalCircuit(std::vector<MKLWECiphertext>& wires, const std::vector<Gate>& gates) const {
+        need_ctx();
+        if (!m_lwe)
+            OPENFHE_THROW(config_error, "keys were loaded for matrix-NTRU ciphertexts");
+        const size_t W = wires.size(), kn = size_t(m_k) * m_n;
+        std::vector<uint32_t> flat(W * kn, 0), b(W, 0), i1, i2, o;
+        split(gates, W, i1, i2, o);
+        for (size_t w = 0; w < W; ++w) {
+            if (!wires[w])
+                continue;
+            shape(wires[w]->GetA());
+            for (uint32_t u = 0; u < m_k; ++u) copy(&flat[w * kn + size_t(u) * m_n], wires[w]->GetA()[u], m_n);
+            b[w] = u32(wires[w]->GetB());
+        }
+        uint32_t levels = 0;
+        check(m_eval_circuit(m_ctx, flat.data(), b.data(), W, i1.data(), i2.data(), o.data(), gates.size(), &levels), "mkfhe_eval_circuit");
+        for (uint32_t w : o) wires[w] = std::make_shared<MKLWECiphertextImpl>(rows(&flat[size_t(w) * kn]), NativeInteger(b[w]));
+        return levels;
+    }
+    uint32_t EvalCircuit(std::vector<MNTRUCiphertext>& wires, const std::vector<Gate>& gates) const {
+        need_ctx();
+        if (m_lwe)
+            OPENFHE_THROW(config_error, "keys were loaded for MK-LWE ciphertexts");
+        if (!m_have_nand)
+            OPENFHE_THROW(config_error, "LoadGateCiphertext has not been called");
+        const size_t W = wires.size(), kn = size_t(m_k) * m_n;
+        std::vector<uint32_t> flat(W * kn, 0), i1, i2, o;
+        split(gates, W, i1, i2, o);
+        for (size_t w = 0; w < W; ++w) {
+            if (!wires[w])
+                continue;
+            shape(wires[w]->GetElements());
+            for (uint32_t u = 0; u < m_k; ++u) copy(&flat[w * kn + size_t(u) * m_n], wires[w]->GetElements()[u], m_n);
+        }
+        uint32_t levels = 0;
+        check(m_eval_circuit(m_ctx, flat.data(), nullptr, W, i1.data(), i2.data(), o.data(), gates.size(), &levels), "mkfhe_eval_circuit");
+        for (uint32_t w : o) wires[w] = std::make_shared<MNTRUCiphertextImpl>(rows(&flat[size_t(w) * kn]));
+        return levels;
+    }
+
 private:
+    // index arrays of a netlist; the reference's independence check (binfhe-base-scheme.cpp:382-383) and the range check that
+    // must precede touching `wires` happen here, the remaining structure checks in the library
+    static void split(const std::vector<Gate>& gates, size_t W, std::vector<uint32_t>& i1, std::vector<uint32_t>& i2,
+                      std::vector<uint32_t>& o) {
+        for (const Gate& g : gates) {
+            if (g.in1 == g.in2)
+                OPENFHE_THROW(config_error, "Input ciphertexts should be independant");
+            if (g.in1 >= W || g.in2 >= W || g.out >= W)
+                OPENFHE_THROW(config_error, "EvalCircuit: wire index out of range");
+            i1.push_back(g.in1);
+            i2.push_back(g.in2);
+            o.push_back(g.out);
+        }
+    }
     static uint32_t u32(const NativeInteger& x) { return x.ConvertToInt<uint32_t>(); }
     static void copy(uint32_t* dst, const NativeVector& v, uint32_t len) { std::memcpy(dst, &v[0], sizeof(uint32_t) * len); }
     std::vector<NativeVector> rows(const uint32_t* src) const {
@@ -257,6 +318,7 @@ private:
     decltype(&mkfhe_load_ksk_mklwe) m_load_ksk_mklwe{nullptr};
     decltype(&mkfhe_load_ctnand) m_load_ctnand{nullptr};
     decltype(&mkfhe_eval_nand) m_eval_nand{nullptr};
+    decltype(&mkfhe_eval_circuit) m_eval_circuit{nullptr};
 };
 
 }  // namespace lbcrypto

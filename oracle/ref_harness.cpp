@@ -511,6 +511,53 @@ int ref_batch_b200_gates(void* h, const uint32_t* ct1, const uint32_t* b1, const
     });
 }
 
+// BinFHEBatchB200::EvalCircuit on reference ciphertext objects: wires [W][k][n] (+ b [W]) flat in/out, `is_input[w]` marks the
+// primary inputs (the other entries start as null pointers), gates as three index arrays.  dec (optional) receives the
+// reference's Decrypt of every wire that is set after the call.
+int ref_batch_b200_circuit(void* h, uint32_t* wires, uint32_t* wb, const uint8_t* is_input, uint64_t W, const uint32_t* in1,
+                           const uint32_t* in2, const uint32_t* out, uint64_t G, uint32_t* levels, int* dec) {
+    auto* c = static_cast<RefCtx*>(h);
+    return guarded(c, [&] {
+        if (!c->batch) throw std::runtime_error("ref_batch_b200_load has not been called");
+        const size_t kn = size_t(c->k) * c->n;
+        std::vector<BinFHEBatchB200::Gate> gates;
+        for (uint64_t g = 0; g < G; ++g) gates.push_back({in1[g], in2[g], out[g]});
+        if (c->scheme == 0) {
+            std::vector<MNTRUCiphertext> w(W);
+            for (uint64_t i = 0; i < W; ++i)
+                if (is_input[i]) w[i] = mk_mntru_ct(c, wires + i * kn, c->q);
+            *levels = c->batch->EvalCircuit(w, gates);
+            for (uint64_t i = 0; i < W; ++i) {
+                if (!w[i]) continue;
+                for (uint32_t u = 0; u < c->k; ++u) put(wires + i * kn + size_t(u) * c->n, w[i]->GetElements()[u]);
+                if (dec) {
+                    MNTRUPlaintext m = 0;
+                    ConstMNTRUCiphertext x = w[i];
+                    c->sch->MNTRU()->Decrypt(c->mntru, c->skN, x, &m, 4);
+                    dec[i] = int(m);
+                }
+            }
+        }
+        else {
+            std::vector<MKLWECiphertext> w(W);
+            for (uint64_t i = 0; i < W; ++i)
+                if (is_input[i]) w[i] = mk_mklwe_ct(c, wires + i * kn, wb[i], c->q);
+            *levels = c->batch->EvalCircuit(w, gates);
+            for (uint64_t i = 0; i < W; ++i) {
+                if (!w[i]) continue;
+                for (uint32_t u = 0; u < c->k; ++u) put(wires + i * kn + size_t(u) * c->n, w[i]->GetA()[u]);
+                wb[i] = w[i]->GetB().ConvertToInt<uint32_t>();
+                if (dec) {
+                    MKLWEPlaintext m = 0;
+                    ConstMKLWECiphertext x = w[i];
+                    c->sch->MKLWE()->Decrypt(c->mklwe, c->skL, x, &m, 4);
+                    dec[i] = int(m);
+                }
+            }
+        }
+    });
+}
+
 // Argument checks of EvalBinGateBatch: returns a bit mask of the cases that threw the reference's config_error
 // (1: gate other than NAND, 2: the same ciphertext object on both sides, 4: input vectors of different length).
 int ref_batch_b200_errors(void* h, int* mask) {

@@ -57,6 +57,8 @@ def lib():
         L.ref_batch_b200_load.argtypes = [C.c_void_p, C.c_char_p]
         L.ref_batch_b200_gates.argtypes = [C.c_void_p, U32P, U32P, U32P, U32P, U32P, U32P, C.c_uint64, C.POINTER(C.c_int)]
         L.ref_batch_b200_errors.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
+        L.ref_batch_b200_circuit.argtypes = [C.c_void_p, U32P, U32P, C.POINTER(C.c_uint8), C.c_uint64, U32P, U32P, U32P, C.c_uint64,
+                                             U32P, C.POINTER(C.c_int)]
         _lib = L
     return _lib
 
@@ -262,3 +264,18 @@ class Ref:
         m = C.c_int(0)
         self._ck(self.L.ref_batch_b200_errors(self.h, C.byref(m)), "ref_batch_b200_errors")
         return int(m.value)
+
+    def batch_b200_circuit(self, wires, wb, n_inputs, gates):
+        """BinFHEBatchB200::EvalCircuit: wires [W][k][n] with the first n_inputs rows set, gates [G][3].  Returns (wires, b,
+        levels, the reference's Decrypt of every wire)."""
+        w = np.ascontiguousarray(wires, dtype=np.uint32).copy()
+        W = w.shape[0]
+        b = np.ascontiguousarray(wb if wb is not None else np.zeros(W), dtype=np.uint32).copy()
+        g = np.ascontiguousarray(gates, dtype=np.uint32).reshape(-1, 3)
+        i1, i2, o = (np.ascontiguousarray(g[:, j]) for j in range(3))
+        isin = (C.c_uint8 * W)(*([1] * n_inputs + [0] * (W - n_inputs)))
+        lv = np.zeros(1, dtype=np.uint32)
+        dec = (C.c_int * W)()
+        self._ck(self.L.ref_batch_b200_circuit(self.h, _p(w), _p(b), isin, W, _p(i1), _p(i2), _p(o), len(g), _p(lv), dec),
+                 "ref_batch_b200_circuit")
+        return w, b, int(lv[0]), np.array(list(dec), dtype=np.int64)

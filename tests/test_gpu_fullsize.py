@@ -194,6 +194,21 @@ def test_batched_gate_class_over_reference_objects(full):
         eo, eb = r.eval_gate(ct1[g].ravel(), int(b1[g]), ct2[g].ravel(), int(b2[g]))
         assert (out[g].ravel() == eo).all() and int(bout[g]) == int(eb)
     assert r.batch_b200_errors() == 7
+    # EvalCircuit of the same class: a + b for one 2-bit adder on reference ciphertext objects
+    from mkfhe_b200.netlist import ripple_carry_adders
+
+    nl, sums = ripple_carry_adders(2, 1)
+    plain = [1, 1, 1, 0, 0]  # a = 3, b = 1, carry-in 0
+    wires = np.zeros((nl.n_wires, p.k, p.n), dtype=np.uint32)
+    wb = np.zeros(nl.n_wires, dtype=np.uint32)
+    for i, m in enumerate(plain):
+        ct, b = r.encrypt(m)
+        wires[i], wb[i] = np.asarray(ct, dtype=np.uint32).reshape(p.k, p.n), b
+    cw, cb, levels, cdec = r.batch_b200_circuit(wires, wb, len(plain), nl.array())
+    gw, gb, glev = ctx.EvalCircuit(wires, nl.array(), wb if p.scheme == 1 else None)
+    assert levels == glev == 8 and (cw == gw).all() and (p.scheme == 0 or (cb == gb).all())
+    if p.scheme == 1:  # MKNTRU outputs do not compose in the reference (see test_adder_circuit_decrypts_to_the_sum)
+        assert sum(int(cdec[s]) << i for i, s in enumerate(sums[0])) == 4
 
 
 @pytest.mark.gpu
