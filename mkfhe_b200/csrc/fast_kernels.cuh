@@ -1179,8 +1179,12 @@ inline bool fast_use_alias(const DevCtx& d) {
 // in all three: 8 / 16 / 32 warps, 128 / 128 / 64 registers);   k = 8: 1398 vs 1252 (2 groups);   k = 4: 4246 vs 3013 -- where
 // several gates fit an SM anyway, the idle groups of the sumV phase cost more than the shorter step brings.
 // So: two groups from k = 16 on.
-inline uint32_t fast_groups(const DevCtx& d) {
-    uint32_t G = d.k >= 16 ? 2 : 1;
+// Small batches are a different regime: with at most one gate per SM the SM is latency-bound, and the shorter step wins
+// (profiles/r1_s49_latency_groups.txt, ms per launch at 148 gates, 1 group vs 2: boolean-mklwe 11.29 vs 9.31, boolean-mkntru
+// 13.80 vs 12.71, k = 4 43.2 vs 37.0; at 296 gates one group is ahead again, 16.1 vs 18.6).  So: two groups whenever the batch
+// does not exceed the SM count -- the single gate of the drop-in accumulator and the narrow levels of a circuit.
+inline uint32_t fast_groups(const DevCtx& d, uint32_t batch, int sms) {
+    uint32_t G = (d.k >= 16 || (d.k >= 2 && batch <= uint32_t(sms))) ? 2 : 1;
     if (const char* e = getenv("MKFHE_GROUPS")) G = uint32_t(atoi(e));
     if (G != 2 && G != 4) return 1;
     if (d.k > 16 || d.k < G) return 1;
@@ -1190,7 +1194,7 @@ inline uint32_t fast_groups(const DevCtx& d) {
 inline cudaError_t fast_blind_rotate(FastState& F, const DevCtx& d, bool gate, const GateIO& io, uint32_t batch, cudaStream_t st,
                                      uint64_t* launches) {
     const bool xzw = d.variant == 0;
-    const uint32_t G = fast_groups(d);
+    const uint32_t G = fast_groups(d, batch, F.sms);
     const bool alias = G > 1 ? grouped_smem_bytes(d.k, d.n, G, false) > 227 * 1024 : fast_use_alias(d);
     const size_t smem = G > 1 ? grouped_smem_bytes(d.k, d.n, G, alias) : fast_smem_bytes(d.k, d.n, alias, xzw);
     auto launch = [&](auto kern) -> cudaError_t {

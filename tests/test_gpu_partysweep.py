@@ -12,16 +12,25 @@ from util import make_oracle
 pytestmark = pytest.mark.gpu
 
 CASES = [  # paramset, environment overrides, gates, which gate to re-compute on the CPU oracle
-    ("STD100_MKNTRU_2", {}, 5, 4),
-    ("STD100_MKNTRU_2", {"MKFHE_GROUPS": "2"}, 3, 0),
-    ("STD100_MKNTRU_2", {"MKFHE_FAST_ALIAS": "1"}, 3, 2),
-    ("STD100_MKNTRU_LWE_2", {"MKFHE_MINB": "4"}, 3, 1),
-    ("STD100_MKNTRU_3", {}, 2, 1),
+    # batches up to the SM count run on the party-parallel kernel by default (two groups); MKFHE_GROUPS=1 selects the
+    # one-group kernel that larger batches use
+    ("STD100_MKNTRU_LWE", {}, 3, 2),
+    ("STD100_MKNTRU_LWE", {"MKFHE_GROUPS": "1"}, 3, 0),
+    ("STD100_MKNTRU", {}, 3, 1),
+    ("STD100_MKNTRU", {"MKFHE_GROUPS": "1"}, 3, 0),
+    ("STD100_MKNTRU_2", {"MKFHE_GROUPS": "1"}, 5, 4),
+    ("STD100_MKNTRU_2", {}, 3, 0),
+    ("STD100_MKNTRU_2", {"MKFHE_GROUPS": "4"}, 3, 1),
+    ("STD100_MKNTRU_2", {"MKFHE_GROUPS": "1", "MKFHE_FAST_ALIAS": "1"}, 3, 2),
+    ("STD100_MKNTRU_LWE_2", {"MKFHE_GROUPS": "1", "MKFHE_MINB": "4"}, 3, 1),
+    ("STD100_MKNTRU_LWE_2", {}, 3, 2),
+    ("STD100_MKNTRU_3", {"MKFHE_GROUPS": "1"}, 2, 1),
+    ("STD100_MKNTRU_3", {}, 2, 0),
     ("STD100_MKNTRU_4", {}, 2, 0),
 ]
 
 
-@pytest.mark.parametrize("paramset,env,gates,pick", CASES, ids=[f"{c[0]}-{'-'.join(c[1]) or 'default'}" for c in CASES])
+@pytest.mark.parametrize("paramset,env,gates,pick", CASES, ids=[f"{c[0]}-{'-'.join(k + v for k, v in c[1].items()) or 'default'}" for c in CASES])
 def test_large_party_counts_vs_oracle(paramset, env, gates, pick, monkeypatch):
     if paramset not in mk.PARAMSETS:
         pytest.skip(f"{paramset} not in the parameter table")
