@@ -77,7 +77,8 @@ int mkfhe_ctx_create(const mkfhe_params* p, mkfhe_ctx** out);
 void mkfhe_ctx_destroy(mkfhe_ctx* ctx);
 /* text of the last error on ctx (ctx == NULL: last mkfhe_ctx_create failure on this thread) */
 const char* mkfhe_last_error(const mkfhe_ctx* ctx);
-/* use `cuda_stream` (a cudaStream_t) for all later work of this context; NULL = the context's own stream */
+/* use `cuda_stream` (a cudaStream_t) for all later work of this context; NULL = the context's own stream.  Waits for the work
+ * already enqueued on the previous stream (the context's workspaces and pooled scratch are ordered on one stream at a time). */
 int mkfhe_ctx_set_stream(mkfhe_ctx* ctx, void* cuda_stream);
 /* block until all work enqueued by this context has finished */
 int mkfhe_ctx_synchronize(mkfhe_ctx* ctx);

@@ -380,7 +380,13 @@ void mkfhe_ctx_destroy(mkfhe_ctx* ctx) {
 
 int mkfhe_ctx_set_stream(mkfhe_ctx* ctx, void* s) {
     if (!ctx) return MKFHE_EINVAL;
-    ctx->stream = s ? static_cast<cudaStream_t>(s) : ctx->own_stream;
+    cudaStream_t next = s ? static_cast<cudaStream_t>(s) : ctx->own_stream;
+    if (next != ctx->stream) {
+        // work and stream-ordered scratch frees of the old stream finish before anything is enqueued on the new one
+        CU(cudaSetDevice(ctx->device));
+        CU(cudaStreamSynchronize(ctx->stream));
+    }
+    ctx->stream = next;
     return MKFHE_OK;
 }
 int mkfhe_ctx_synchronize(mkfhe_ctx* ctx) {
