@@ -1209,6 +1209,10 @@ inline cudaError_t fast_blind_rotate(FastState& F, const DevCtx& d, bool gate, c
     // XZW at 64 registers spills in the step loop; 3 gates per SM with 80 registers measured 3% faster than 4 with 64
     // (16.66k vs 16.17k gates/s, boolean-mkntru k = 2, profiles/r1_s28_xzw_quick.txt); XZW_B measured equal, stays at 4
     if (xzw && minb > 3) minb = 3;
+    // a batch that puts fewer gates on an SM than the budget allows gets the registers of the absent ones: ms per launch at
+    // 296 gates, 64 / 80 / 128 registers: 16.14 / 15.57 / 14.91 (boolean-mklwe); at 444: 22.31 / 21.56 / 22.72
+    // (profiles/r1_s57_minb_midrange.txt)
+    minb = std::min(minb, std::max(2, int((batch + uint32_t(F.sms) - 1) / uint32_t(F.sms))));
     if (const char* ev = getenv("MKFHE_MINB")) minb = std::min(4, std::max(2, atoi(ev)));
     if (alias) minb = 4;  // the fallback layout is built for the 64-register budget only
     if (G > 1) {
