@@ -11,10 +11,13 @@ generates, NCCL broadcast) and bootstraps its own batch (weak scaling, no data-p
 after the timed region.
 
 One JSON line on stdout (rank 0).  `value` = gates/s with inputs resident in HBM; `e2e` = the same through the C ABI with
-host buffers (H2D + D2H inside the timed region); `roofline` = integer-pipe fraction of the blind-rotation kernel against
-the IMAD rate measured on this GPU in this run (SURVEY.md section 8d cost model: 7 instr / butterfly, 5 / pointwise MAC);
-`roofline_hbm` = key-stream bytes against MEASURED_PEAKS.json; `cpu_baseline` = the reference's own code (oracle/_ref,
-compiled unmodified) on all host cores over a bounded sample.
+host buffers (H2D + D2H inside the timed region; N > 1: + the result gather); `roofline` = modular multiplications per second
+of the blind-rotation kernel (SURVEY.md section 8d count) against the lazy-butterfly rate measured on this GPU in this run,
+and against the analytic 8-cycle floor; `roofline_hbm` = key-stream bytes against MEASURED_PEAKS.json; `cpu_baseline` = the
+reference's own code (oracle/_ref, compiled unmodified) on all host cores over a bounded sample, plus the single-thread
+single-gate latency the reference's examples print.  The default workload adds `also.boolean_mkntru`: the same measurement
+for STD100_MKNTRU (the XZW accumulator of mk-acc-xzw.cpp), k = 2, same batch.  Parity inside the run (outside the timed
+regions): every output decrypted = NAND, 64 gates bit-exact against the CPU oracle.
 """
 from __future__ import annotations
 
@@ -89,16 +92,29 @@ def ncu_traffic(paramset, batch):
 
 # ---------------------------------------------------------------- clocks sampling (B200_PROFILING.md recipe)
 class ClockSampler:
+    """nvidia-smi clocks / throttle reasons every 100 ms while a timed region runs (the recipe's clocks line), plus one
+    synchronous sample at start() and one at stop(), so a region shorter than the sampling period still has a record; arms
+    whose K steps would take well under a second repeat them until the region is long enough to be sampled under load."""
     Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index: int):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.proc, self.edge = index, [], None, []
+
+    def _once(self):
+        try:
+            out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits"],
+                                 capture_output=True, text=True, timeout=20).stdout
+            for line in out.splitlines():
+                self.edge.append([x.strip() for x in line.split(",")])
+        except Exception as e:
+            log("clock sampler: one-shot query failed:", e)
 
     def start(self):
+        self._once()
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE, text=True)
+                                          "--format=csv,noheader,nounits", "-lms", "100"], stdout=subprocess.PIPE, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except Exception as e:  # nvidia-smi missing: report it, do not fake numbers
             log("clock sampler unavailable:", e)
@@ -110,20 +126,22 @@ class ClockSampler:
     def stop(self):
         if self.proc:
             self.proc.terminate()
-        sm = sorted(int(r[1]) for r in self.rows if len(r) > 2 and r[1].isdigit())
-        mx = [int(r[2]) for r in self.rows if len(r) > 2 and r[2].isdigit()]
+        self._once()
+        rows = self.rows if self.rows else self.edge
+        sm = sorted(int(r[1]) for r in rows if len(r) > 2 and r[1].isdigit())
+        mx = [int(r[2]) for r in rows + self.edge if len(r) > 2 and r[2].isdigit()]
         reasons = set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        for r in rows + self.edge:
             for nme, v in zip(names, r[5:9]):
                 if v.lower().startswith("active"):
                     reasons.add(nme)
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx[0] if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "samples_during": len(self.rows), "samples_edge": len(self.edge)}
 
 
 # ---------------------------------------------------------------- workload (keys + ciphertexts)
-def make_workload(paramset: str, method: str, batch: int, seed: int):
+def make_workload(paramset: str, method: str, batch: int, seed: int, encrypt: bool = True):
     """Keys and input ciphertexts.  With the prebuilt reference present (oracle/_ref) they are the reference's own keygen and
     Encrypt output, so a sample of results can be decrypted and checked = NAND after the run; otherwise random residues of
     the right shapes (throughput is data-independent).  Returns (Params, keys dict, ct1, b1, ct2, b2, bits or None, ref)."""
@@ -143,6 +161,9 @@ def make_workload(paramset: str, method: str, batch: int, seed: int):
         else:
             keys["ksk"], _ = r.ksk_mntru()
             keys["ctnand"] = r.ctnand()
+        if not encrypt:  # the caller builds its own inputs from this context (distinct_gate_inputs)
+            log(f"[bench] reference keygen: {time.time() - t0:.1f}s (data: reference keys)")
+            return P, keys, None, None, None, None, None, r
         nuniq = min(batch, 64)  # distinct fresh encryptions, tiled to the batch
         m0, m1 = rng.integers(0, 2, nuniq), rng.integers(0, 2, nuniq)
         e0 = [r.encrypt(int(m)) for m in m0]
@@ -197,43 +218,65 @@ def cpu_gates_per_s(paramset: str, threads: int, gates: int, ref=None):
     return gates / secs, "port", secs
 
 
+def reference_gates(paramset, steps, warmup, gates_per_thread):
+    """The reference's EvalBinGate(NAND) for `paramset` on all host threads: K steps of threads * gates_per_thread gates."""
+    from oracle import refapi
+
+    cores = os.cpu_count() or 1
+    threads = cores
+    gates_per_step = max(threads, 1) * gates_per_thread
+    ref = None
+    if refapi.available() and paramset in refapi.PARAMSETS:
+        ref = refapi.Ref.from_paramset(paramset)
+        ref.keygen()
+    for _ in range(warmup):
+        cpu_gates_per_s(paramset, threads, threads, ref)
+    times, kind = [], "port"
+    for _ in range(steps):
+        gps, kind, secs = cpu_gates_per_s(paramset, threads, gates_per_step, ref)
+        times.append(secs)
+    total = sum(times)
+    value = gates_per_step * steps / total
+    sample = f"{steps} steps x {gates_per_step} EvalBinGate(NAND) on {threads} threads, shared keys"
+    cb = {"value": value, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample}
+    if ref is not None:
+        ms = sorted(ref.time_gate(5))
+        cb["single_thread_ms"] = ms[len(ms) // 2]
+        cb["single_thread_sample"] = "median of 5 single EvalBinGate(NAND) calls, steady_clock, 1 thread"
+    return value, 1e3 * total / steps, kind, cb
+
+
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return  # rank 0 alone runs the CPU arm; the others exit 0 without work
-    cores = os.cpu_count() or 1
-    threads = cores
-    gates_per_step = max(threads, 1) * args.ref_gates_per_thread
-    from oracle import refapi
-
-    ref = None
-    if refapi.available() and args.paramset in refapi.PARAMSETS:
-        ref = refapi.Ref.from_paramset(args.paramset)
-        ref.keygen()
-    for _ in range(args.warmup):
-        cpu_gates_per_s(args.paramset, threads, threads, ref)
-    times, kind = [], "port"
-    for _ in range(args.steps):
-        gps, kind, secs = cpu_gates_per_s(args.paramset, threads, gates_per_step, ref)
-        times.append(secs)
-    total = sum(times)
-    value = gates_per_step * args.steps / total
-    sample = f"{args.steps} steps x {gates_per_step} EvalBinGate(NAND) on {threads} threads, shared keys"
+    value, ms_step, kind, cb = reference_gates(args.paramset, args.steps, args.warmup, args.ref_gates_per_thread)
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u32", "data": "reference keygen + Encrypt" if kind == "reference" else "synthetic",
-            "config": workload_config(args),
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
+            "config": workload_config(args), "cpu_baseline": cb,
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
+    if args.paramset == "STD100_MKNTRU_LWE" and not args.no_also:  # the boolean-mkntru block of the GPU arm, on the CPU
+        v2, ms2, kind2, cb2 = reference_gates("STD100_MKNTRU", min(args.steps, 2), min(args.warmup, 1), max(1, args.ref_gates_per_thread // 2))
+        line["also"] = {"boolean_mkntru": {"impl": "reference", "metric": METRIC, "value": v2, "unit": UNIT, "ms_per_step": ms2,
+                                           "config": gates_config("STD100_MKNTRU", args.batch, args.gpus), "cpu_baseline": cb2}}
     emit(line)
 
 
+def gates_config(paramset, batch, world, distinct=None):
+    lwe = "LWE" in paramset
+    k = {"": 2, "2": 4, "3": 8, "4": 16}.get(paramset.rsplit("_", 1)[-1] if paramset[-1].isdigit() else "", 2)
+    cfg = {"workload": f"{paramset} ({'boolean-mklwe' if lwe else 'boolean-mkntru'} shape, k={k}), NAND gate batch {batch} per GPU",
+           "paramset": paramset, "batch_per_gpu": batch, "l2": "L2 flushed (256 MiB write) between timed steps",
+           "parallelism": f"gates sharded x{world}, keys replicated"}
+    if distinct is not None:
+        cfg["distinct_gates"] = distinct
+    return cfg
+
+
 def workload_config(args, batch=None):
-    return {"workload": f"{args.paramset} ({'boolean-mklwe' if 'LWE' in args.paramset else 'boolean-mkntru'} shape), "
-                        f"NAND gate batch {batch if batch is not None else args.batch} per GPU",
-            "paramset": args.paramset, "batch_per_gpu": batch if batch is not None else args.batch,
-            "l2": "L2 flushed (256 MiB write) between timed steps", "parallelism": f"gates sharded x{args.gpus}, keys replicated"}
+    return gates_config(args.paramset, batch if batch is not None else args.batch, args.gpus)
 
 
 def make_oracle(P):
@@ -243,94 +286,145 @@ def make_oracle(P):
                           baseKS=P.baseKS, dKS=P.dKS, variant=P.variant, scheme=P.scheme)
 
 
+# ---------------------------------------------------------------- GPU arm
+def distinct_gate_inputs(ctx, P, ref, rng, B):
+    """B DISTINCT gates from 2 * nu reference encryptions (nu = min(64, ceil(sqrt(B)))): all nu x nu pairings.
+    boolean-mklwe: the paired ciphertexts are REFRESHED ones (outputs of a first NAND level computed here on the GPU) -- the
+    inputs every interior gate of a circuit sees, dense mod q; the reference's MKLWE Encrypt samples `a` from a narrow
+    Gaussian (mklwe-pke.cpp:53-54), so fresh ciphertexts rotate by ~0 everywhere, a degenerate input.  boolean-mkntru: fresh
+    encryptions are dense already (ct = (m q/4 + e) F^-1, mntru-pke.cpp:158-205) and are paired directly; refreshed MKNTRU
+    outputs do not compose in the reference itself, so a second level would not decrypt to NAND.
+    Returns ct1, b1, ct2, b2 [B...] and the expected plaintext of every gate."""
+    lwe = P.scheme == 1
+    nu = min(64, max(2, int(np.ceil(np.sqrt(B)))))
+    m0, m1 = rng.integers(0, 2, nu).astype(np.int64), rng.integers(0, 2, nu).astype(np.int64)
+    e0 = [ref.encrypt(int(m)) for m in m0]
+    e1 = [ref.encrypt(int(m)) for m in m1]
+    f1 = np.array([x[0] for x in e0], dtype=np.uint32).reshape(nu, P.k, P.n)
+    f2 = np.array([x[0] for x in e1], dtype=np.uint32).reshape(nu, P.k, P.n)
+    fb1 = np.array([x[1] for x in e0], dtype=np.uint32)
+    fb2 = np.array([x[1] for x in e1], dtype=np.uint32)
+    if lwe:
+        r1 = lambda a: np.roll(a, 1, axis=0)
+        x, bx = ctx.EvalBinGate("NAND", f1, f2, fb1, fb2)
+        y, by = ctx.EvalBinGate("NAND", r1(f1), f2, r1(fb1), fb2)
+        mx, my = 1 - (m0 & m1), 1 - (r1(m0) & m1)
+    else:
+        x, bx, y, by, mx, my = f1, fb1, f2, fb2, m0, m1
+    g = np.arange(B) % (nu * nu)
+    i, j = g // nu, g % nu
+    c = np.ascontiguousarray
+    return c(x[i]), c(np.asarray(bx)[i]), c(y[j]), c(np.asarray(by)[j]), (1 - (mx[i] & my[j])).astype(np.int64), nu * nu
+
+
 def check_against_oracle(P, keys, ct1, b1, ct2, b2, out, bout, count):
-    """Bit-exact check of `count` gates (first, last, evenly spread) against the CPU oracle, outside the timed region.
-    The oracle is the checker here, never the thing measured."""
+    """Bit-exact check of `count` gates (first, last, evenly spread) against the CPU oracle on all host threads (the C
+    library releases the GIL), outside the timed region.  The oracle is the checker here, never the thing measured."""
     if not count:
         return 0
+    from concurrent.futures import ThreadPoolExecutor
+
     o = make_oracle(P)
     B = len(out)
     idx = sorted(set(int(x) for x in np.linspace(0, B - 1, count)))
     t0 = time.time()
-    for i in idx:
+
+    def one(i):
         eo, eb = o.eval_nand(keys["bk"], keys["pkey"], keys.get("kskA", keys.get("ksk")), keys.get("kskB"), keys.get("ctnand"),
                              np.ascontiguousarray(ct1[i]).ravel(), int(b1[i]) if b1 is not None else 0,
                              np.ascontiguousarray(ct2[i]).ravel(), int(b2[i]) if b2 is not None else 0)
-        ok = (out[i].ravel() == eo).all() and (bout is None or int(bout[i]) == eb)
-        if not ok:
-            raise SystemExit(f"bench.py: gate {i} differs from the oracle")
+        return bool((out[i].ravel() == eo).all() and (bout is None or int(bout[i]) == eb))
+
+    with ThreadPoolExecutor(max_workers=os.cpu_count() or 1) as ex:
+        ok = list(ex.map(one, idx))
+    if not all(ok):
+        raise SystemExit(f"bench.py: gate {idx[ok.index(False)]} differs from the oracle")
     log(f"[bench] {len(idx)} gates bit-exact vs the CPU oracle ({time.time() - t0:.1f}s)")
     return len(idx)
 
 
-# ---------------------------------------------------------------- GPU arm
-def run_gpu_arm(args):
-    import torch
+class GpuEnv:
+    """Process-wide state of the GPU arm: rank, device, communicator, one side stream, the L2 flush buffer."""
+
+    def __init__(self):
+        import torch
+
+        self.torch = torch
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device; the GPU arm has no CPU fallback (use --impl reference for the CPU arm)")
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        self.dist, self.nccl_init_s = None, 0.0
+        if self.world > 1:
+            import torch.distributed as dist
+
+            t0 = time.time()
+            dist.init_process_group("nccl", device_id=self.dev)
+            w = torch.ones(1, device=self.dev)
+            dist.all_reduce(w)  # the first collective builds the communicator (rings / NVLS trees)
+            torch.cuda.synchronize()
+            self.nccl_init_s = time.time() - t0
+            self.dist = dist
+        self.stream = torch.cuda.Stream(device=self.dev)  # an explicit stream for torch and the library alike
+        torch.cuda.set_stream(self.stream)
+        self.flush = torch.empty(256 << 20, dtype=torch.uint8, device=self.dev)
+        self.smi_index = self.local if os.environ.get("CUDA_VISIBLE_DEVICES") is None else \
+            int(os.environ["CUDA_VISIBLE_DEVICES"].split(",")[self.local])
+
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, values):
+        t = self.torch.tensor(values, dtype=self.torch.float64, device=self.dev)
+        if self.dist is not None:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return [float(x) for x in t.tolist()]
+
+
+def measure_gate_batch(env, paramset, B, steps, warmup, check_oracle, cpu_gates_per_thread, no_cpu_baseline, seed=2):
+    """K timed steps of EvalBinGate(NAND) over one batch of B gates per GPU for `paramset`; returns (on rank 0) the fields of
+    a bench line: value / e2e / roofline / checks / cpu_baseline.  Every rank runs it; only rank 0 gets the dict."""
+    import ctypes as C
 
     import mkfhe_b200 as mk
     from mkfhe_b200 import shard
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device; the GPU arm has no CPU fallback (use --impl reference for the CPU arm)")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-
-        dist.init_process_group("nccl", device_id=dev)
-    method = mk.MKNTRU_LWE if "LWE" in args.paramset else mk.MKNTRU
-    B = args.batch
-
-    # ---- keys: rank 0 generates on the host, everyone receives the flattened bytes over NCCL (NVLink) ----
-    ref, bits = None, None
+    torch, dist, dev, rank, world = env.torch, env.dist, env.dev, env.rank, env.world
+    method = mk.MKNTRU_LWE if "LWE" in paramset else mk.MKNTRU
+    # ---- keys: rank 0 generates on the host (the reference's own keygen when oracle/_ref is present) and loads them; the
+    # RESIDENT images are then broadcast device to device into every other rank's context (mkfhe_b200/shard.py) ----
+    ref, bits, keys = None, None, None
     if rank == 0:
-        P, keys, ct1, b1, ct2, b2, bits, ref = make_workload(args.paramset, method, B, seed=2)
+        P, keys, ct1, b1, ct2, b2, bits, ref = make_workload(paramset, method, B, seed=seed, encrypt=False)
     else:
-        P = mk.derive_params(mk.PARAMSETS[args.paramset], method)
-        keys = None
-    P.device = local
+        P = mk.derive_params(mk.PARAMSETS[paramset], method)
+    P.device = env.local
     ctx = mk.BinFHEContext().GenerateFromParams(P)
+    ctx.set_stream(env.stream.cuda_stream)
     lwe = ctx.is_lwe
-    # keys: rank 0 -> every rank, device to device (mkfhe_b200/shard.py)
     torch.cuda.synchronize()
     t0 = time.time()
-    dkeys = shard.broadcast_keys(keys, dev, dist)
-    torch.cuda.synchronize()
-    t_bcast = time.time() - t0 if world > 1 else 0.0
-    ctx.LoadKeys(dkeys["bk"], dkeys["pkey"], ksk=dkeys.get("ksk"), kskA=dkeys.get("kskA"), kskB=dkeys.get("kskB"),
-                 ctnand=dkeys.get("ctnand"))
-    key_bytes_total = sum(t.numel() * 4 for t in dkeys.values())
-    del dkeys
-    torch.cuda.empty_cache()
-
-    # ---- inputs.  The timed gates take REFRESHED ciphertexts (outputs of a first NAND level computed here on the GPU), the
-    # inputs every interior gate of a circuit sees: their `a` parts are dense mod q.  (The reference's MKLWE Encrypt samples
-    # `a` from a narrow Gaussian, mklwe-pke.cpp:53-54, so fresh ciphertexts rotate by ~0 everywhere -- a degenerate input.)
-    # Synthetic (no oracle/_ref) inputs are uniform mod q, dense as well.
-    stream = torch.cuda.Stream(device=dev)  # an explicit stream: torch's default stream handle is 0 = "the context's own"
-    torch.cuda.set_stream(stream)
-    ctx.set_stream(stream.cuda_stream)
-    expect = None
     if rank == 0:
-        if bits is not None:
-            m0, m1 = bits
-            f1, f2, fb1, fb2 = ct1, ct2, b1, b2
-            r1 = lambda a: np.roll(a, 1, axis=0)
-            if lwe:
-                x, bx = ctx.EvalBinGate("NAND", f1, f2, fb1, fb2)
-                y, by = ctx.EvalBinGate("NAND", r1(f1), f2, r1(fb1), fb2)
-            else:
-                x, y = ctx.EvalBinGate("NAND", f1, f2), ctx.EvalBinGate("NAND", r1(f1), f2)
-                bx = by = np.zeros(len(x), dtype=np.uint32)
-            mx, my = 1 - (m0 & m1), 1 - (r1(m0) & m1)
-            expect1 = 1 - (mx & my)
-            reps = (B + len(x) - 1) // len(x)
-            tile = lambda a: np.ascontiguousarray(np.tile(a, (reps,) + (1,) * (a.ndim - 1))[:B])
-            ct1, ct2, b1, b2, expect = tile(x), tile(y), tile(bx), tile(by), tile(expect1)
+        ctx.LoadKeys(keys["bk"], keys["pkey"], ksk=keys.get("ksk"), kskA=keys.get("kskA"), kskB=keys.get("kskB"),
+                     ctnand=keys.get("ctnand"))
+    torch.cuda.synchronize()
+    t_h2d = time.time() - t0
+    env.barrier()
+    t0 = time.time()
+    key_bytes_total = shard.replicate_key_images(ctx, dev, dist)
+    env.barrier()
+    t_bcast = time.time() - t0 if world > 1 else 0.0
+
+    # ---- inputs: B distinct gates (rank 0), broadcast; rank r works on them rotated by r ----
+    expect, nuniq = None, None
+    if rank == 0:
+        if ref is not None:
+            ct1, b1, ct2, b2, expect, nuniq = distinct_gate_inputs(ctx, P, ref, np.random.default_rng(seed), B)
         pack = [torch.from_numpy(np.ascontiguousarray(v).view(np.int32)).to(dev) for v in (ct1, ct2, b1, b2)]
     else:
         pack = [torch.empty(B * P.k * P.n, dtype=torch.int32, device=dev).view(B, P.k, P.n) for _ in range(2)] + \
@@ -344,12 +438,10 @@ def run_gpu_arm(args):
     d_bout = torch.empty_like(d_b1)
     h_ct1, h_ct2, h_b1, h_b2 = (t.cpu().pin_memory() for t in pack)
     h_out, h_bout = torch.empty_like(h_ct1).pin_memory(), torch.empty_like(h_b1).pin_memory()
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    stream = env.stream
 
     def step_dev():
         ctx.EvalBinGateDevice(d_ct1, d_ct2, d_out, d_b1 if lwe else None, d_b2 if lwe else None, d_bout if lwe else None)
-
-    import ctypes as C
 
     hp = lambda t: C.c_void_p(t.data_ptr())
 
@@ -357,74 +449,74 @@ def run_gpu_arm(args):
         ctx._ck(ctx._L.mkfhe_eval_nand(ctx._h, hp(h_ct1), hp(h_b1) if lwe else None, hp(h_ct2), hp(h_b2) if lwe else None,
                                        hp(h_out), hp(h_bout) if lwe else None, B), "mkfhe_eval_nand")
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    # ---- warm-up ----
-    for _ in range(args.warmup):
+    for _ in range(warmup):
         step_dev()
     torch.cuda.synchronize()
     launches0 = ctx.launch_count()
 
     # ---- timed: EXACTLY K steps, device events per step, L2 flushed between steps ----
-    sampler = ClockSampler(local if os.environ.get("CUDA_VISIBLE_DEVICES") is None else
-                           int(os.environ["CUDA_VISIBLE_DEVICES"].split(",")[local]))
+    sampler = ClockSampler(env.smi_index)
     if rank == 0:
         sampler.start()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
     rot_ms, ks_ms = [], []
-    barrier()
+    env.barrier()
     wall0 = time.time()
-    for i in range(args.steps):
-        flush.fill_(i & 0xff)
+    for i in range(steps):
+        env.flush.fill_(i & 0xff)
         ev[i][0].record(stream)
         step_dev()
         ev[i][1].record(stream)
         a, b = ctx.last_gate_timing()  # waits for the step; kernel-only split for the roofline
         rot_ms.append(a)
         ks_ms.append(b)
-    barrier()
+    env.barrier()
     wall = time.time() - wall0
     launches = ctx.launch_count() - launches0
     dev_ms = sum(e0.elapsed_time(e1) for e0, e1 in ev)
 
-    # ---- e2e: same K steps through the host-buffer entry point ----
+    # ---- e2e: the same K steps through the host-buffer entry point; with several GPUs every step also gathers the ranks'
+    # results on rank 0 (NCCL all_gather of the step's output rows), inside the timed region ----
     step_host()
-    barrier()
+    gathered = shard.gather_results(d_out, B * world, dist)
+    env.barrier()
+    gather_ms = 0.0
     t0 = time.time()
-    for i in range(args.steps):
+    for i in range(steps):
         step_host()
-    barrier()
+        if world > 1:
+            g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            g0.record(stream)
+            gathered = shard.gather_results(d_out, B * world, dist)
+            g1.record(stream)
+            g1.synchronize()
+            gather_ms += g0.elapsed_time(g1)
+    env.barrier()
     e2e_s = time.time() - t0
     clocks = sampler.stop() if rank == 0 else None
+    dev_ms, e2e_ms, rot_sum, ks_sum, gather_ms = env.max_over_ranks([dev_ms, e2e_s * 1e3, sum(rot_ms), sum(ks_ms), gather_ms])
 
-    tt = torch.tensor([dev_ms, e2e_s * 1e3, sum(rot_ms), sum(ks_ms)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)  # max over ranks
-    gathered = shard.gather_results(d_out, B * world, dist)  # results to rank 0 (outside the timed region)
-    dev_ms, e2e_ms, rot_sum, ks_sum = (float(x) for x in tt.tolist())
-
+    res = None
     if rank == 0:
-        # correctness inside the bench run (outside the timed region): device and host paths agree; sample decrypts to NAND
+        # correctness inside the bench run (outside the timed region)
         out_np = d_out.cpu().numpy().view(np.uint32)
+        bo = d_bout.cpu().numpy().view(np.uint32) if lwe else None
         assert (out_np == h_out.numpy().view(np.uint32)).all(), "device-pointer and host-pointer paths disagree"
-        checked = None
-        if ref is not None and expect is not None:
-            bo = d_bout.cpu().numpy().view(np.uint32) if lwe else np.zeros(B, dtype=np.uint32)
-            idx = list(range(0, min(B, 64), 2))
-            got = [ref.decrypt(out_np[i].ravel(), int(bo[i])) for i in idx]
-            assert got == [int(expect[i]) for i in idx], "bootstrapped gates do not decrypt to NAND"
-            checked = len(idx)
-        oracle_checked = check_against_oracle(P, keys, ct1, b1, ct2, b2, out_np,
-                                              d_bout.cpu().numpy().view(np.uint32) if lwe else None, args.check_oracle)
-        assert gathered is None or (gathered[:B].cpu().numpy().view(np.uint32) == out_np).all()
+        assert gathered is None or world == 1 or (gathered[:B].cpu().numpy().view(np.uint32) == out_np).all()
+        nand_checked = None
+        if ref is not None and expect is not None:  # EVERY output, decrypted on the GPU with the reference's secret key
+            ctx.LoadSecretKey(ref.sk())
+            got = ctx.Decrypt(out_np, bo).astype(np.int64)
+            bad = np.nonzero(got != expect)[0]
+            assert len(bad) == 0, f"{len(bad)} of {B} bootstrapped gates do not decrypt to NAND (first: gate {bad[0]})"
+            sample = list(range(0, B, max(1, B // 16)))[:16]  # and a sample with the reference's own Decrypt
+            assert [ref.decrypt(out_np[i].ravel(), int(bo[i]) if lwe else 0) for i in sample] == [int(expect[i]) for i in sample]
+            nand_checked = int(B)
+        oracle_checked = check_against_oracle(P, keys, ct1, b1, ct2, b2, out_np, bo, check_oracle)
         wm = work_model(P)
-        total_gates = B * world * args.steps
+        total_gates = B * world * steps
         value = total_gates / (dev_ms * 1e-3)
         e2e = total_gates / (e2e_ms * 1e-3)
-        imad_peak = ctx.measure_int32_peak()
         bfly_peak = ctx.measure_butterfly_peak()
         peaks = {}
         try:
@@ -432,50 +524,80 @@ def run_gpu_arm(args):
         except Exception:
             pass
         hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
-        rot_s = rot_sum * 1e-3 / args.steps  # average blind-rotation launch duration (max over ranks)
-        instr_per_launch = wm["instr"] * B
-        ach = instr_per_launch / rot_s
+        rot_s = rot_sum * 1e-3 / steps  # average blind-rotation launch duration (max over ranks)
         mm_ach = wm["modmul"] * B / rot_s  # modular multiplications per second (SURVEY 8d per-gate figure x gates per launch)
         key_ach = wm["key_bytes"] * B / rot_s / 1e9
-        traffic = ncu_traffic(args.paramset, B)
-        line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "u32", "data": "synthetic gate batch: reference keygen + Encrypt (oracle/_ref), refreshed by one NAND level, tiled" if ref is not None else "synthetic (uniform residues)",
-            "config": workload_config(args),
+        traffic = ncu_traffic(paramset, B)
+        sm_hz = 1e6 * float((clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz") or 1965.0)
+        floor_peak = 148 * 4 * 32 * sm_hz / 8.0  # analytic: IMAD.HI (4) + 2 IMAD (2 + 2) fma-pipe cycles per warp-butterfly
+        data = (f"synthetic gate batch: reference keygen + Encrypt (oracle/_ref), {nuniq} distinct gates"
+                + (" of refreshed ciphertexts (one NAND level first)" if lwe else " of fresh encryptions")
+                if ref is not None else "synthetic (uniform residues)")
+        res = {
+            "value": value, "ms_per_step": dev_ms / steps, "data": data,
+            "config": gates_config(paramset, B, world, nuniq),
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": int((2 * B * P.k * P.n + (2 * B if lwe else 0)) * 4),
-                    "d2h_bytes_per_step": int((B * P.k * P.n + (B if lwe else 0)) * 4)},
+                    "d2h_bytes_per_step": int((B * P.k * P.n + (B if lwe else 0)) * 4),
+                    "gather_s_per_step": gather_ms * 1e-3 / steps,
+                    "note": "mkfhe_eval_nand on host buffers per rank; N > 1: + all_gather of the results to rank 0, timed"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "int32", "kernel": "blind_rotate", "achieved": mm_ach / 1e12, "peak": bfly_peak / 1e12,
                          "unit": "Tmodmul/s", "frac": mm_ach / bfly_peak, "traffic": traffic,
+                         "frac_of_analytic_floor": mm_ach / floor_peak, "analytic_floor_peak": floor_peak / 1e12,
                          "model": "achieved = SURVEY 8d modular multiplications per gate (butterflies + pointwise MACs) x gates "
                                   "per launch / launch time; peak = register-resident lazy Shoup butterflies/s measured on this "
-                                  "GPU in this run (mkfhe_measure_butterfly_peak: nothing but butterflies, no memory traffic)",
+                                  "GPU in this run (mkfhe_measure_butterfly_peak: nothing but butterflies, no memory traffic); "
+                                  "analytic floor = 8 fma-pipe cycles per warp-butterfly at the sampled SM clock",
                          "modmul_per_gate": wm["modmul"], "kernel_ms": rot_s * 1e3, "share_of_step": rot_sum / dev_ms},
-            "roofline_imad_model": {"bound": "int32", "achieved": ach / 1e12, "peak": imad_peak / 1e12, "unit": "Tinstr/s",
-                                    "frac": ach / imad_peak, "instr_per_gate": wm["instr"],
-                                    "model": "SURVEY 8d fixed cost model: 7 instr/butterfly + 5/pointwise MAC against the IMAD-chain "
-                                             "rate measured in this run; the kernel's butterfly is 5 instructions on two pipes, so "
-                                             "this fraction can exceed 1 -- kept for continuity with earlier rounds"},
             "roofline_hbm": {"bound": "hbm", "kernel": "blind_rotate key stream", "achieved": key_ach, "peak": hbm_peak,
                              "unit": "GB/s", "frac": key_ach / hbm_peak, "traffic": traffic,
                              "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback 6650",
                              "bytes_per_gate": wm["key_bytes"], "note": "algorithmic key bytes if every gate streamed its own copy"},
-            "kernels_ms": {"blind_rotate": rot_sum / args.steps, "key_switch": ks_sum / args.steps},
-            "clocks": clocks, "wall_s_timed": wall, "key_bytes_replicated": key_bytes_total, "key_broadcast_s": t_bcast,
-            "nand_checked": checked, "oracle_checked": oracle_checked,
+            "kernels_ms": {"blind_rotate": rot_sum / steps, "key_switch": ks_sum / steps},
+            "clocks": clocks, "wall_s_timed": wall, "key_bytes_replicated": key_bytes_total,
+            "key_replication": {"nccl_init_s": env.nccl_init_s, "h2d_and_relayout_s": t_h2d, "bcast_s": t_bcast,
+                                "bytes": key_bytes_total, "what": "rank 0: pageable H2D + Montgomery/register-order/u16 re-layout; "
+                                "then the resident images broadcast device to device (NCCL)"},
+            "key_broadcast_s": t_bcast, "gather_s": gather_ms * 1e-3 / steps,
+            "nand_checked": nand_checked, "oracle_checked": oracle_checked,
         }
-        if world == 1 and not args.no_cpu_baseline:
+        if world == 1 and not no_cpu_baseline:
             cores = os.cpu_count() or 1
-            gates = cores * args.cpu_baseline_gates_per_thread  # bounded sample: ~10-20 s of host work
-            gps, kind, secs = cpu_gates_per_s(args.paramset, cores, gates, ref)
-            line["cpu_baseline"] = {"value": gps, "unit": UNIT, "cores": cores, "kind": kind,
-                                    "sample": f"{gates} EvalBinGate(NAND) on {cores} threads in {secs:.1f}s, same paramset"}
-        emit(line)
+            gates = cores * cpu_gates_per_thread  # bounded sample: ~10-20 s of host work
+            gps, kind, secs = cpu_gates_per_s(paramset, cores, gates, ref)
+            res["cpu_baseline"] = {"value": gps, "unit": UNIT, "cores": cores, "kind": kind,
+                                   "sample": f"{gates} EvalBinGate(NAND) on {cores} threads in {secs:.1f}s, same paramset"}
+            if ref is not None:  # the reference example's own measurement: one gate, one thread (boolean-mkntru.cpp:34-38)
+                ms = sorted(ref.time_gate(5))
+                res["cpu_baseline"]["single_thread_ms"] = ms[len(ms) // 2]
+                res["cpu_baseline"]["single_thread_sample"] = "median of 5 single EvalBinGate(NAND) calls, steady_clock, 1 thread"
     ctx.close()
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
+    del ctx
+    torch.cuda.empty_cache()
+    return res
+
+
+def run_gpu_arm(args):
+    env = GpuEnv()
+    main = measure_gate_batch(env, args.paramset, args.batch, args.steps, args.warmup, args.check_oracle,
+                              args.cpu_baseline_gates_per_thread, args.no_cpu_baseline)
+    also = None
+    if args.paramset == "STD100_MKNTRU_LWE" and not args.no_also:
+        # north_star names mk-acc-xzw.cpp: the boolean-mkntru (XZW, ternary) shape at the same k and batch, as its own block
+        also = measure_gate_batch(env, "STD100_MKNTRU", args.batch, args.also_steps, min(args.warmup, 3), args.check_oracle,
+                                  max(1, args.cpu_baseline_gates_per_thread // 2), args.no_cpu_baseline, seed=3)
+    if env.rank == 0:
+        line = {"metric": METRIC, "value": main["value"], "unit": UNIT, "n_gpus": env.world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": main["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "u32"}
+        line.update({k: v for k, v in main.items() if k not in ("value", "ms_per_step")})
+        if also is not None:
+            also.update({"metric": METRIC, "unit": UNIT, "steps": args.also_steps, "n_gpus": env.world})
+            line["also"] = {"boolean_mkntru": also}
+        emit(line)
+    if env.dist is not None:
+        env.dist.barrier()
+        env.dist.destroy_process_group()
 
 
 # ---------------------------------------------------------------- configs[3]: a fixed job sharded over the GPUs
@@ -922,7 +1044,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--synthetic-keys", action="store_true", help="uniform random key residues instead of the reference keygen "
                     "(throughput does not depend on key values; the reference's keygen takes minutes at k >= 8)")
-    ap.add_argument("--check-oracle", type=int, default=0, help="gates to re-compute on the CPU oracle after the run")
+    ap.add_argument("--check-oracle", type=int, default=64, help="gates to re-compute on the CPU oracle after the run (all host threads)")
+    ap.add_argument("--no-also", action="store_true", help="default workload only: skip the boolean-mkntru (XZW) block")
+    ap.add_argument("--also-steps", type=int, default=5)
     ap.add_argument("--workload", default="gates", choices=["gates", "sharded", "ntt", "keygen", "circuit"],
                     help="gates: configs[1]/[2] (batch per GPU); sharded: configs[3] (--total-gates split over the GPUs, "
                          "counter-based inputs); ntt: configs[4] (batched transform micro-benchmark)")

@@ -78,7 +78,14 @@ void mkfhe_ctx_destroy(mkfhe_ctx* ctx);
 /* text of the last error on ctx (ctx == NULL: last mkfhe_ctx_create failure on this thread) */
 const char* mkfhe_last_error(const mkfhe_ctx* ctx);
 /* use `cuda_stream` (a cudaStream_t) for all later work of this context; NULL = the context's own stream.  Waits for the work
- * already enqueued on the previous stream (the context's workspaces and pooled scratch are ordered on one stream at a time). */
+ * already enqueued on the previous stream (the context's workspaces and pooled scratch are ordered on one stream at a time).
+ * ORDERING CONTRACT of every *_dev entry point: the call reads its inputs and writes its outputs in stream order on the
+ * context's current stream, and returns without waiting.  The context's own stream is an ordinary (blocking) stream, so it is
+ * ordered with the LEGACY default stream: a caller that produces inputs / consumes outputs on the legacy default stream
+ * (PyTorch's default stream, plain cudaMemcpy) needs no extra synchronisation.  A caller working on any other stream -- a
+ * cudaStreamNonBlocking stream, a torch side stream, cudaStreamPerThread -- must hand that stream to mkfhe_ctx_set_stream
+ * (the handles cudaStreamLegacy = (void*)1 and cudaStreamPerThread = (void*)2 are accepted as they are) or order the work
+ * itself with events. */
 int mkfhe_ctx_set_stream(mkfhe_ctx* ctx, void* cuda_stream);
 /* block until all work enqueued by this context has finished */
 int mkfhe_ctx_synchronize(mkfhe_ctx* ctx);
@@ -100,6 +107,19 @@ int mkfhe_load_ksk_mklwe(mkfhe_ctx* ctx, const uint32_t* A_host_or_dev, uint64_t
                          uint64_t wordsB);
 /* m_ctNAND of BinFHEContext (binfhecontext.h:88; built by ctGateGen, binfhe-base-scheme.cpp:340-376): [u < k][n]; MNTRU only */
 int mkfhe_load_ctnand(mkfhe_ctx* ctx, const uint32_t* ct_host_or_dev, uint64_t words);
+
+/* Resident key images, for replicating keys between the GPUs of one box (north_star: "each GPU holds a replica of all parties'
+ * bootstrapping keys ... NCCL over NVLink only to broadcast keys"; the reference has one address space and no such step).
+ * An image is the key as the kernels read it from HBM -- bootstrapping key and Pkey in Montgomery form and register order,
+ * key-switch key as padded u16 rows, ctNAND as loaded -- so a replica needs no conversion and the MKLWE key-switch key travels
+ * as 403 MB instead of the 806 MB of its u32 boundary layout.  Rank 0 loads keys with mkfhe_load_* / mkfhe_keyfile_load; every
+ * rank calls mkfhe_key_image (which allocates the image where no key is loaded yet) and broadcasts `bytes` bytes from rank 0's
+ * pointer into the others' (ncclBroadcast / torch.distributed.broadcast on the raw device memory); receivers then call
+ * mkfhe_key_image_commit.  Images are only meaningful between contexts created from identical mkfhe_params on the same
+ * library build.  MKFHE_IMAGE_KSK exists on the fused key-switch path only (qKS < 2^16: every reference parameter set). */
+enum { MKFHE_IMAGE_BK = 0, MKFHE_IMAGE_PKEY = 1, MKFHE_IMAGE_KSK = 2, MKFHE_IMAGE_CTNAND = 3 };
+int mkfhe_key_image(mkfhe_ctx* ctx, int which, void** dev_ptr, uint64_t* bytes);
+int mkfhe_key_image_commit(mkfhe_ctx* ctx, int which);
 
 /* The decrypting parties' secret, only needed by mkfhe_decrypt: MNTRUPrivateKeyImpl::GetF_col0() (mntru-privatekey.h) or
  * MKLWEPrivateKeyImpl::GetElement() (mklwe-privatekey.h), [u < k][n] residues (reduced mod q at upload, as Decrypt's

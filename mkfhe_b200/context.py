@@ -320,8 +320,30 @@ class BinFHEContext:
         self._ck(self._L.mkfhe_decompose(self._h, _ptr(a)[0], _ptr(out)[0], a.shape[0]), "mkfhe_decompose")
         return out
 
+    # -- resident key images (include/mkfhe_b200.h "Resident key images"): what mkfhe_b200/shard.py broadcasts between GPUs
+    def KeyImages(self):
+        """[(which, device pointer, bytes)] of this context's key images, allocating those not loaded yet."""
+        P = self.params
+        which = [_lib.MKFHE_IMAGE_BK, _lib.MKFHE_IMAGE_PKEY, _lib.MKFHE_IMAGE_KSK]
+        if P.scheme == _lib.MKFHE_SCHEME_MNTRU:
+            which.append(_lib.MKFHE_IMAGE_CTNAND)
+        out = []
+        for w in which:
+            ptr, nb = C.c_void_p(), C.c_uint64()
+            self._ck(self._L.mkfhe_key_image(self._h, w, C.byref(ptr), C.byref(nb)), "mkfhe_key_image")
+            out.append((w, int(ptr.value), int(nb.value)))
+        return out
+
+    def CommitKeyImages(self, which=None):
+        for w in (which if which is not None else [x[0] for x in self.KeyImages()]):
+            self._ck(self._L.mkfhe_key_image_commit(self._h, int(w)), "mkfhe_key_image_commit")
+
     # -- plumbing
     def set_stream(self, cuda_stream_handle: int | None):
+        """All later work of this context goes to `cuda_stream_handle` (a cudaStream_t as an integer, e.g.
+        torch.cuda.Stream().cuda_stream).  None / 0: the context's own stream, an ordinary blocking stream and therefore ordered
+        with the legacy default stream (torch's default stream); lib.CUDA_STREAM_LEGACY (1) selects the legacy default stream
+        itself.  *Device methods read inputs and write outputs in stream order on that stream and do not wait."""
         self._ck(self._L.mkfhe_ctx_set_stream(self._h, C.c_void_p(cuda_stream_handle) if cuda_stream_handle else None),
                  "mkfhe_ctx_set_stream")
 

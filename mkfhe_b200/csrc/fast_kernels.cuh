@@ -736,6 +736,118 @@ __global__ void __launch_bounds__(FT, 4) ntt_batch_fast(const FastTables T, cons
     }
 }
 
+// ---- the same transform fed by the bulk-copy engine (TMA): cp.async.bulk + mbarrier ring ------------------------------------
+// One elected thread streams whole polynomials (8 KiB, contiguous in HBM) global -> shared with `cp.async.bulk` (1-D bulk copy,
+// SASS UBLKCP), completion signalled on an mbarrier per ring slot (`complete_tx::bytes`); the CTA's 256 threads pick their
+// coefficients out of the slot, transform in registers exactly as ntt_batch_fast does, put the result back INTO THE SAME SLOT
+// (every thread has passed a block barrier since it read the slot), and the elected thread sends the slot back with
+// `cp.async.bulk.global.shared::cta` (bulk store).  NTT_STAGES slots per CTA: while polynomial i is transformed, the loads of
+// i+1 .. i+S-1 and the stores of i-1, i-2 are in flight -- no thread holds a register for data in flight, no LDG/STG issue
+// slots, no long-scoreboard stalls in the compute warps.  Slot reuse: the store of iteration i-1 must have finished READING
+// its slot before the load of polynomial i+S-1 may overwrite it (`cp.async.bulk.wait_group.read 1`: all bulk groups but the
+// newest).  Generic-proxy writes (STS of the results) are made visible to the async proxy by `fence.proxy.async` before the
+// barrier that precedes the store.
+constexpr int NTT_STAGES = 4;
+__host__ __device__ inline size_t ntt_tma_smem_bytes() { return (size_t(NTT_STAGES) * FN + FNP) * 4 + NTT_STAGES * 8; }
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    const uint32_t a = smem_u32(bar);
+    uint32_t done;
+    do {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(done) : "r"(a), "r"(parity) : "memory");
+    } while (!done);
+}
+__device__ __forceinline__ void bulk_load(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void bulk_store(void* gmem_dst, const void* smem_src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gmem_dst), "r"(smem_u32(smem_src)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+
+// x in [0, 2^32) -> [0, 2Q) without a multiplication by a reciprocal: with sh = bits of Q and delta = 2^sh - Q,
+// x - (x >> sh) Q = (x mod 2^sh) + (x >> sh) delta < 2^sh + 32 delta <= 2Q whenever 32 delta <= Q - delta (true for the
+// reference's Q = 2^27 - 40959 and for every "previous prime below 2^27"); one SHF + one IMAD instead of IMAD.HI + IMAD.
+__device__ __forceinline__ uint32_t fold_shift27(uint32_t x, uint32_t Q) { return x - (x >> 27) * Q; }
+__host__ __device__ inline bool fold_shift27_ok(uint32_t Q) { return Q < (1u << 27) && Q > (1u << 26) && 33ull * ((1u << 27) - Q) <= Q; }
+
+template <bool HALF, bool SHIFTFOLD>
+__global__ void __launch_bounds__(FT, 4) ntt_batch_tma(const FastTables T, const uint32_t Q, const uint2 one2, uint32_t* polys,
+                                                       const uint64_t batch, const int inverse) {
+    extern __shared__ __align__(128) uint32_t sm[];
+    uint32_t* ring = sm;
+    uint32_t* E = ring + NTT_STAGES * FN;
+    uint64_t* full = reinterpret_cast<uint64_t*>(E + FNP);
+    const uint32_t tid = threadIdx.x;
+    constexpr uint32_t BYTES = FN * 4;
+    const uint64_t mine = blockIdx.x < batch ? (batch - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;  // polynomials of this CTA
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < NTT_STAGES; ++s) mbar_init(full + s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        for (uint64_t i = 0; i < mine && i < NTT_STAGES - 1; ++i) {
+            mbar_expect_tx(full + i, BYTES);
+            bulk_load(ring + i * FN, polys + (blockIdx.x + i * gridDim.x) * FN, BYTES, full + i);
+        }
+    }
+    __syncthreads();
+    for (uint64_t i = 0; i < mine; ++i) {
+        const uint32_t s = uint32_t(i % NTT_STAGES), parity = uint32_t(i / NTT_STAGES) & 1u;
+        uint32_t* buf = ring + s * FN;
+        mbar_wait(full + s, parity);
+        if (!inverse) {
+            uint32_t x[1][8];
+#pragma unroll
+            for (int r = 0; r < 8; ++r) x[0][r] = buf[tid + 256 * r];
+            fwd_ntt_regs<1, false, HALF>(x, E, T, Q, tid);
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                uint4 v;
+                if (SHIFTFOLD) {
+                    v.x = fold1(fold_shift27(x[0][4 * c + 0], Q), Q); v.y = fold1(fold_shift27(x[0][4 * c + 1], Q), Q);
+                    v.z = fold1(fold_shift27(x[0][4 * c + 2], Q), Q); v.w = fold1(fold_shift27(x[0][4 * c + 3], Q), Q);
+                } else {
+                    v.x = fold1(shoup_lazy(x[0][4 * c + 0], one2, Q), Q); v.y = fold1(shoup_lazy(x[0][4 * c + 1], one2, Q), Q);
+                    v.z = fold1(shoup_lazy(x[0][4 * c + 2], one2, Q), Q); v.w = fold1(shoup_lazy(x[0][4 * c + 3], one2, Q), Q);
+                }
+                *reinterpret_cast<uint4*>(buf + 8 * tid + 4 * c) = v;
+            }
+        } else {
+            uint32_t x[8];
+#pragma unroll
+            for (int c = 0; c < 2; ++c) {
+                const uint4 v = *reinterpret_cast<const uint4*>(buf + 8 * tid + 4 * c);
+                x[4 * c] = v.x; x[4 * c + 1] = v.y; x[4 * c + 2] = v.z; x[4 * c + 3] = v.w;
+            }
+            inv_ntt_regs<false, HALF>(x, E, T, Q, tid);
+#pragma unroll
+            for (int r = 0; r < 8; ++r) buf[tid + 256 * r] = fold1(x[r], Q);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // this thread's STS -> visible to the bulk-copy engine
+        __syncthreads();  // results complete in the slot; E free for the next polynomial
+        if (tid == 0) {
+            bulk_store(polys + (blockIdx.x + i * gridDim.x) * FN, buf, BYTES);
+            const uint64_t nx = i + NTT_STAGES - 1;  // goes to slot (i - 1) % S, whose store was issued one iteration ago
+            if (nx < mine) {
+                if (i > 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                const uint32_t ns = uint32_t(nx % NTT_STAGES);
+                mbar_expect_tx(full + ns, BYTES);
+                bulk_load(ring + ns * FN, polys + (blockIdx.x + nx * gridDim.x) * FN, BYTES, full + ns);
+            }
+        }
+    }
+    if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // shared memory stays valid until the stores have read it
+}
+
 // ---- butterfly micro-benchmark: the measured peak the gate kernel's roofline is quoted against -----------------------------
 // Register-resident lazy Shoup butterflies (the exact instruction sequence of the transforms: IMAD.HI + 2 IMAD + 2 IADD3), 16
 // values per thread, 4 radix-2 stages per iteration, twiddles in registers, no memory traffic: what the integer pipes of
@@ -1264,6 +1376,23 @@ inline cudaError_t fast_ntt(FastState& F, const DevCtx& d, uint32_t* polys, uint
                             uint64_t* launches) {
     // HALF: batch counts PAIRS of size-1024 polynomials (the caller sends an odd last one through the generic kernel)
     const unsigned grid = unsigned(std::min<uint64_t>(batch, uint64_t(F.sms) * 4));
+    // default: the bulk-copy ring (ntt_batch_tma); MKFHE_NTT_VARIANT=ldg selects the register-prefetch kernel it is measured against
+    const char* var = getenv("MKFHE_NTT_VARIANT");
+    if (!getenv("MKFHE_NTT16") && !(var && var[0] == 'l')) {
+        const size_t smem = ntt_tma_smem_bytes();
+        const bool sf = fold_shift27_ok(d.mod.Q) && !(var && var[0] == 'b');  // 'b': Barrett-style final fold, for A/B runs
+        auto launch = [&](auto kern) -> cudaError_t {
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+            if (e != cudaSuccess) return e;
+            kern<<<grid, FT, smem, st>>>(F.T, d.mod.Q, F.one2, polys, batch, inverse);
+            return cudaSuccess;
+        };
+        cudaError_t e = F.half ? (sf ? launch(ntt_batch_tma<true, true>) : launch(ntt_batch_tma<true, false>))
+                               : (sf ? launch(ntt_batch_tma<false, true>) : launch(ntt_batch_tma<false, false>));
+        if (e != cudaSuccess) return e;
+        ++*launches;
+        return cudaGetLastError();
+    }
     if (!F.half && getenv("MKFHE_NTT16")) {  // experimental: 16 coefficients per thread, two exchanges
         const unsigned g16 = unsigned(std::min<uint64_t>(batch, uint64_t(F.sms) * 8));
         ntt_batch_fast16<<<g16, FT16, 0, st>>>(F.T, d.mod.Q, F.one2, polys, batch, inverse);

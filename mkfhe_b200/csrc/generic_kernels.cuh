@@ -518,10 +518,12 @@ __global__ void keyswitch_mklwe_generic(const DevCtx P, const uint32_t* __restri
     const uint32_t g = blockIdx.x, u = blockIdx.y, i0 = blockIdx.z * ichunk;
     const uint32_t i1 = min(P.N, i0 + ichunk), n = P.n;
     const uint32_t* msr = ms + (size_t(g) * P.k + u) * P.N;
-    uint32_t bacc = 0;
+    // 64-bit accumulators: a chunk adds ichunk * dKS words below qKS < 2^24, which overflows 32 bits from dKS * qKS >= 2^24 on
+    // (mkfhe_ctx_create admits qKS < 2^24, dKS <= 16); the partial sums handed to the atomics are reduced mod qKS first
+    unsigned long long bacc = 0;
     for (uint32_t x0 = 0; x0 < n; x0 += blockDim.x) {
         const uint32_t x = x0 + threadIdx.x;
-        uint32_t acc = 0;
+        unsigned long long acc = 0;
         for (uint32_t i = i0; i < i1; ++i) {
             uint32_t v = msr[i];
             for (uint32_t j = 0; j < P.dKS; ++j) {
@@ -532,9 +534,9 @@ __global__ void keyswitch_mklwe_generic(const DevCtx P, const uint32_t* __restri
                 if (x0 == 0 && threadIdx.x == 0) bacc += __ldg(Bk + row);
             }
         }
-        if (x < n) atomicAdd(raw + (size_t(g) * P.k + u) * n + x, acc % P.qKS);
+        if (x < n) atomicAdd(raw + (size_t(g) * P.k + u) * n + x, static_cast<uint32_t>(acc % P.qKS));
     }
-    if (threadIdx.x == 0) atomicAdd(braw + g, bacc % P.qKS);
+    if (threadIdx.x == 0) atomicAdd(braw + g, static_cast<uint32_t>(bacc % P.qKS));
 }
 // out = 0 - raw mod qKS ; bout = RoundqQ(Q/8+1) - braw mod qKS (binfhe-base-scheme.cpp:450-458)
 __global__ void keyswitch_mklwe_finish(const DevCtx P, const uint32_t* raw, const uint32_t* braw, uint32_t* out, uint32_t* bout,
@@ -570,9 +572,9 @@ __global__ void __launch_bounds__(256) decrypt_batch(const DevCtx P, const uint3
     for (uint32_t x = lane; x < kn; x += 32) acc += static_cast<unsigned long long>(c[x]) * __ldg(sk + x);
     uint32_t r = static_cast<uint32_t>(acc % q);
 #pragma unroll
-    for (int o = 16; o; o >>= 1) r += __shfl_xor_sync(0xffffffffu, r, o);  // 32 * q < 2^32 (q * 2N < 2^32)
+    for (int o = 16; o; o >>= 1) r = addmod(r, __shfl_xor_sync(0xffffffffu, r, o), q);  // canonical at every level: any q < 2^31
     if (lane == 0) {
-        uint32_t inner = r % q;
+        uint32_t inner = r;
         if (P.scheme == 0) {
             inner = addmod(inner, q / pmod, q);
         } else {

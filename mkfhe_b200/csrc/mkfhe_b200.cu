@@ -259,6 +259,9 @@ int mkfhe_ctx_create(const mkfhe_params* p, mkfhe_ctx** out) {
         return fail(nullptr, MKFHE_EINVAL, "bad q/qKS/baseKS/dKS");
     if (uint64_t(p->q) * 2 * p->N >= (1ull << 32) || p->qKS >= (1u << 24))
         return fail(nullptr, MKFHE_EINVAL, "q*2N must fit 32 bits (mk-acc-xzw.cpp:110 uses 32-bit NativeInteger) and qKS < 2^24");
+    if (p->q != p->qKS)  // both MK paths refresh into the input modulus (binfhecontext.cpp:137-146: qKS == q in every row); Decrypt
+                         // and the fused key switch rely on it
+        return fail(nullptr, MKFHE_EINVAL, "q must equal qKS (gate outputs are ciphertexts mod qKS and feed the next gate mod q)");
     if (h_powmod(p->psi, p->N, p->Q) != p->Q - 1) return fail(nullptr, MKFHE_EINVAL, "psi is not a primitive 2N-th root of unity mod Q");
 
     int ndev = 0;
@@ -277,7 +280,9 @@ int mkfhe_ctx_create(const mkfhe_params* p, mkfhe_ctx** out) {
         mkfhe_ctx_destroy(ctx);
         return rc;
     };
-    if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess)
+    // An ordinary (blocking) stream: work on it is ordered with the legacy default stream, which is where a caller that never
+    // chose a stream (PyTorch's default, plain cudaMemcpy) produces the inputs of the *_dev entry points and reads their outputs.
+    if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamDefault) != cudaSuccess)
         return bail(fail(ctx, MKFHE_ECUDA, "cudaStreamCreate failed"));
     ctx->stream = ctx->own_stream;
     for (auto& e : ctx->ev)
@@ -447,6 +452,55 @@ int mkfhe_load_ctnand(mkfhe_ctx* ctx, const uint32_t* ct, uint64_t words) {
     if (words != uint64_t(ctx->p.k) * ctx->p.n) return fail(ctx, MKFHE_EINVAL, "mkfhe_load_ctnand: wrong size");
     CU(cudaSetDevice(ctx->device));
     return upload(ctx, &ctx->ctnand, ct, words, false);
+}
+
+// ---- resident key images (replication between GPUs) ----
+static uint64_t ksk16_bytes(const mkfhe_ctx* ctx) { return uint64_t(ctx->p.k) * ctx->d.ks_rows * ctx->d.npad * sizeof(uint16_t); }
+int mkfhe_key_image(mkfhe_ctx* ctx, int which, void** dev_ptr, uint64_t* bytes) {
+    if (!ctx || !dev_ptr || !bytes) return MKFHE_EINVAL;
+    CU(cudaSetDevice(ctx->device));
+    const mkfhe_params& p = ctx->p;
+    int rc = MKFHE_OK;
+    switch (which) {
+        case MKFHE_IMAGE_BK:
+            *bytes = bk_words(p) * 4;
+            if (!ctx->bk) rc = dev_alloc(ctx, &ctx->bk, bk_words(p));
+            *dev_ptr = ctx->bk;
+            break;
+        case MKFHE_IMAGE_PKEY:
+            *bytes = uint64_t(p.k) * (p.digitsG - 1) * p.N * 4;
+            if (!ctx->pkey) rc = dev_alloc(ctx, &ctx->pkey, *bytes / 4);
+            *dev_ptr = ctx->pkey;
+            break;
+        case MKFHE_IMAGE_KSK:
+            if (!ctx->fuse_ks) return fail(ctx, MKFHE_EINVAL, "the key-switch key has a resident image only on the fused path (qKS < 2^16)");
+            *bytes = ksk16_bytes(ctx);
+            if (!ctx->ksk16) {
+                CU(cudaMalloc(&ctx->ksk16, *bytes));
+                ctx->dev_bytes += *bytes;
+            }
+            *dev_ptr = ctx->ksk16;
+            break;
+        case MKFHE_IMAGE_CTNAND:
+            if (p.scheme != MKFHE_SCHEME_MNTRU) return fail(ctx, MKFHE_EINVAL, "ctNAND exists only on the MNTRU path");
+            *bytes = uint64_t(p.k) * p.n * 4;
+            if (!ctx->ctnand) rc = dev_alloc(ctx, &ctx->ctnand, *bytes / 4);
+            *dev_ptr = ctx->ctnand;
+            break;
+        default: return fail(ctx, MKFHE_EINVAL, "unknown key image %d", which);
+    }
+    return rc;
+}
+int mkfhe_key_image_commit(mkfhe_ctx* ctx, int which) {
+    if (!ctx) return MKFHE_EINVAL;
+    switch (which) {
+        case MKFHE_IMAGE_BK: if (!ctx->bk) break; ctx->d.bk = ctx->bk; return MKFHE_OK;
+        case MKFHE_IMAGE_PKEY: if (!ctx->pkey) break; ctx->d.pkey = ctx->pkey; return MKFHE_OK;
+        case MKFHE_IMAGE_KSK: if (!ctx->ksk16) break; ctx->d.ksk16 = ctx->ksk16; return MKFHE_OK;
+        case MKFHE_IMAGE_CTNAND: if (!ctx->ctnand) break; return MKFHE_OK;
+        default: return fail(ctx, MKFHE_EINVAL, "unknown key image %d", which);
+    }
+    return fail(ctx, MKFHE_ENOKEY, "key image %d was never obtained with mkfhe_key_image", which);
 }
 
 // the decryptor's secret (the party set that decrypts jointly): residues mod q

@@ -15,12 +15,15 @@ U32P = C.POINTER(C.c_uint32)
 
 MKFHE_VARIANT_XZW, MKFHE_VARIANT_XZW_B = 0, 1
 MKFHE_SCHEME_MNTRU, MKFHE_SCHEME_MKLWE = 0, 1
+MKFHE_IMAGE_BK, MKFHE_IMAGE_PKEY, MKFHE_IMAGE_KSK, MKFHE_IMAGE_CTNAND = 0, 1, 2, 3
+CUDA_STREAM_LEGACY, CUDA_STREAM_PER_THREAD = 1, 2  # the driver's own handles (cudaStreamLegacy, cudaStreamPerThread)
 ERRORS = {-1: "MKFHE_EINVAL", -2: "MKFHE_ENODEV", -3: "MKFHE_ECUDA", -4: "MKFHE_ENOKEY", -5: "MKFHE_ENOMEM"}
 
 # every symbol include/mkfhe_b200.h declares (tests/test_cabi.py checks the header against this list and the .so)
 SYMBOLS = [
     "mkfhe_ctx_create", "mkfhe_ctx_destroy", "mkfhe_last_error", "mkfhe_ctx_set_stream", "mkfhe_ctx_synchronize",
     "mkfhe_load_bk", "mkfhe_load_pkey", "mkfhe_load_ksk_mntru", "mkfhe_load_ksk_mklwe", "mkfhe_load_ctnand",
+    "mkfhe_key_image", "mkfhe_key_image_commit",
     "mkfhe_eval_acc", "mkfhe_eval_acc_dev", "mkfhe_eval_nand", "mkfhe_eval_nand_dev", "mkfhe_ntt", "mkfhe_ntt_dev",
     "mkfhe_load_sk", "mkfhe_decrypt", "mkfhe_decrypt_dev", "mkfhe_eval_circuit", "mkfhe_eval_circuit_dev", "mkfhe_circuit_levels", "mkfhe_keygen_bk", "mkfhe_keygen_pkey", "mkfhe_keygen_ksk_mntru", "mkfhe_keygen_ksk_mklwe", "mkfhe_encrypt_mntru", "mkfhe_encrypt_mklwe", "mkfhe_keyfile_write", "mkfhe_keyfile_info", "mkfhe_keyfile_load",
     "mkfhe_decompose", "mkfhe_last_gate_timing", "mkfhe_launch_count", "mkfhe_device_bytes", "mkfhe_version", "mkfhe_measure_int32_peak", "mkfhe_measure_butterfly_peak",
@@ -61,6 +64,8 @@ def load():
     for name in ("mkfhe_load_bk", "mkfhe_load_pkey", "mkfhe_load_ksk_mntru", "mkfhe_load_ctnand", "mkfhe_load_sk"):
         getattr(L, name).argtypes = [vp, vp, u64]
     L.mkfhe_load_ksk_mklwe.argtypes = [vp, vp, u64, vp, u64]
+    L.mkfhe_key_image.argtypes = [vp, i32, C.POINTER(vp), C.POINTER(u64)]
+    L.mkfhe_key_image_commit.argtypes = [vp, i32]
     L.mkfhe_eval_acc.argtypes = [vp, vp, vp, u32, vp, u64]
     L.mkfhe_eval_acc_dev.argtypes = [vp, vp, vp, u32, vp, u64]
     L.mkfhe_eval_nand.argtypes = [vp, vp, vp, vp, vp, vp, vp, u64]

@@ -134,6 +134,34 @@ def broadcast_keys(keys: dict | None, device, dist=None, src: int = 0) -> dict:
     return out
 
 
+class _DevMem:
+    """A span of raw device memory as something torch.as_tensor understands (CUDA array interface, int32 words)."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.__cuda_array_interface__ = {"shape": (nbytes // 4,), "typestr": "<i4", "data": (ptr, False), "version": 2}
+
+
+def replicate_key_images(ctx, device, dist=None, src: int = 0) -> int:
+    """Replicate the RESIDENT key images of rank `src`'s context (mkfhe_key_image: the keys as the kernels read them --
+    Montgomery form, register order, u16 key-switch rows) into every other rank's context: one broadcast per image straight
+    into the destination context's own HBM buffers (NCCL over NVLink / NVSwitch on the GPU box), no staging copy, no
+    conversion on the receivers.  Rank `src` must have loaded its keys already.  Returns the bytes replicated per rank."""
+    import torch
+
+    total = 0
+    images = ctx.KeyImages()
+    for which, ptr, nbytes in images:
+        assert nbytes % 4 == 0
+        total += nbytes
+        if dist is not None:
+            t = torch.as_tensor(_DevMem(ptr, nbytes), device=device)
+            dist.broadcast(t, src)
+    if dist is not None and dist.get_rank() != src:
+        torch.cuda.synchronize(device)
+        ctx.CommitKeyImages([w for w, _, _ in images])
+    return total
+
+
 def gather_results(local, total: int, dist=None, dst: int = 0):
     """Rows of every rank's `local` tensor ([hi-lo, ...]) concatenated in gate order on rank `dst` (None elsewhere).
     Shards may be ragged (sizes differ by one): rows are padded to the largest shard for the collective."""

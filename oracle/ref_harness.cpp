@@ -432,6 +432,37 @@ int ref_bench_gates(void* h, uint32_t gates, uint32_t threads, double* seconds) 
     });
 }
 
+// Single-gate latency as the reference's example measures it (src/binfhe/examples/boolean-mkntru.cpp:34-38,
+// boolean-mklwe.cpp:33-35: one EvalBinGate(NAND) on fresh encryptions of (1, 0), one thread): `reps` calls, each timed
+// separately with steady_clock around the EvalBinGate call alone; ms[i] = wall milliseconds of call i.  One untimed call
+// first (static NTT tables).
+int ref_time_gate(void* h, uint32_t reps, double* ms) {
+    auto* c = static_cast<RefCtx*>(h);
+    return guarded(c, [&] {
+        const uint32_t kn = c->k * c->n;
+        std::vector<uint32_t> a(kn), b(kn);
+        uint32_t ba = 0, bb = 0;
+        ref_encrypt(h, 1, a.data(), &ba);
+        ref_encrypt(h, 0, b.data(), &bb);
+        for (uint32_t r = 0; r <= reps; ++r) {
+            std::chrono::steady_clock::time_point t0, t1;
+            if (c->scheme == 0) {
+                ConstMNTRUCiphertext x1 = mk_mntru_ct(c, a.data(), c->q), x2 = mk_mntru_ct(c, b.data(), c->q), nd = c->ctNAND;
+                t0 = std::chrono::steady_clock::now();
+                auto out = c->sch->EvalBinGate(c->params, NAND, c->ek, x1, x2, nd);
+                t1 = std::chrono::steady_clock::now();
+            }
+            else {
+                ConstMKLWECiphertext x1 = mk_mklwe_ct(c, a.data(), ba, c->q), x2 = mk_mklwe_ct(c, b.data(), bb, c->q);
+                t0 = std::chrono::steady_clock::now();
+                auto out = c->sch->EvalBinGate(c->params, NAND, c->ek, x1, x2);
+                t1 = std::chrono::steady_clock::now();
+            }
+            if (r > 0) ms[r - 1] = std::chrono::duration<double, std::milli>(t1 - t0).count();
+        }
+    });
+}
+
 // Swap the reference's CPU accumulator for the drop-in GPU one (integration/unienc_acc_b200.h); `lib` is the path of
 // libmkfhe_b200.so.  After this call ref_eval_acc / ref_eval_gate run the reference's own orchestration code with the
 // blind rotation executed by the B200 library through its C ABI.  restore = 1 puts the CPU accumulator back.

@@ -53,6 +53,7 @@ def lib():
         L.ref_ntt.argtypes = [C.c_void_p, U32P, C.c_uint64, C.c_int]
         L.ref_decompose.argtypes = [C.c_void_p, U32P, U32P]
         L.ref_bench_gates.argtypes = [C.c_void_p, C.c_uint32, C.c_uint32, C.POINTER(C.c_double)]
+        L.ref_time_gate.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_double)]
         L.ref_use_accumulator_b200.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
         L.ref_batch_b200_load.argtypes = [C.c_void_p, C.c_char_p]
         L.ref_batch_b200_gates.argtypes = [C.c_void_p, U32P, U32P, U32P, U32P, U32P, U32P, C.c_uint64, C.POINTER(C.c_int)]
@@ -238,6 +239,12 @@ class Ref:
         s = C.c_double(0.0)
         self._ck(self.L.ref_bench_gates(self.h, gates, threads, C.byref(s)), "ref_bench_gates")
         return float(s.value)
+
+    def time_gate(self, reps: int = 5):
+        """Wall milliseconds of `reps` single EvalBinGate(NAND) calls on one thread (the reference example's own measurement)."""
+        ms = (C.c_double * reps)()
+        self._ck(self.L.ref_time_gate(self.h, reps, ms), "ref_time_gate")
+        return [float(x) for x in ms]
 
     def use_accumulator_b200(self, libpath: str, restore: bool = False):
         self._ck(self.L.ref_use_accumulator_b200(self.h, libpath.encode(), 1 if restore else 0), "ref_use_accumulator_b200")

@@ -1,0 +1,32 @@
+#!/bin/bash
+# Round-2 GPU sessions, one script: tools/gpu_r2.sh <session> <tag>.  Everything lands in gpurun_out/<tag>_*.
+#   prof   ncu --set full of the gate kernels at k = 4 / 8 / 16, the 128-register k = 2 build, the batched transform; per-line
+#          shared-memory conflict attribution of the k = 2 gate kernel; integer-pipe peaks
+S=$1; TAG=$2; mkdir -p gpurun_out
+prof() { # prof <name> <kernel regex> <skip> <count> <bench args...>
+  name=$1; rx=$2; skip=$3; cnt=$4; shift 4
+  CMD="python bench.py --no-cpu-baseline $*"
+  $CMD > gpurun_out/${TAG}_${name}_plain.json 2> gpurun_out/${TAG}_${name}_plain.err || { echo "$name: plain run failed"; tail -3 gpurun_out/${TAG}_${name}_plain.err; return; }
+  cut -c1-260 gpurun_out/${TAG}_${name}_plain.json
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:$rx -s $skip -c $cnt -o gpurun_out/${TAG}_${name} $CMD > gpurun_out/${TAG}_${name}_full.log 2>&1
+  python tools/ncu_summary.py gpurun_out/${TAG}_${name}.ncu-rep > gpurun_out/${TAG}_${name}.txt 2>&1
+  python tools/ncu_stalls.py gpurun_out/${TAG}_${name}.ncu-rep >> gpurun_out/${TAG}_${name}.txt 2>&1
+  python tools/ncu_lines.py gpurun_out/${TAG}_${name}.ncu-rep 30 >> gpurun_out/${TAG}_${name}.txt 2>&1
+  rm -f gpurun_out/${TAG}_${name}.ncu-rep; }
+peaks() {
+  nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o /tmp/pipe_microbench tools/pipe_microbench.cu && /tmp/pipe_microbench > gpurun_out/${TAG}_pipe_microbench.json 2> gpurun_out/${TAG}_pipe_microbench.err
+  nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o /tmp/bfly_microbench tools/bfly_microbench.cu && /tmp/bfly_microbench > gpurun_out/${TAG}_bfly_microbench.txt 2>&1
+  nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,clocks.mem,power.draw --format=csv > gpurun_out/${TAG}_smi.txt; }
+case $S in
+prof)
+  peaks
+  prof k4_444   blind_rotate 1 1 --paramset STD100_MKNTRU_2 --batch 444 --steps 1 --warmup 1 --synthetic-keys
+  prof k8_296   blind_rotate 1 1 --paramset STD100_MKNTRU_3 --batch 296 --steps 1 --warmup 1 --synthetic-keys
+  prof k16_148  blind_rotate 1 1 --paramset STD100_MKNTRU_4 --batch 148 --steps 1 --warmup 1 --synthetic-keys
+  prof mklwe296 blind_rotate 3 1 --batch 296 --steps 1 --warmup 3 --synthetic-keys
+  prof mklwe1184 blind_rotate 3 1 --batch 1184 --steps 1 --warmup 3 --synthetic-keys
+  prof ntt2048  ntt_batch 2 2 --workload ntt --ntt-n 2048 --steps 1 --warmup 1
+  prof ntt1024  ntt_batch 2 2 --workload ntt --ntt-n 1024 --steps 1 --warmup 1
+  ;;
+esac
+ls -la gpurun_out | head -50

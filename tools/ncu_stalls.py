@@ -15,7 +15,12 @@ src = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_ou
 rows = list(csv.reader(io.StringIO(src)))
 hi = next(i for i, x in enumerate(rows) if x and x[0] == "Address")
 h = rows[hi]; col = {n: i for i, n in enumerate(h)}
-body = [x for x in rows[hi + 1:] if len(x) == len(h)]
+body = []
+for x in rows[hi + 1:]:  # the first kernel of the report only (a second one repeats the header row)
+    if len(x) == len(h) and x[0] == "Address":
+        break
+    if len(x) == len(h):
+        body.append(x)
 f = lambda x, n: float(x[col[n]] or 0)
 tot = sum(f(x, "# Samples") for x in body)
 print("static instructions", len(body), "samples", tot)
