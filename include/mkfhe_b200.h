@@ -247,6 +247,19 @@ int mkfhe_keyfile_write(const char* path, const mkfhe_params* p, const uint32_t*
                         const uint32_t* ctnand, uint64_t ctnand_words);
 int mkfhe_keyfile_info(const char* path, mkfhe_params* p, uint64_t* words_by_tag);
 int mkfhe_keyfile_load(mkfhe_ctx* ctx, const char* path);
+/* The reader does not trust the file: parameters are compared before any section is read; the section table is checked
+ * against the file size and the word counts this parameter set implies (unknown / duplicate / mis-sized sections, kskA
+ * without kskB: MKFHE_EINVAL); every checksum is verified BEFORE the first upload, so a refused file leaves the context's
+ * keys as they were; allocation failures return MKFHE_ENOMEM. */
+
+/* Binary ciphertext / wire-table file: n_ct ciphertexts in the batch layout of mkfhe_eval_nand / mkfhe_eval_circuit
+ * (ct [n_ct][k][n] mod q, b [n_ct] for MKLWE, NULL for MNTRU) behind the same checksummed, parameter-stamped framing as the
+ * key file (mkfhe_b200/csrc/keyfile.h).  Replaces, for batches, the reference's per-object cereal save/load of
+ * MNTRUCiphertextImpl (mntru-ciphertext.h:116-125) and MKLWECiphertextImpl (mklwe-ciphertext.h:161-172).  No GPU needed.
+ * mkfhe_ctfile_read: `expect` (may be NULL) must equal the file's parameters; at most capacity_ct ciphertexts are accepted. */
+int mkfhe_ctfile_write(const char* path, const mkfhe_params* p, const uint32_t* ct, const uint32_t* b, uint64_t n_ct);
+int mkfhe_ctfile_info(const char* path, mkfhe_params* p, uint64_t* n_ct);
+int mkfhe_ctfile_read(const char* path, const mkfhe_params* expect, uint32_t* ct, uint32_t* b, uint64_t capacity_ct, uint64_t* n_ct);
 
 const char* mkfhe_version(void);
 /* INT32 pipe micro-benchmark (dependent IMAD chains on every SM): returns thread-level IMAD/s in *imad_per_s.

@@ -63,10 +63,13 @@ public:
         return m_cpu->KeyGenAcc(params, invskNTT, sk, CRS);
     }
 
-    // Upload BSkey + Pkey once (they are constant across EvalAcc calls).  n and q are the additive scheme's dimension and
-    // modulus (needed for the key layout and, for XZW, the rotation scaling c = ct*2N/q, mk-acc-xzw.cpp:110).
+    // Upload BSkey + Pkey (they are constant across EvalAcc calls).  OPTIONAL: EvalAcc uploads lazily the first time it sees a
+    // key object (see below), so the integration is the two make_shared lines of INTEGRATION.md section 2 and nothing else;
+    // call this to move the one-time upload (flatten + H2D, ~0.1 s for 70 MiB) out of the first gate.  n and q are the
+    // additive scheme's dimension and modulus (the key layout needs n; XZW scales rotations by 2N/q, mk-acc-xzw.cpp:110,
+    // with the modulus EvalAcc reads from ct itself).
     void LoadKeys(const std::shared_ptr<UniEncCryptoParams>& params, ConstUniEncACCKey& ek,
-                  const std::vector<std::vector<NativePoly>>& Pkey, uint32_t n, uint32_t q) {
+                  const std::vector<std::vector<NativePoly>>& Pkey, uint32_t n, uint32_t q) const {
         static_assert(sizeof(NativeInteger) == sizeof(uint32_t), "build the reference with NATIVE_SIZE=32 (README.md:19)");
         const uint32_t k = params->Getk(), N = params->GetN(), ell = params->GetDigitsG() - 1;
         const uint32_t S = m_variant == XZW ? 2 : 1;
@@ -80,7 +83,7 @@ public:
         p.variant = m_variant;
         p.scheme  = m_variant == XZW ? MKFHE_SCHEME_MNTRU : MKFHE_SCHEME_MKLWE;
         p.device  = -1;
-        if (m_ctx) { m_destroy(m_ctx); m_ctx = nullptr; }
+        if (m_ctx) { m_destroy(m_ctx); m_ctx = nullptr; m_loaded = nullptr; }
         check(m_create(&p, &m_ctx), "mkfhe_ctx_create");
 
         std::vector<uint32_t> flat((size_t(k) * S * n + 1) * ell * 2 * N);
@@ -104,15 +107,20 @@ public:
                 std::memcpy(&pk[(size_t(u) * ell + j) * N], &Pkey[u][j].GetValues()[0], sizeof(uint32_t) * N);
         check(m_load_pkey(m_ctx, pk.data(), pk.size()), "mkfhe_load_pkey");
         m_k = k; m_N = N; m_n = n;
+        m_loaded = ek.get();
     }
 
-    // Same signature and semantics as the reference's EvalAcc; `ek`, `Pkey` were uploaded by LoadKeys, `skf` is unused by
-    // the reference as well (it is a debugging leftover, mk-acc-xzw.cpp:89-130).
+    // Same signature and semantics as the reference's EvalAcc; `skf` is unused by the reference as well (it is a debugging
+    // leftover, mk-acc-xzw.cpp:89-130).
     void EvalAcc(const std::shared_ptr<UniEncCryptoParams>& params, ConstUniEncACCKey& ek,
                  std::vector<std::vector<NativePoly>> Pkey, std::vector<NativePoly> skf, MKACCCiphertext& acc,
                  const std::vector<NativeVector>& ct) const override {
-        if (!m_ctx)
-            OPENFHE_THROW(config_error, "UniEncAccumulatorB200: LoadKeys has not been called");
+        // The reference hands the keys to every EvalAcc call (mk-acc.h:67-71); they are uploaded the first time a key object is
+        // seen (identity of the UniEncACCKeyImpl the shared_ptr owns) and stay resident for all later calls.
+        if (ct.empty() || ct.size() != params->Getk())
+            OPENFHE_THROW(config_error, "UniEncAccumulatorB200: one rotation vector per party expected");
+        if (!m_ctx || m_loaded != ek.get())
+            LoadKeys(params, ek, Pkey, ct[0].GetLength(), ct[0].GetModulus().ConvertToInt<uint32_t>());
         if (ct.size() != m_k || ct[0].GetLength() != m_n)
             OPENFHE_THROW(config_error, "UniEncAccumulatorB200: ciphertext shape differs from the loaded keys");
         std::vector<uint32_t> a(size_t(m_k) * m_N), r(size_t(m_k) * m_n);
@@ -146,8 +154,9 @@ private:
 
     Variant m_variant;
     void* m_lib{nullptr};
-    mkfhe_ctx* m_ctx{nullptr};
-    uint32_t m_k{0}, m_N{0}, m_n{0};
+    mutable mkfhe_ctx* m_ctx{nullptr};           // EvalAcc is const in the interface; the resident copy of the keys is a cache
+    mutable const void* m_loaded{nullptr};       // the UniEncACCKeyImpl whose keys are resident
+    mutable uint32_t m_k{0}, m_N{0}, m_n{0};
     std::shared_ptr<UniEncAccumulator> m_cpu;
     decltype(&mkfhe_ctx_create) m_create{nullptr};
     decltype(&mkfhe_ctx_destroy) m_destroy{nullptr};

@@ -449,6 +449,30 @@ def KeyFileInfo(path: str):
     return p, {names[i]: int(w[i]) for i in names if w[i]}
 
 
+def SaveCiphertexts(path: str, params: Params, ct, b=None):
+    """Write ciphertexts ct [n, k, n_lwe] (and b [n] for MKNTRU_LWE) as one checksummed wire-table file (no GPU needed)."""
+    L = _lib.load()
+    c = np.ascontiguousarray(ct, dtype=np.uint32).reshape(-1, params.k, params.n)
+    bb = None if b is None else np.ascontiguousarray(b, dtype=np.uint32).reshape(c.shape[0])
+    if L.mkfhe_ctfile_write(os.fsencode(path), C.byref(params), _ptr(c)[0], _ptr(bb)[0], c.shape[0]) != 0:
+        raise _lib.MkfheError(-1, "mkfhe_ctfile_write", f"cannot write {path} (MKNTRU_LWE ciphertexts need b)")
+
+
+def LoadCiphertexts(path: str, params: Params | None = None):
+    """(Params, ct [n, k, n_lwe], b [n] or None) of a wire-table file; `params`, when given, must match the file's."""
+    L = _lib.load()
+    p, n = Params(), C.c_uint64()
+    if L.mkfhe_ctfile_info(os.fsencode(path), C.byref(p), C.byref(n)) != 0:
+        raise _lib.MkfheError(-1, "mkfhe_ctfile_info", f"{path}: unreadable, not a ciphertext file, or checksum mismatch")
+    ct = np.empty((n.value, p.k, p.n), dtype=np.uint32)
+    b = np.empty(n.value, dtype=np.uint32) if p.scheme == _lib.MKFHE_SCHEME_MKLWE else None
+    got = C.c_uint64()
+    if L.mkfhe_ctfile_read(os.fsencode(path), C.byref(params) if params is not None else None, _ptr(ct)[0], _ptr(b)[0], n.value,
+                           C.byref(got)) != 0:
+        raise _lib.MkfheError(-1, "mkfhe_ctfile_read", f"{path}: written for a different parameter set")
+    return p, ct, b
+
+
 def CircuitLevels(n_wires: int, gates):
     """Levelisation EvalCircuit applies (no GPU needed): gates int [G, 3] rows (in1, in2, out) -> (levels, level of each gate).
     Raises config_error for a netlist EvalCircuit refuses (index out of range, in1 == in2, a wire written twice or read

@@ -49,6 +49,8 @@ struct FastTables {
     uint2 itwB[32];       // itw2[0..31]: the second inverse pass (4 distinct addresses per warp)
     uint32_t zero;        // 0, opaque to the compiler: makes "u + t" a three-input add, which ptxas maps to IADD3 (alu pipe)
                           // instead of IMAD.IADD (fma pipe, the saturated one: profiles/r1_fast_v2_blind_rotate.txt)
+    uint32_t stagger_ns;  // experiment (MKFHE_STAGGER_NS): CTA b of the gate kernel starts (b mod 4) * stagger_ns late, so that the
+                          // resident gates of an SM run out of phase; 0 = off
 };
 
 // y * w mod Q in [0, 2Q) for ANY 32-bit y (Harvey's lazy Shoup multiplication)
@@ -533,6 +535,7 @@ __global__ void __launch_bounds__(FT, MINB) blind_rotate_fast(const DevCtx P, co
     uint32_t* Ms = ALIAS ? E2 : E2 + FNP;
     uint16_t* crot = reinterpret_cast<uint16_t*>(XZW ? Ms + N : Ms);
 
+    if (T.stagger_ns) __nanosleep((blockIdx.x & 3u) * T.stagger_ns);
     rotate_prologue<GATE>(P, io, blockIdx.x, a, crot);
     fast_step<XZW, true, ALIAS>(P, T, a, E1, E2, Ms, 0, crot[0], tid);
     for (uint32_t s = 1; s < k * n; ++s) {
@@ -660,7 +663,7 @@ __device__ __forceinline__ void grouped_step(const DevCtx& P, const FastTables& 
     __syncthreads();  // a[] complete (and every group past its last exchange) before the next step
 }
 
-template <bool GATE, bool XZW, bool ALIAS, int MAXT>  // MAXT = 256 G: 2 groups get 128 registers per thread, 4 groups 64
+template <bool GATE, bool XZW, bool ALIAS, int MAXT>  // MAXT = 256 G: 2 groups get 128 registers per thread, 3 groups 80, 4 groups 64
 __global__ void __launch_bounds__(MAXT, 1) blind_rotate_grouped(const DevCtx P, const FastTables T, const GateIO io) {
     extern __shared__ __align__(16) uint32_t sm[];
     const uint32_t k = P.k, n = P.n, G = blockDim.x >> 8, grp = threadIdx.x >> 8, tid = threadIdx.x & 255;
@@ -747,8 +750,10 @@ __global__ void __launch_bounds__(FT, 4) ntt_batch_fast(const FastTables T, cons
 // its slot before the load of polynomial i+S-1 may overwrite it (`cp.async.bulk.wait_group.read 1`: all bulk groups but the
 // newest).  Generic-proxy writes (STS of the results) are made visible to the async proxy by `fence.proxy.async` before the
 // barrier that precedes the store.
-constexpr int NTT_STAGES = 4;
-__host__ __device__ inline size_t ntt_tma_smem_bytes() { return (size_t(NTT_STAGES) * FN + FNP) * 4 + NTT_STAGES * 8; }
+// Resident CTAs per SM (CTAS) and ring depth: the transform needs 48 registers with one polynomial in flight per thread, so 5
+// CTAs (40 warps) fit the register file with a 4-deep ring (42 KiB each) and 6 CTAs (40 registers) with a 3-deep ring.
+__host__ __device__ constexpr int ntt_stages(int ctas) { return ctas >= 6 ? 3 : 4; }
+__host__ __device__ inline size_t ntt_tma_smem_bytes(int ctas) { return (size_t(ntt_stages(ctas)) * FN + FNP) * 4 + ntt_stages(ctas) * 8; }
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
@@ -780,10 +785,11 @@ __device__ __forceinline__ void bulk_store(void* gmem_dst, const void* smem_src,
 __device__ __forceinline__ uint32_t fold_shift27(uint32_t x, uint32_t Q) { return x - (x >> 27) * Q; }
 __host__ __device__ inline bool fold_shift27_ok(uint32_t Q) { return Q < (1u << 27) && Q > (1u << 26) && 33ull * ((1u << 27) - Q) <= Q; }
 
-template <bool HALF, bool SHIFTFOLD>
-__global__ void __launch_bounds__(FT, 4) ntt_batch_tma(const FastTables T, const uint32_t Q, const uint2 one2, uint32_t* polys,
+template <bool HALF, bool SHIFTFOLD, int CTAS>
+__global__ void __launch_bounds__(FT, CTAS) ntt_batch_tma(const FastTables T, const uint32_t Q, const uint2 one2, uint32_t* polys,
                                                        const uint64_t batch, const int inverse) {
     extern __shared__ __align__(128) uint32_t sm[];
+    constexpr int NTT_STAGES = ntt_stages(CTAS);
     uint32_t* ring = sm;
     uint32_t* E = ring + NTT_STAGES * FN;
     uint64_t* full = reinterpret_cast<uint64_t*>(E + FNP);
@@ -1298,7 +1304,7 @@ inline bool fast_use_alias(const DevCtx& d) {
 inline uint32_t fast_groups(const DevCtx& d, uint32_t batch, int sms) {
     uint32_t G = (d.k >= 16 || (d.k >= 2 && batch <= uint32_t(sms))) ? 2 : 1;
     if (const char* e = getenv("MKFHE_GROUPS")) G = uint32_t(atoi(e));
-    if (G != 2 && G != 4) return 1;
+    if (G < 2 || G > 4) return 1;
     if (d.k > 16 || d.k < G) return 1;
     return grouped_smem_bytes(d.k, d.n, G, true) <= 227 * 1024 ? G : 1;
 }
@@ -1307,6 +1313,7 @@ inline cudaError_t fast_blind_rotate(FastState& F, const DevCtx& d, bool gate, c
                                      uint64_t* launches) {
     const bool xzw = d.variant == 0;
     const uint32_t G = fast_groups(d, batch, F.sms);
+    F.T.stagger_ns = getenv("MKFHE_STAGGER_NS") ? uint32_t(atoi(getenv("MKFHE_STAGGER_NS"))) : 0u;
     const bool alias = G > 1 ? grouped_smem_bytes(d.k, d.n, G, false) > 227 * 1024 : fast_use_alias(d);
     const size_t smem = G > 1 ? grouped_smem_bytes(d.k, d.n, G, alias) : fast_smem_bytes(d.k, d.n, alias, xzw);
     auto launch = [&](auto kern) -> cudaError_t {
@@ -1328,7 +1335,9 @@ inline cudaError_t fast_blind_rotate(FastState& F, const DevCtx& d, bool gate, c
     if (const char* ev = getenv("MKFHE_MINB")) minb = std::min(4, std::max(2, atoi(ev)));
     if (alias) minb = 4;  // the fallback layout is built for the 64-register budget only
     if (G > 1) {
-#define MKFHE_LAUNCH_G(G_, X_, A_) (G == 2 ? launch(blind_rotate_grouped<G_, X_, A_, 512>) : launch(blind_rotate_grouped<G_, X_, A_, 1024>))
+#define MKFHE_LAUNCH_G(G_, X_, A_)                                                                                         \
+    (G == 2 ? launch(blind_rotate_grouped<G_, X_, A_, 512>)                                                                 \
+            : G == 3 ? launch(blind_rotate_grouped<G_, X_, A_, 768>) : launch(blind_rotate_grouped<G_, X_, A_, 1024>))
         switch (sel) {
             case 0: e = MKFHE_LAUNCH_G(false, false, false); break;
             case 1: e = MKFHE_LAUNCH_G(false, false, true); break;
@@ -1379,16 +1388,21 @@ inline cudaError_t fast_ntt(FastState& F, const DevCtx& d, uint32_t* polys, uint
     // default: the bulk-copy ring (ntt_batch_tma); MKFHE_NTT_VARIANT=ldg selects the register-prefetch kernel it is measured against
     const char* var = getenv("MKFHE_NTT_VARIANT");
     if (!getenv("MKFHE_NTT16") && !(var && var[0] == 'l')) {
-        const size_t smem = ntt_tma_smem_bytes();
+        int ctas = 5;  // measured on B200 (profiles/r2_s3_ntt*.json)
+        if (const char* c = getenv("MKFHE_NTT_CTAS")) ctas = std::min(6, std::max(4, atoi(c)));
+        const size_t smem = ntt_tma_smem_bytes(ctas);
+        const unsigned g = unsigned(std::min<uint64_t>(batch, uint64_t(F.sms) * ctas));
         const bool sf = fold_shift27_ok(d.mod.Q) && !(var && var[0] == 'b');  // 'b': Barrett-style final fold, for A/B runs
         auto launch = [&](auto kern) -> cudaError_t {
             cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
             if (e != cudaSuccess) return e;
-            kern<<<grid, FT, smem, st>>>(F.T, d.mod.Q, F.one2, polys, batch, inverse);
+            kern<<<g, FT, smem, st>>>(F.T, d.mod.Q, F.one2, polys, batch, inverse);
             return cudaSuccess;
         };
-        cudaError_t e = F.half ? (sf ? launch(ntt_batch_tma<true, true>) : launch(ntt_batch_tma<true, false>))
-                               : (sf ? launch(ntt_batch_tma<false, true>) : launch(ntt_batch_tma<false, false>));
+#define MKFHE_NTT_TMA(H_, S_) (ctas == 4 ? launch(ntt_batch_tma<H_, S_, 4>) : ctas == 5 ? launch(ntt_batch_tma<H_, S_, 5>) : launch(ntt_batch_tma<H_, S_, 6>))
+        cudaError_t e = F.half ? (sf ? MKFHE_NTT_TMA(true, true) : MKFHE_NTT_TMA(true, false))
+                               : (sf ? MKFHE_NTT_TMA(false, true) : MKFHE_NTT_TMA(false, false));
+#undef MKFHE_NTT_TMA
         if (e != cudaSuccess) return e;
         ++*launches;
         return cudaGetLastError();

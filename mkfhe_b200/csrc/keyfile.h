@@ -8,7 +8,13 @@
 //   header  : "MKFHEKEY" | u32 version (1) | u32 section count | 13 x u32 parameters (mkfhe_params without `device`) | u32 0
 //   section : u32 tag | u32 0 | u64 words | u64 FNV-1a-64 of the payload bytes | payload (words x u32 LE) | pad to 16 bytes
 //   tags    : 1 bk, 2 pkey, 3 ksk (MNTRU digit-1 slice), 4 kskA, 5 kskB (MKLWE), 6 ctnand (MNTRU)
+//
+// Ciphertext / wire-table file (magic "MKFHECTX", same header and section framing): the reference serialises ciphertexts one
+// object at a time through cereal (mntru-ciphertext.h:116-125, mklwe-ciphertext.h:161-172); here a whole table travels as
+//   tags    : 8 a-parts [n_ct][k][n] mod q, 9 b-parts [n_ct] (MKLWE only)
+// which is the layout mkfhe_eval_nand / mkfhe_eval_circuit take.
 #pragma once
+#include <algorithm>
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
@@ -19,8 +25,9 @@
 namespace mkfhe_keyfile {
 
 constexpr char MAGIC[8] = {'M', 'K', 'F', 'H', 'E', 'K', 'E', 'Y'};
+constexpr char MAGIC_CT[8] = {'M', 'K', 'F', 'H', 'E', 'C', 'T', 'X'};  // ciphertext / wire-table file (same container)
 constexpr uint32_t VERSION = 1;
-enum Tag : uint32_t { BK = 1, PKEY = 2, KSK = 3, KSKA = 4, KSKB = 5, CTNAND = 6, TAG_MAX = 6 };
+enum Tag : uint32_t { BK = 1, PKEY = 2, KSK = 3, KSKA = 4, KSKB = 5, CTNAND = 6, TAG_MAX = 6, CT_A = 8, CT_B = 9, TAG_SLOTS = 10 };
 
 struct Header {
     char magic[8];
@@ -51,11 +58,11 @@ inline void words_to_params(const uint32_t (&w)[13], mkfhe_params& p) {
 struct Writer {
     FILE* f{nullptr};
     uint32_t count{0};
-    bool open(const char* path, const mkfhe_params& p) {
+    bool open(const char* path, const mkfhe_params& p, const char* magic = MAGIC) {
         f = fopen(path, "wb");
         if (!f) return false;
         Header h{};
-        memcpy(h.magic, MAGIC, 8);
+        memcpy(h.magic, magic, 8);
         h.version = VERSION;
         params_to_words(p, h.par);
         return fwrite(&h, sizeof h, 1, f) == 1;
@@ -76,33 +83,77 @@ struct Writer {
     }
 };
 
-// Reads the file section by section; `sink(tag, data, words)` consumes each payload (0 = ok).  Returns 0, or a negative code:
-// -1 cannot open / short read, -2 bad magic or version, -3 checksum mismatch, -4 unknown tag, or the sink's value.
+// What a file must contain to be accepted: the magic of its kind, and for every tag the exact word count (0 = any).
+struct Expect {
+    const char* magic;
+    const uint64_t* words_by_tag;  // [TAG_SLOTS] or null
+};
+
+// Reads the file section by section; `sink(tag, data, words)` consumes each payload (0 = ok).  The file is NOT trusted: the
+// section table is validated against the file size (and `expect`) and every checksum is verified in a first pass, before the
+// sink sees a single byte -- so a corrupt, truncated or foreign file never leaves a consumer half-updated, and no allocation
+// is sized by an unchecked field.  Returns 0, or a negative code: -1 cannot open / short read, -2 bad magic or version,
+// -3 checksum mismatch, -4 malformed section table (unknown or duplicate tag, size beyond the file, unexpected word count,
+// kskA without kskB), or the sink's value.
 template <class Sink>
-int read(const char* path, mkfhe_params* par, uint64_t (*words_by_tag)[TAG_MAX + 1], Sink&& sink) {
+int read(const char* path, const Expect& expect, mkfhe_params* par, uint64_t (*words_by_tag)[TAG_SLOTS], Sink&& sink) {
     FILE* f = fopen(path, "rb");
     if (!f) return -1;
+    struct Closer {
+        FILE* f;
+        ~Closer() { fclose(f); }
+    } closer{f};
+    if (fseek(f, 0, SEEK_END) != 0) return -1;
+    const long end = ftell(f);
+    if (end < long(sizeof(Header)) || fseek(f, 0, SEEK_SET) != 0) return -1;
     Header h{};
-    int rc = 0;
-    std::vector<uint32_t> buf;
-    if (fread(&h, sizeof h, 1, f) != 1) rc = -1;
-    else if (memcmp(h.magic, MAGIC, 8) != 0 || h.version != VERSION) rc = -2;
-    if (!rc && par) words_to_params(h.par, *par);
+    if (fread(&h, sizeof h, 1, f) != 1) return -1;
+    if (memcmp(h.magic, expect.magic, 8) != 0 || h.version != VERSION) return -2;
+    if (par) words_to_params(h.par, *par);
     if (words_by_tag) memset(*words_by_tag, 0, sizeof *words_by_tag);
-    for (uint32_t i = 0; !rc && i < h.nsections; ++i) {
+    if (h.nsections > TAG_SLOTS) return -4;
+    struct Entry {
+        Section s;
+        long at;
+    } table[TAG_SLOTS];
+    uint64_t have[TAG_SLOTS] = {0};
+    std::vector<uint32_t> buf;
+    constexpr size_t CHUNK = size_t(1) << 22;  // words per read: bounded scratch, whatever the section claims
+    buf.resize(CHUNK);
+    long pos = long(sizeof h);
+    for (uint32_t i = 0; i < h.nsections; ++i) {  // pass 1: structure and checksums
         Section s{};
-        if (fread(&s, sizeof s, 1, f) != 1) { rc = -1; break; }
-        if (s.tag == 0 || s.tag > TAG_MAX) { rc = -4; break; }
-        buf.resize(s.words);
-        if (fread(buf.data(), 4, s.words, f) != s.words) { rc = -1; break; }
-        if (fnv1a(buf.data(), s.words * 4) != s.fnv) { rc = -3; break; }
-        if (words_by_tag) (*words_by_tag)[s.tag] = s.words;
-        rc = sink(s.tag, buf.data(), s.words);
-        const size_t tail = (16 - (sizeof s + s.words * 4) % 16) % 16;
-        if (!rc && tail && fseek(f, long(tail), SEEK_CUR) != 0) rc = -1;
+        if (fread(&s, sizeof s, 1, f) != 1) return -1;
+        pos += long(sizeof s);
+        if (s.tag == 0 || s.tag >= TAG_SLOTS || have[s.tag] || s.words == 0) return -4;
+        if (s.words > uint64_t(end - pos) / 4) return -4;
+        if (expect.words_by_tag && expect.words_by_tag[s.tag] != s.words) return -4;
+        uint64_t hsh = 1469598103934665603ull;
+        for (uint64_t done = 0; done < s.words;) {
+            const size_t take = size_t(std::min<uint64_t>(CHUNK, s.words - done));
+            if (fread(buf.data(), 4, take, f) != take) return -1;
+            hsh = fnv1a(buf.data(), take * 4, hsh);
+            done += take;
+        }
+        if (hsh != s.fnv) return -3;
+        have[s.tag] = s.words;
+        table[i] = Entry{s, pos};
+        pos += long(s.words * 4);
+        const long tail = long((16 - (sizeof s + s.words * 4) % 16) % 16);
+        pos += tail;
+        if (pos > end && i + 1 < h.nsections) return -4;
+        if (tail && i + 1 < h.nsections && fseek(f, tail, SEEK_CUR) != 0) return -1;
     }
-    fclose(f);
-    return rc;
+    if ((have[KSKA] != 0) != (have[KSKB] != 0)) return -4;
+    if (words_by_tag) memcpy(*words_by_tag, have, sizeof have);
+    for (uint32_t i = 0; i < h.nsections; ++i) {  // pass 2: hand the verified payloads to the consumer
+        const Section& s = table[i].s;
+        if (fseek(f, table[i].at, SEEK_SET) != 0) return -1;
+        std::vector<uint32_t> payload(s.words);  // bounded by the file size (checked above)
+        if (fread(payload.data(), 4, s.words, f) != s.words) return -1;
+        if (const int rc = sink(s.tag, payload.data(), s.words)) return rc;
+    }
+    return 0;
 }
 
 }  // namespace mkfhe_keyfile

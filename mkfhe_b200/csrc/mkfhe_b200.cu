@@ -10,6 +10,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <exception>
+#include <new>
 #include <string>
 #include <vector>
 
@@ -237,6 +239,32 @@ struct TmpBuf {  // device scratch of one call, returned to the context's pool (
     }
 };
 }  // namespace
+
+// exceptions (std::bad_alloc on a huge but well-formed file) must not cross the C boundary
+template <class F>
+static int guarded_io(mkfhe_ctx* ctx, F&& body) {
+    try {
+        return body();
+    } catch (const std::bad_alloc&) {
+        return fail(ctx, MKFHE_ENOMEM, "out of host memory");
+    } catch (const std::exception& e) {
+        return fail(ctx, MKFHE_EINVAL, "%s", e.what());
+    }
+}
+
+static void expected_key_words(const mkfhe_params& p, uint64_t (&w)[mkfhe_keyfile::TAG_SLOTS]) {
+    using namespace mkfhe_keyfile;
+    memset(w, 0, sizeof w);
+    w[BK] = bk_words(p);
+    w[PKEY] = uint64_t(p.k) * (p.digitsG - 1) * p.N;
+    if (p.scheme == MKFHE_SCHEME_MKLWE) {
+        w[KSKB] = uint64_t(p.k) * p.N * p.baseKS * p.dKS;
+        w[KSKA] = w[KSKB] * p.n;
+    } else {
+        w[KSK] = uint64_t(p.k) * p.N * p.dKS * p.n;
+        w[CTNAND] = uint64_t(p.k) * p.n;
+    }
+}
 
 extern "C" {
 
@@ -1057,48 +1085,123 @@ int mkfhe_keyfile_write(const char* path, const mkfhe_params* p, const uint32_t*
 
 int mkfhe_keyfile_info(const char* path, mkfhe_params* p, uint64_t* words_by_tag /* [7], index = section tag */) {
     if (!path) return MKFHE_EINVAL;
-    uint64_t w[mkfhe_keyfile::TAG_MAX + 1];
-    const int rc = mkfhe_keyfile::read(path, p, &w, [](uint32_t, const uint32_t*, uint64_t) { return 0; });
-    if (words_by_tag) memcpy(words_by_tag, w, sizeof w);
-    return rc ? MKFHE_EINVAL : MKFHE_OK;
+    return guarded_io(nullptr, [&]() -> int {
+        uint64_t w[mkfhe_keyfile::TAG_SLOTS];
+        const int rc = mkfhe_keyfile::read(path, mkfhe_keyfile::Expect{mkfhe_keyfile::MAGIC, nullptr}, p, &w,
+                                           [](uint32_t, const uint32_t*, uint64_t) { return 0; });
+        if (words_by_tag) memcpy(words_by_tag, w, sizeof(uint64_t) * (mkfhe_keyfile::TAG_MAX + 1));
+        return rc ? MKFHE_EINVAL : MKFHE_OK;
+    });
 }
 
 int mkfhe_keyfile_load(mkfhe_ctx* ctx, const char* path) {
     if (!ctx || !path) return MKFHE_EINVAL;
     using namespace mkfhe_keyfile;
-    // first pass: header only -- the file must describe this context's parameter set
-    mkfhe_params fp{};
-    std::vector<uint32_t> kskA;  // MKLWE: A is held until B arrives (mkfhe_load_ksk_mklwe takes both)
-    bool params_checked = false;
-    int inner = MKFHE_OK;
-    const int rc = read(path, &fp, nullptr, [&](uint32_t tag, const uint32_t* data, uint64_t words) -> int {
-        if (!params_checked) {
+    return guarded_io(ctx, [&]() -> int {
+        // the header first: the file must describe this context's parameter set before any section is looked at
+        mkfhe_params fp{};
+        {
+            FILE* f = fopen(path, "rb");
+            Header h{};
+            const bool ok = f && fread(&h, sizeof h, 1, f) == 1;
+            if (f) fclose(f);
+            if (!ok) return fail(ctx, MKFHE_EINVAL, "mkfhe_keyfile_load: cannot read %s", path);
+            if (memcmp(h.magic, MAGIC, 8) != 0 || h.version != VERSION)
+                return fail(ctx, MKFHE_EINVAL, "mkfhe_keyfile_load: %s is not a version-%u key file", path, VERSION);
+            words_to_params(h.par, fp);
             uint32_t a[13], b[13];
             params_to_words(fp, a);
             params_to_words(ctx->p, b);
-            if (memcmp(a, b, sizeof a) != 0) return -5;
-            params_checked = true;
+            if (memcmp(a, b, sizeof a) != 0)
+                return fail(ctx, MKFHE_EINVAL, "mkfhe_keyfile_load: %s was written for a different parameter set", path);
         }
-        switch (tag) {
-            case BK: inner = mkfhe_load_bk(ctx, data, words); break;
-            case PKEY: inner = mkfhe_load_pkey(ctx, data, words); break;
-            case KSK: inner = mkfhe_load_ksk_mntru(ctx, data, words); break;
-            case KSKA: kskA.assign(data, data + words); break;
-            case KSKB: inner = kskA.empty() ? MKFHE_EINVAL : mkfhe_load_ksk_mklwe(ctx, kskA.data(), kskA.size(), data, words); break;
-            case CTNAND: inner = mkfhe_load_ctnand(ctx, data, words); break;
-            default: return -4;
+        // every section present must have exactly the size this parameter set implies (absent sections stay 0 = not expected)
+        uint64_t want[TAG_SLOTS];
+        expected_key_words(ctx->p, want);
+        std::vector<uint32_t> kskA;  // MKLWE: A is held until B arrives (mkfhe_load_ksk_mklwe takes both)
+        int inner = MKFHE_OK;
+        // read() verifies the whole section table and every checksum BEFORE the first upload below, so a bad file leaves the
+        // context's keys untouched
+        const int rc = read(path, Expect{MAGIC, want}, nullptr, nullptr, [&](uint32_t tag, const uint32_t* data, uint64_t words) -> int {
+            switch (tag) {
+                case BK: inner = mkfhe_load_bk(ctx, data, words); break;
+                case PKEY: inner = mkfhe_load_pkey(ctx, data, words); break;
+                case KSK: inner = mkfhe_load_ksk_mntru(ctx, data, words); break;
+                case KSKA: kskA.assign(data, data + words); break;
+                case KSKB: inner = kskA.empty() ? MKFHE_EINVAL : mkfhe_load_ksk_mklwe(ctx, kskA.data(), kskA.size(), data, words); break;
+                case CTNAND: inner = mkfhe_load_ctnand(ctx, data, words); break;
+                default: return -4;
+            }
+            return inner ? -6 : 0;
+        });
+        switch (rc) {
+            case 0: return MKFHE_OK;
+            case -1: return fail(ctx, MKFHE_EINVAL, "mkfhe_keyfile_load: cannot read %s", path);
+            case -2: return fail(ctx, MKFHE_EINVAL, "mkfhe_keyfile_load: %s is not a version-%u key file", path, VERSION);
+            case -3: return fail(ctx, MKFHE_EINVAL, "mkfhe_keyfile_load: checksum mismatch in %s", path);
+            case -6: return inner;  // mkfhe_load_* already recorded the reason
+            default: return fail(ctx, MKFHE_EINVAL, "mkfhe_keyfile_load: malformed section table in %s (unknown, duplicate or mis-sized section, "
+                                 "kskA without kskB, or data beyond the end of the file)", path);
         }
-        return inner ? -6 : 0;
     });
-    switch (rc) {
-        case 0: return MKFHE_OK;
-        case -1: return fail(ctx, MKFHE_EINVAL, "mkfhe_keyfile_load: cannot read %s", path);
-        case -2: return fail(ctx, MKFHE_EINVAL, "mkfhe_keyfile_load: %s is not a version-%u key file", path, VERSION);
-        case -3: return fail(ctx, MKFHE_EINVAL, "mkfhe_keyfile_load: checksum mismatch in %s", path);
-        case -5: return fail(ctx, MKFHE_EINVAL, "mkfhe_keyfile_load: %s was written for a different parameter set", path);
-        case -6: return inner;  // mkfhe_load_* already recorded the reason
-        default: return fail(ctx, MKFHE_EINVAL, "mkfhe_keyfile_load: malformed section in %s", path);
-    }
+}
+
+// ---- ciphertext / wire-table files (no GPU involved) ----
+int mkfhe_ctfile_write(const char* path, const mkfhe_params* p, const uint32_t* ct, const uint32_t* b, uint64_t n_ct) {
+    if (!path || !p || !ct || n_ct == 0) return MKFHE_EINVAL;
+    const bool lwe = p->scheme == MKFHE_SCHEME_MKLWE;
+    if (lwe && !b) return MKFHE_EINVAL;
+    using namespace mkfhe_keyfile;
+    Writer w;
+    if (!w.open(path, *p, MAGIC_CT)) return MKFHE_EINVAL;
+    bool ok = w.section(CT_A, ct, n_ct * p->k * p->n) && (!lwe || w.section(CT_B, b, n_ct));
+    ok = w.close() && ok;
+    return ok ? MKFHE_OK : MKFHE_EINVAL;
+}
+
+int mkfhe_ctfile_info(const char* path, mkfhe_params* p, uint64_t* n_ct) {
+    if (!path) return MKFHE_EINVAL;
+    return guarded_io(nullptr, [&]() -> int {
+        using namespace mkfhe_keyfile;
+        mkfhe_params fp{};
+        uint64_t w[TAG_SLOTS];
+        if (read(path, Expect{MAGIC_CT, nullptr}, &fp, &w, [](uint32_t, const uint32_t*, uint64_t) { return 0; })) return MKFHE_EINVAL;
+        const uint64_t kn = uint64_t(fp.k) * fp.n;
+        if (kn == 0 || w[CT_A] == 0 || w[CT_A] % kn) return MKFHE_EINVAL;
+        const uint64_t n = w[CT_A] / kn;
+        if ((fp.scheme == MKFHE_SCHEME_MKLWE) != (w[CT_B] != 0) || (w[CT_B] && w[CT_B] != n)) return MKFHE_EINVAL;
+        if (p) *p = fp;
+        if (n_ct) *n_ct = n;
+        return MKFHE_OK;
+    });
+}
+
+int mkfhe_ctfile_read(const char* path, const mkfhe_params* expect, uint32_t* ct, uint32_t* b, uint64_t capacity_ct, uint64_t* n_ct) {
+    if (!path || !ct) return MKFHE_EINVAL;
+    return guarded_io(nullptr, [&]() -> int {
+        using namespace mkfhe_keyfile;
+        mkfhe_params fp{};
+        uint64_t n = 0;
+        int rc = mkfhe_ctfile_info(path, &fp, &n);
+        if (rc) return rc;
+        if (expect) {
+            uint32_t a[13], e[13];
+            params_to_words(fp, a);
+            params_to_words(*expect, e);
+            if (memcmp(a, e, sizeof a) != 0) return MKFHE_EINVAL;
+        }
+        const bool lwe = fp.scheme == MKFHE_SCHEME_MKLWE;
+        if (n > capacity_ct || (lwe && !b)) return MKFHE_EINVAL;
+        rc = read(path, Expect{MAGIC_CT, nullptr}, nullptr, nullptr, [&](uint32_t tag, const uint32_t* data, uint64_t words) -> int {
+            if (tag == CT_A) memcpy(ct, data, words * 4);
+            else if (tag == CT_B) memcpy(b, data, words * 4);
+            else return -4;
+            return 0;
+        });
+        if (rc) return MKFHE_EINVAL;
+        if (n_ct) *n_ct = n;
+        return MKFHE_OK;
+    });
 }
 
 int mkfhe_measure_butterfly_peak(mkfhe_ctx* ctx, double* bfly_per_s) {

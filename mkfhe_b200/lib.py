@@ -25,7 +25,7 @@ SYMBOLS = [
     "mkfhe_load_bk", "mkfhe_load_pkey", "mkfhe_load_ksk_mntru", "mkfhe_load_ksk_mklwe", "mkfhe_load_ctnand",
     "mkfhe_key_image", "mkfhe_key_image_commit",
     "mkfhe_eval_acc", "mkfhe_eval_acc_dev", "mkfhe_eval_nand", "mkfhe_eval_nand_dev", "mkfhe_ntt", "mkfhe_ntt_dev",
-    "mkfhe_load_sk", "mkfhe_decrypt", "mkfhe_decrypt_dev", "mkfhe_eval_circuit", "mkfhe_eval_circuit_dev", "mkfhe_circuit_levels", "mkfhe_keygen_bk", "mkfhe_keygen_pkey", "mkfhe_keygen_ksk_mntru", "mkfhe_keygen_ksk_mklwe", "mkfhe_encrypt_mntru", "mkfhe_encrypt_mklwe", "mkfhe_keyfile_write", "mkfhe_keyfile_info", "mkfhe_keyfile_load",
+    "mkfhe_load_sk", "mkfhe_decrypt", "mkfhe_decrypt_dev", "mkfhe_eval_circuit", "mkfhe_eval_circuit_dev", "mkfhe_circuit_levels", "mkfhe_keygen_bk", "mkfhe_keygen_pkey", "mkfhe_keygen_ksk_mntru", "mkfhe_keygen_ksk_mklwe", "mkfhe_encrypt_mntru", "mkfhe_encrypt_mklwe", "mkfhe_keyfile_write", "mkfhe_keyfile_info", "mkfhe_keyfile_load", "mkfhe_ctfile_write", "mkfhe_ctfile_info", "mkfhe_ctfile_read",
     "mkfhe_decompose", "mkfhe_last_gate_timing", "mkfhe_launch_count", "mkfhe_device_bytes", "mkfhe_version", "mkfhe_measure_int32_peak", "mkfhe_measure_butterfly_peak",
 ]
 
@@ -85,6 +85,9 @@ def load():
     L.mkfhe_keyfile_write.argtypes = [C.c_char_p, C.POINTER(Params), vp, u64, vp, u64, vp, u64, vp, u64, vp, u64]
     L.mkfhe_keyfile_info.argtypes = [C.c_char_p, C.POINTER(Params), C.POINTER(C.c_uint64)]
     L.mkfhe_keyfile_load.argtypes = [vp, C.c_char_p]
+    L.mkfhe_ctfile_write.argtypes = [C.c_char_p, C.POINTER(Params), vp, vp, u64]
+    L.mkfhe_ctfile_info.argtypes = [C.c_char_p, C.POINTER(Params), C.POINTER(u64)]
+    L.mkfhe_ctfile_read.argtypes = [C.c_char_p, C.POINTER(Params), vp, vp, u64, C.POINTER(u64)]
     L.mkfhe_ntt.argtypes = [vp, vp, u64, i32]
     L.mkfhe_ntt_dev.argtypes = [vp, vp, u64, i32]
     L.mkfhe_decompose.argtypes = [vp, vp, vp, u64]

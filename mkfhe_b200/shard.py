@@ -164,7 +164,8 @@ def replicate_key_images(ctx, device, dist=None, src: int = 0) -> int:
 
 def gather_results(local, total: int, dist=None, dst: int = 0):
     """Rows of every rank's `local` tensor ([hi-lo, ...]) concatenated in gate order on rank `dst` (None elsewhere).
-    Shards may be ragged (sizes differ by one): rows are padded to the largest shard for the collective."""
+    Shards may be ragged (sizes differ by one): rows are padded to the largest shard for the collective.  A gather, not an
+    all-gather: only `dst` holds the whole table (2^20 gates at k = 4 are 9.4 GB)."""
     import torch
 
     if dist is None:
@@ -175,10 +176,12 @@ def gather_results(local, total: int, dist=None, dst: int = 0):
     pad = local
     if local.shape[0] < most:
         pad = torch.cat([local, local.new_zeros((most - local.shape[0],) + tuple(local.shape[1:]))])
-    bufs = [torch.empty_like(pad) for _ in range(world)]
-    dist.all_gather(bufs, pad.contiguous())
+    bufs = [torch.empty_like(pad) for _ in range(world)] if rank == dst else None
+    dist.gather(pad.contiguous(), bufs, dst=dst)
     if rank != dst:
         return None
+    if all(hi - lo == most for lo, hi in sizes):
+        return torch.cat(bufs)
     return torch.cat([b[: hi - lo] for b, (lo, hi) in zip(bufs, sizes)])
 
 
@@ -191,3 +194,34 @@ def xor_hash_np(rows: np.ndarray, first_gate: int = 0) -> int:
         for w in range(rows.shape[1]):  # sequential over words, vectorised over gates
             acc = _splitmix_np(acc ^ rows[:, w].astype(np.uint64)) + np.uint64(w)
     return int(np.bitwise_xor.reduce(acc)) if len(rows) else 0
+
+
+def xor_hash_torch(rows, first_gate: int = 0, block: int = 1 << 16) -> int:
+    """xor_hash_np on a torch tensor (int32 storage of the uint32 words), computed where the tensor lives -- the digest of a
+    9 GB result table is taken on the GPU that gathered it.  Same value as xor_hash_np for the same rows."""
+    import torch
+
+    def lsr(x, s):
+        return (x >> s) & ((1 << (64 - s)) - 1)
+
+    def mix(x):
+        x = x ^ lsr(x, 30)
+        x = x * _s64(_MIX1)
+        x = x ^ lsr(x, 27)
+        x = x * _s64(_MIX2)
+        return x ^ lsr(x, 31)
+
+    rows = rows.reshape(rows.shape[0], -1)
+    total = 0
+    for a in range(0, rows.shape[0], block):
+        r = rows[a:a + block]
+        acc = (torch.arange(first_gate + a, first_gate + a + r.shape[0], dtype=torch.int64, device=rows.device) + 1) * _s64(_C_GATE)
+        wide = r.to(torch.int64) & 0xFFFFFFFF
+        for w in range(wide.shape[1]):
+            acc = mix(acc ^ wide[:, w]) + w
+        while acc.shape[0] > 1:  # XOR-reduce by halving
+            half = acc.shape[0] // 2
+            rest = acc[2 * half:]
+            acc = torch.cat([acc[:half] ^ acc[half:2 * half], rest])
+        total ^= int(acc[0].item()) & _M64 if acc.shape[0] else 0
+    return total

@@ -478,7 +478,8 @@ int ref_use_accumulator_b200(void* h, const char* lib, int restore) {
         }
         auto acc = std::make_shared<UniEncAccumulatorB200>(
             lib, c->scheme == 0 ? UniEncAccumulatorB200::XZW : UniEncAccumulatorB200::XZW_B);
-        acc->LoadKeys(c->unienc, c->ek.BSkey, c->ek.Pkey, c->n, c->q);
+        // no LoadKeys call: the accumulator uploads the keys the first time EvalAcc sees them (what INTEGRATION.md section 2
+        // asks of a maintainer is the make_shared line alone)
         c->sch->Acc() = acc;
     });
 }
@@ -493,6 +494,69 @@ int ref_batch_b200_load(void* h, const char* lib) {
         c->batch = std::make_shared<BinFHEBatchB200>(lib);
         c->batch->LoadKeys(c->params, c->method, c->ek);
         if (c->scheme == 0) c->batch->LoadGateCiphertext(c->ctNAND);
+    });
+}
+
+// SaveKeyFile from the reference's own key objects (no GPU involved), and a FRESH evaluator created from that file alone.
+int ref_batch_b200_save_keyfile(void* h, const char* lib, const char* path) {
+    auto* c = static_cast<RefCtx*>(h);
+    return guarded(c, [&] {
+        BinFHEBatchB200 w(lib);
+        w.SaveKeyFile(path, c->params, c->method, c->ek, c->scheme == 0 ? c->ctNAND : nullptr);
+    });
+}
+int ref_batch_b200_load_keyfile(void* h, const char* lib, const char* path) {
+    auto* c = static_cast<RefCtx*>(h);
+    return guarded(c, [&] {
+        c->batch = std::make_shared<BinFHEBatchB200>(lib);
+        c->batch->LoadKeyFile(path);
+    });
+}
+// Ciphertext table round trip through the reference's objects: n encryptions of bits[] -> SaveCiphertexts -> LoadCiphertexts*;
+// flat_out receives the loaded table, dec the reference's Decrypt of every loaded object.  Needs a loaded evaluator (for the
+// parameter stamp); touches no GPU memory.
+int ref_batch_b200_ct_roundtrip(void* h, const char* path, const uint8_t* bits, uint64_t n_ct, uint32_t* flat_in, uint32_t* b_in,
+                                uint32_t* flat_out, uint32_t* b_out, int* dec) {
+    auto* c = static_cast<RefCtx*>(h);
+    return guarded(c, [&] {
+        if (!c->batch) throw std::runtime_error("ref_batch_b200_load has not been called");
+        const size_t kn = size_t(c->k) * c->n;
+        if (c->scheme == 0) {
+            std::vector<MNTRUCiphertext> in;
+            for (uint64_t g = 0; g < n_ct; ++g) {
+                auto x = c->sch->MNTRU()->Encrypt(c->mntru, c->skN, bits[g], 4, NativeInteger(c->q));
+                for (uint32_t u = 0; u < c->k; ++u) put(flat_in + g * kn + size_t(u) * c->n, x->GetElements()[u]);
+                in.push_back(x);
+            }
+            c->batch->SaveCiphertexts(path, in);
+            auto out = c->batch->LoadCiphertextsNTRU(path);
+            if (out.size() != n_ct) throw std::runtime_error("ciphertext count changed on the way through the file");
+            for (uint64_t g = 0; g < n_ct; ++g) {
+                for (uint32_t u = 0; u < c->k; ++u) put(flat_out + g * kn + size_t(u) * c->n, out[g]->GetElements()[u]);
+                MNTRUPlaintext r = 0;
+                c->sch->MNTRU()->Decrypt(c->mntru, c->skN, out[g], &r, 4);
+                dec[g] = int(r);
+            }
+        }
+        else {
+            std::vector<MKLWECiphertext> in;
+            for (uint64_t g = 0; g < n_ct; ++g) {
+                auto x = c->sch->MKLWE()->Encrypt(c->mklwe, c->skL, bits[g], 4, NativeInteger(c->q));
+                for (uint32_t u = 0; u < c->k; ++u) put(flat_in + g * kn + size_t(u) * c->n, x->GetA()[u]);
+                b_in[g] = x->GetB().ConvertToInt<uint32_t>();
+                in.push_back(x);
+            }
+            c->batch->SaveCiphertexts(path, in);
+            auto out = c->batch->LoadCiphertextsLWE(path);
+            if (out.size() != n_ct) throw std::runtime_error("ciphertext count changed on the way through the file");
+            for (uint64_t g = 0; g < n_ct; ++g) {
+                for (uint32_t u = 0; u < c->k; ++u) put(flat_out + g * kn + size_t(u) * c->n, out[g]->GetA()[u]);
+                b_out[g] = out[g]->GetB().ConvertToInt<uint32_t>();
+                MKLWEPlaintext r = 0;
+                c->sch->MKLWE()->Decrypt(c->mklwe, c->skL, out[g], &r, 4);
+                dec[g] = int(r);
+            }
+        }
     });
 }
 

@@ -56,6 +56,10 @@ def lib():
         L.ref_time_gate.argtypes = [C.c_void_p, C.c_uint32, C.POINTER(C.c_double)]
         L.ref_use_accumulator_b200.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
         L.ref_batch_b200_load.argtypes = [C.c_void_p, C.c_char_p]
+        L.ref_batch_b200_save_keyfile.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p]
+        L.ref_batch_b200_load_keyfile.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p]
+        L.ref_batch_b200_ct_roundtrip.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_uint8), C.c_uint64, U32P, U32P, U32P, U32P,
+                                                  C.POINTER(C.c_int)]
         L.ref_batch_b200_gates.argtypes = [C.c_void_p, U32P, U32P, U32P, U32P, U32P, U32P, C.c_uint64, C.POINTER(C.c_int)]
         L.ref_batch_b200_errors.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
         L.ref_batch_b200_circuit.argtypes = [C.c_void_p, U32P, U32P, C.POINTER(C.c_uint8), C.c_uint64, U32P, U32P, U32P, C.c_uint64,
@@ -252,6 +256,25 @@ class Ref:
     # ---- integration/binfhe_batch_b200.h: EvalBinGateBatch over the reference's own key and ciphertext objects ----
     def batch_b200_load(self, libpath: str):
         self._ck(self.L.ref_batch_b200_load(self.h, libpath.encode()), "ref_batch_b200_load")
+
+    def batch_b200_save_keyfile(self, libpath: str, path: str):
+        """BinFHEBatchB200::SaveKeyFile over this context's UniEncBTKey (+ ctNAND): host only, no GPU."""
+        self._ck(self.L.ref_batch_b200_save_keyfile(self.h, libpath.encode(), os.fsencode(path)), "ref_batch_b200_save_keyfile")
+
+    def batch_b200_load_keyfile(self, libpath: str, path: str):
+        """A fresh BinFHEBatchB200 created from the key file alone (replaces the evaluator batch_b200_load made)."""
+        self._ck(self.L.ref_batch_b200_load_keyfile(self.h, libpath.encode(), os.fsencode(path)), "ref_batch_b200_load_keyfile")
+
+    def batch_b200_ct_roundtrip(self, path: str, bits):
+        """Encrypt `bits` with the reference, SaveCiphertexts, LoadCiphertexts*: (table in, b in, table out, b out, Decrypt of out)."""
+        bits = np.ascontiguousarray(bits, dtype=np.uint8)
+        n = len(bits)
+        fin, fout = (np.zeros((n, self.p.k, self.p.n), dtype=np.uint32) for _ in range(2))
+        bin_, bout = (np.zeros(n, dtype=np.uint32) for _ in range(2))
+        dec = (C.c_int * n)()
+        self._ck(self.L.ref_batch_b200_ct_roundtrip(self.h, os.fsencode(path), bits.ctypes.data_as(C.POINTER(C.c_uint8)), n, _p(fin),
+                                                    _p(bin_), _p(fout), _p(bout), dec), "ref_batch_b200_ct_roundtrip")
+        return fin, bin_, fout, bout, np.array(list(dec), dtype=np.int64)
 
     def batch_b200_gates(self, ct1, b1, ct2, b2):
         """ct1, ct2: [B][k][n]; b1, b2: [B] (MK-LWE; ignored for matrix-NTRU).  Returns (out [B][k][n], bout [B], the reference's

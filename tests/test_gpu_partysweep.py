@@ -7,31 +7,38 @@ import numpy as np
 import pytest
 
 import mkfhe_b200 as mk
+from concurrent.futures import ThreadPoolExecutor
+from oracle import refapi
 from util import make_oracle
 
 pytestmark = pytest.mark.gpu
 
-CASES = [  # paramset, environment overrides, gates, which gate to re-compute on the CPU oracle
+# gates re-computed on the CPU oracle per party count (16 for k <= 4, 4 for k = 8, 1 for k = 16) on the
+# kernel the host picks by default; the forced variants check fewer (the oracle costs 0.3 s x 3 k (k + 1) / 18 per gate)
+FULL = {2: 16, 4: 16, 8: 4, 16: 1}
+
+CASES = [  # paramset, environment overrides, gates in the batch, gates re-computed on the CPU oracle
     # batches up to the SM count run on the party-parallel kernel by default (two groups); MKFHE_GROUPS=1 selects the
     # one-group kernel that larger batches use
-    ("STD100_MKNTRU_LWE", {}, 3, 2),
-    ("STD100_MKNTRU_LWE", {"MKFHE_GROUPS": "1"}, 3, 0),
-    ("STD100_MKNTRU", {}, 3, 1),
-    ("STD100_MKNTRU", {"MKFHE_GROUPS": "1"}, 3, 0),
-    ("STD100_MKNTRU_2", {"MKFHE_GROUPS": "1"}, 5, 4),
-    ("STD100_MKNTRU_2", {}, 3, 0),
-    ("STD100_MKNTRU_2", {"MKFHE_GROUPS": "4"}, 3, 1),
+    ("STD100_MKNTRU_LWE", {}, 17, 16),
+    ("STD100_MKNTRU_LWE", {"MKFHE_GROUPS": "1"}, 17, 16),
+    ("STD100_MKNTRU", {}, 17, 16),
+    ("STD100_MKNTRU", {"MKFHE_GROUPS": "1"}, 17, 16),
+    ("STD100_MKNTRU_2", {"MKFHE_GROUPS": "1"}, 17, 16),
+    ("STD100_MKNTRU_2", {}, 17, 16),
+    ("STD100_MKNTRU_2", {"MKFHE_GROUPS": "4"}, 3, 2),
     ("STD100_MKNTRU_2", {"MKFHE_GROUPS": "1", "MKFHE_FAST_ALIAS": "1"}, 3, 2),
-    ("STD100_MKNTRU_LWE_2", {"MKFHE_GROUPS": "1", "MKFHE_MINB": "4"}, 3, 1),
-    ("STD100_MKNTRU_LWE_2", {}, 3, 2),
-    ("STD100_MKNTRU_3", {"MKFHE_GROUPS": "1"}, 2, 1),
-    ("STD100_MKNTRU_3", {}, 2, 0),
-    ("STD100_MKNTRU_4", {}, 2, 0),
+    ("STD100_MKNTRU_LWE_2", {"MKFHE_GROUPS": "1", "MKFHE_MINB": "4"}, 3, 2),
+    ("STD100_MKNTRU_LWE_2", {}, 5, 4),
+    ("STD100_MKNTRU_3", {"MKFHE_GROUPS": "1"}, 5, 4),
+    ("STD100_MKNTRU_3", {}, 5, 4),
+    ("STD100_MKNTRU_4", {}, 2, 1),
+    ("STD100_MKNTRU_4", {"MKFHE_GROUPS": "1"}, 2, 1),
 ]
 
 
-@pytest.mark.parametrize("paramset,env,gates,pick", CASES, ids=[f"{c[0]}-{'-'.join(k + v for k, v in c[1].items()) or 'default'}" for c in CASES])
-def test_large_party_counts_vs_oracle(paramset, env, gates, pick, monkeypatch):
+@pytest.mark.parametrize("paramset,env,gates,checked", CASES, ids=[f"{c[0]}-{'-'.join(k + v for k, v in c[1].items()) or 'default'}" for c in CASES])
+def test_large_party_counts_vs_oracle(paramset, env, gates, checked, monkeypatch):
     if paramset not in mk.PARAMSETS:
         pytest.skip(f"{paramset} not in the parameter table")
     for k_, v in env.items():
@@ -58,14 +65,51 @@ def test_large_party_counts_vs_oracle(paramset, env, gates, pick, monkeypatch):
     ct2 = rng.integers(0, P.q, size=(gates, P.k, P.n), dtype=np.uint32)
     b1 = rng.integers(0, P.q, size=gates, dtype=np.uint32)
     b2 = rng.integers(0, P.q, size=gates, dtype=np.uint32)
-    dup = (pick + 1) % gates  # a copy of the checked gate elsewhere in the batch must come out identical
+    pick, dup = 0, gates - 1  # a copy of a checked gate elsewhere in the batch must come out identical
     ct1[dup], ct2[dup], b1[dup], b2[dup] = ct1[pick], ct2[pick], b1[pick], b2[pick]
     if lwe:
         out, bout = ctx.EvalBinGate("NAND", ct1, ct2, b1, b2)
     else:
         out, bout = ctx.EvalBinGate("NAND", ct1, ct2), np.zeros(gates, dtype=np.uint32)
+    out = np.asarray(out)
     o = make_oracle(P)
-    eo, eb = o.eval_nand(bk, pkey, kskA, kskB, ctnand, ct1[pick].ravel(), int(b1[pick]), ct2[pick].ravel(), int(b2[pick]))
-    assert (np.asarray(out)[pick].ravel() == eo).all() and (not lwe or int(bout[pick]) == eb)
-    assert (np.asarray(out)[dup] == np.asarray(out)[pick]).all() and int(bout[dup]) == int(bout[pick])
+
+    def one(i):
+        eo, eb = o.eval_nand(bk, pkey, kskA, kskB, ctnand, ct1[i].ravel(), int(b1[i]), ct2[i].ravel(), int(b2[i]))
+        return bool((out[i].ravel() == eo).all() and (not lwe or int(bout[i]) == eb))
+
+    with ThreadPoolExecutor(max_workers=os.cpu_count() or 1) as ex:  # the C oracle releases the GIL
+        ok = list(ex.map(one, range(checked)))
+    assert all(ok), f"gates {[i for i, v in enumerate(ok) if not v]} differ from the oracle"
+    assert (out[dup] == out[pick]).all() and int(bout[dup]) == int(bout[pick])
     ctx.close()
+
+
+@pytest.mark.skipif(not refapi.available(), reason="oracle/_ref/libmkfhe_ref.so not present")
+def test_k4_full_size_against_the_compiled_reference():
+    """the party sweep never touched the unmodified reference above k = 2.  One full-size k = 4 context
+    (STD100_MKNTRU_2: the reference's own keygen, 140 MiB bootstrapping key): EvalAcc on a random accumulator and one NAND
+    gate on the reference's encryptions, bit for bit against UniEncAccumulatorXZW::EvalAcc / BinFHEScheme::EvalBinGate."""
+    from gpu_util import ctx_from_params, load_ref_keys
+    from util import params_from_ref
+
+    r = refapi.Ref.from_paramset("STD100_MKNTRU_2")
+    r.keygen()
+    p = params_from_ref(r.p)
+    assert p.k == 4
+    ctx = ctx_from_params(p)
+    load_ref_keys(ctx, r)
+    rng = np.random.default_rng(44)
+    acc = rng.integers(0, p.Q, size=(1, p.k, p.N), dtype=np.uint32)
+    rot = rng.integers(0, p.rot_mod, size=(1, p.k, p.n), dtype=np.uint32)
+    got = ctx.EvalAcc(acc, rot, p.rot_mod)
+    assert (got[0].ravel() == r.eval_acc(acc[0].ravel(), rot[0].ravel(), p.rot_mod)).all()
+    c1, _ = r.encrypt(1)
+    c2, _ = r.encrypt(0)
+    eo, _ = r.eval_gate(c1, 0, c2, 0)
+    for B in (1, 149):  # the party-parallel (latency) kernel and the one-group kernel
+        out = np.asarray(ctx.EvalBinGate("NAND", np.tile(c1.reshape(1, p.k, p.n), (B, 1, 1)), np.tile(c2.reshape(1, p.k, p.n), (B, 1, 1))))
+        assert (out.reshape(B, -1) == eo).all()
+    assert r.decrypt(eo, 0) == 1
+    ctx.close()
+    r.close()

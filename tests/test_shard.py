@@ -85,6 +85,7 @@ def _worker(rank, world, port, total, out_path):
         h = 0
         for p in parts:
             h ^= p
+        assert shard.xor_hash_torch(allout, 0, block=16) == h  # the device-side digest of the gathered table (bench.py, config 4)
         np.savez(out_path, out=allout.numpy().view(np.uint32), hash=np.uint64(h),
                  keysum=np.int64(sum(int(t.to(torch.int64).sum()) for t in dkeys.values())), names=np.array(sorted(dkeys)))
     else:

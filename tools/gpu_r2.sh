@@ -17,7 +17,31 @@ peaks() {
   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o /tmp/pipe_microbench tools/pipe_microbench.cu && /tmp/pipe_microbench > gpurun_out/${TAG}_pipe_microbench.json 2> gpurun_out/${TAG}_pipe_microbench.err
   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o /tmp/bfly_microbench tools/bfly_microbench.cu && /tmp/bfly_microbench > gpurun_out/${TAG}_bfly_microbench.txt 2>&1
   nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,clocks.mem,power.draw --format=csv > gpurun_out/${TAG}_smi.txt; }
+run() { name=$1; shift; (time timeout 1500 python bench.py "$@") > gpurun_out/${TAG}_${name}.json 2> gpurun_out/${TAG}_${name}.err; \
+        echo "== $name"; cut -c1-600 gpurun_out/${TAG}_${name}.json; tail -2 gpurun_out/${TAG}_${name}.err; }
 case $S in
+check)  # full GPU test suite, smoke, default bench line, both transform loaders at N = 2048 / 1024
+  (time python -m pytest tests -m gpu -x -q) > gpurun_out/${TAG}_tests.log 2>&1; tail -5 gpurun_out/${TAG}_tests.log
+  python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${TAG}_smoke.log 2>&1; tail -2 gpurun_out/${TAG}_smoke.log
+  run bench --steps 5 --warmup 3
+  run ntt2048 --workload ntt --ntt-n 2048 --steps 20 --warmup 3 --ntt-variants tma,ldg,b
+  run ntt1024 --workload ntt --ntt-n 1024 --steps 20 --warmup 3 --ntt-variants tma,ldg,b
+  ;;
+exp1)   # experiments: transform-kernel occupancy, CTA de-phasing, shuffle vs shared-memory exchange, 3 party-parallel groups
+  nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o /tmp/exchange_microbench tools/exchange_microbench.cu && /tmp/exchange_microbench > gpurun_out/${TAG}_exchange_microbench.txt 2>&1
+  cat gpurun_out/${TAG}_exchange_microbench.txt
+  for c in 4 5 6; do MKFHE_NTT_CTAS=$c run ntt2048_ctas$c --workload ntt --ntt-n 2048 --steps 20 --warmup 3 --ntt-variants tma --min-seconds 1.5; done
+  for c in 4 5 6; do MKFHE_NTT_CTAS=$c run ntt1024_ctas$c --workload ntt --ntt-n 1024 --steps 20 --warmup 3 --ntt-variants tma --min-seconds 1.5; done
+  q() { echo "== $*"; env "$@" python tests/dev_quick_bench.py --paramset $PS --batches $BT --check $CK --reps 3 2>&1 | grep -E "batch|MISMATCH|exact|Error|error" ; }
+  PS=STD100_MKNTRU_LWE BT=4096 CK=2
+  q X=0; q MKFHE_STAGGER_NS=3000; q MKFHE_STAGGER_NS=6000; q MKFHE_STAGGER_NS=12000
+  PS=STD100_MKNTRU_3 BT=148,296,592 CK=1
+  q X=0; q MKFHE_GROUPS=3; q MKFHE_GROUPS=2
+  PS=STD100_MKNTRU_4 BT=148,296 CK=1
+  q X=0; q MKFHE_GROUPS=3; q MKFHE_GROUPS=1
+  PS=STD100_MKNTRU_2 BT=148,444,888 CK=1
+  q X=0; q MKFHE_GROUPS=3
+  ;;
 prof)
   peaks
   prof k4_444   blind_rotate 1 1 --paramset STD100_MKNTRU_2 --batch 444 --steps 1 --warmup 1 --synthetic-keys
