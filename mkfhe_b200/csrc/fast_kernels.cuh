@@ -49,6 +49,8 @@ struct FastTables {
     uint2 itwB[32];       // itw2[0..31]: the second inverse pass (4 distinct addresses per warp)
     uint32_t zero;        // 0, opaque to the compiler: makes "u + t" a three-input add, which ptxas maps to IADD3 (alu pipe)
                           // instead of IMAD.IADD (fma pipe, the saturated one: profiles/r1_fast_v2_blind_rotate.txt)
+    uint32_t prefetch;    // 1: every step asks L2 for the NEXT step's key tile (prefetch.global.L2, one 128-byte line per thread, no
+                          // registers): with few gates in flight the tile comes from HBM and the step would wait for it
     uint32_t stagger_ns;  // experiment (MKFHE_STAGGER_NS): CTA b of the gate kernel starts (b mod 4) * stagger_ns late, so that the
                           // resident gates of an SM run out of phase; 0 = off
 };
@@ -317,6 +319,17 @@ __device__ __forceinline__ uint4 ldg4_stream(const uint32_t* p) {
     return v;
 }
 
+// L2 prefetch of the evaluation key(s) of step s (32 KiB each: 256 threads x one 128-byte line); s past the end: nothing
+template <bool XZW>
+__device__ __forceinline__ void prefetch_step_keys(const DevCtx& P, uint32_t s, uint32_t tid) {
+    if (s >= P.k * P.n) return;
+    const uint32_t u = s / P.n, i = s - u * P.n;
+    const size_t per = size_t(2) * 2 * FN;
+    const uint32_t* ev1 = P.bk + (size_t(u * P.S) * P.n + i) * per + 32 * tid;
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(ev1));
+    if (XZW) asm volatile("prefetch.global.L2 [%0];" ::"l"(ev1 + size_t(P.n) * per));
+}
+
 // 4 consecutive slots of one key polynomial as HbProd uses it in a step s > 0 (Montgomery form, canonical):
 //   XZW_B: ev1                       (mk-acc-xzw_B.cpp:306-309)
 //   XZW  : ev1 - ev2 * X^-c          (mk-acc-xzw.cpp:322-325: ev1 - ev2*(X^-c - 1) - ev2)
@@ -426,7 +439,7 @@ __device__ __forceinline__ void key_mac4(const DevCtx& P, const uint32_t* k1p, c
 // key evs + ev1 (X^c - 1) [+ ev2 (X^-c - 1)] is assembled per slot, the accumulator itself is decomposed (no monomial) and
 // the result REPLACES it.  Runs once per gate, so it is a separate instantiation instead of selects in the hot loop.
 // Entry: a[] visible to all threads, nobody still reading E1 / E2.  Exit: as entry (ends with a block barrier).
-template <bool XZW, bool FIRST, bool ALIAS>
+template <bool XZW, bool FIRST, bool ALIAS, bool PREFETCH = false>  // PREFETCH: the builds that serve small batches (MINB < 4)
 __device__ __forceinline__ void fast_step(const DevCtx& P, const FastTables& T, uint32_t* a, uint32_t* E1, uint32_t* E2, uint32_t* Ms,
                                           uint32_t s, uint32_t c, uint32_t tid) {
     constexpr uint32_t N = FN, M = 2 * FN;
@@ -439,6 +452,7 @@ __device__ __forceinline__ void fast_step(const DevCtx& P, const FastTables& T, 
     const uint32_t* evs = P.bk + size_t(k) * P.S * n * per + 4 * tid;  // evk* = ek[0][0][n] (mk-acc-xzw.cpp:51,72-74)
     const uint32_t brv8 = __brev(tid) >> 24;
     const uint32_t e0n = cneg * (2 * brv8 + 1), e0p = c * (2 * brv8 + 1);
+    if (PREFETCH && T.prefetch) prefetch_step_keys<XZW>(P, s + 1, tid);
     uint32_t keep[8];  // V while parties are processed, then X of the key owner
     uint32_t y[8];
     // XZW: Q - X^-c at this thread's 8 slots is the same in all k + 1 iterations of the step.  Gathering it from the power
@@ -537,11 +551,11 @@ __global__ void __launch_bounds__(FT, MINB) blind_rotate_fast(const DevCtx P, co
 
     if (T.stagger_ns) __nanosleep((blockIdx.x & 3u) * T.stagger_ns);
     rotate_prologue<GATE>(P, io, blockIdx.x, a, crot);
-    fast_step<XZW, true, ALIAS>(P, T, a, E1, E2, Ms, 0, crot[0], tid);
+    fast_step<XZW, true, ALIAS, (MINB < 4)>(P, T, a, E1, E2, Ms, 0, crot[0], tid);
     for (uint32_t s = 1; s < k * n; ++s) {
         const uint32_t c = crot[s];
         if (c == 0) continue;  // X^0 - 1 = 0: the step leaves acc unchanged
-        fast_step<XZW, false, ALIAS>(P, T, a, E1, E2, Ms, s, c, tid);
+        fast_step<XZW, false, ALIAS, (MINB < 4)>(P, T, a, E1, E2, Ms, s, c, tid);
     }
     rotate_epilogue<GATE>(P, io, blockIdx.x, a, E1);
 }
@@ -551,8 +565,8 @@ __global__ void __launch_bounds__(FT, MINB) blind_rotate_fast(const DevCtx P, co
 // 256-thread CTA per gate leaves the SM with 16 or 8 warps.  Here one CTA of G x 256 threads owns one gate and the G groups
 // process different parties of the same step concurrently: the parties' terms of HbProd (mk-acc-xzw.cpp:240-271) are
 // independent except for sumV, which the groups accumulate in shared memory with atomic adds (sums of canonical residues:
-// k Q < 2^32).  Then one group runs the sumV term (:273-289) while the others wait: a step takes ceil(k / G) + 1 transform
-// rounds instead of k + 1.  Group barriers are named barriers (1 + group); block barriers separate the phases.
+// k Q < 2^32).  Then the owner's group runs the sumV term (:273-289) while the others finish their last party: a step takes
+// ceil(k / G) + 1 transform rounds instead of k + 1, and the same 3k + 3 transforms as the sequential schedule.  Group barriers are named barriers (1 + group); block barriers separate the phases.
 // Shared memory: a[k][N] | per group E1[2][FNP] | E2[FNP] (absent when ALIAS) | Vs[N] | Ms[N] (XZW: Q - X^-c per slot, shared by
 // the groups).  The rotation amounts are not kept on chip (k = 16 needs the space): rotation_amount() re-derives the step's
 // amount from the gate's inputs.
@@ -575,6 +589,7 @@ __device__ __forceinline__ void grouped_step(const DevCtx& P, const FastTables& 
     const uint32_t brv8 = __brev(tid) >> 24;
     const uint32_t e0n = cneg * (2 * brv8 + 1), e0p = c * (2 * brv8 + 1);
     uint32_t y[8];
+    if (T.prefetch && grp == 0) prefetch_step_keys<XZW>(P, s + 1, tid);
     // XZW: Q - X^-c per slot, once per step (see fast_step).  Every group writes the same values to the same words (slot =
     // f(tid) only), each thread reads back the words it wrote itself; steps are separated by block barriers.
     uint32_t* Mt = Ms + 4 * tid;
@@ -586,9 +601,12 @@ __device__ __forceinline__ void grouped_step(const DevCtx& P, const FastTables& 
             *reinterpret_cast<uint4*>(Mt + (N / 2) * ch) = make_uint4(Q - mq[0], Q - mq[1], Q - mq[2], Q - mq[3]);
         }
     }
-    // ---- phase 1: the parties, round-robin over the groups (order index k - 1 = the key owner).  The owner's <D_u, d> is
-    // transformed back and added to a_u like everybody else's (one more inverse transform per step than the sequential
-    // schedule, which adds it to <g^-1(sumV), f> in the evaluation domain: same sum, and no registers held across phases) ----
+    // ---- phase 1: the parties, round-robin over the groups (order index k - 1 = the key owner, always the LAST party of its
+    // group).  Every party's <D_p, d> is transformed back and added to a_p right away -- except a group's last party: its
+    // product stays in registers (y) across the barrier that completes sumV, so that the critical path of a step (the owner
+    // group: party terms, then the sumV term) loses one inverse transform: the owner's <D_u, d> is added to <g^-1(sumV), f> in
+    // the evaluation domain and transformed back once (as the sequential kernel does), and the other groups transform their
+    // held product back WHILE the owner group works on the sumV term, instead of idling through it.
 #pragma unroll 1
     for (uint32_t it = grp; it < k; it += G) {
         uint32_t D[2][8];
@@ -613,7 +631,7 @@ __device__ __forceinline__ void grouped_step(const DevCtx& P, const FastTables& 
                 y[sl] = x4[q];
             }
         }
-        {
+        if (it + G < k) {  // not this group's last party: back to coefficients now
             inv_ntt_regs<true>(y, ALIAS ? E1 : E2, T, Q, tid, bar);
 #pragma unroll
             for (int r = 0; r < 8; ++r) {
@@ -628,36 +646,46 @@ __device__ __forceinline__ void grouped_step(const DevCtx& P, const FastTables& 
             if (ALIAS) gate_sync<true>(bar);
         }
     }
+    // the party whose product this group still holds in y (evaluation domain, < 3Q): order index of its last iteration
+    const uint32_t itl = grp + ((k - 1 - grp) / G) * G;
+    const uint32_t pl = (itl + 1 < k) ? (itl < u ? itl : itl + 1) : u;
     __syncthreads();  // sumV complete in Vs
-    // ---- phase 2: the sumV term <g^-1(sumV), f>, added to a_u by the group that processed the owner ----
     if (grp == (k - 1) % G) {
-        uint32_t D[2][8];
+        // ---- phase 2 (owner group): the sumV term <g^-1(sumV), f>, added to the held <D_u, d>, one inverse, a_u ----
+        uint32_t D[2][8], v8[8];
 #pragma unroll
         for (int sl = 0; sl < 8; ++sl) {  // Vs[256 sl + tid] = slot 8 tid + sl: conflict-free for the atomics and here
             uint32_t v = Vs[256 * sl + tid];  // < 16Q
             Vs[256 * sl + tid] = 0;           // ready for the next step
             v = min(v, v - 8 * Q);
-            y[sl] = min(v, v - 4 * Q);        // < 4Q
+            v8[sl] = min(v, v - 4 * Q);       // < 4Q
         }
-        inv_ntt_regs<true>(y, ALIAS ? E1 : E2, T, Q, tid, bar);
+        inv_ntt_regs<true>(v8, ALIAS ? E1 : E2, T, Q, tid, bar);
         if (ALIAS) gate_sync<true>(bar);
 #pragma unroll
-        for (int r = 0; r < 8; ++r) decompose2(fold1(y[r], Q), Q, g, D[0][r], D[1][r]);
+        for (int r = 0; r < 8; ++r) decompose2(fold1(v8[r], Q), Q, g, D[0][r], D[1][r]);
         fwd_ntt_regs<2, true>(D, E1, T, Q, tid, bar);
 #pragma unroll
         for (int ch = 0; ch < 2; ++ch) {
             uint32_t x4[4];
             key_mac4<XZW, FIRST>(P, ev1 + N, ev2 + N, evs + N, c, cneg, e0p, e0n, ch, D, x4, (XZW && !FIRST) ? Mt : nullptr);  // "f" column
 #pragma unroll
-            for (int q = 0; q < 4; ++q) y[4 * ch + q] = x4[q];  // < 3Q
+            for (int q = 0; q < 4; ++q) y[4 * ch + q] += x4[q];  // < 6Q
         }
+    }
+    // every group: its held product (the owner group's now includes the sumV term) back to coefficients, into a_pl
+    {
         inv_ntt_regs<true>(y, ALIAS ? E1 : E2, T, Q, tid, bar);
-        uint32_t* ap = a + u * N;
+        uint32_t* ap = a + pl * N;
 #pragma unroll
         for (int r = 0; r < 8; ++r) {
-            uint32_t v = ap[tid + 256 * r] + y[r];
-            v = min(v, v - 2 * Q);
-            ap[tid + 256 * r] = min(v, v - Q);
+            if (FIRST) {
+                ap[tid + 256 * r] = fold1(y[r], Q);
+            } else {
+                uint32_t v = ap[tid + 256 * r] + y[r];
+                v = min(v, v - 2 * Q);
+                ap[tid + 256 * r] = min(v, v - Q);
+            }
         }
     }
     __syncthreads();  // a[] complete (and every group past its last exchange) before the next step
@@ -1314,6 +1342,11 @@ inline cudaError_t fast_blind_rotate(FastState& F, const DevCtx& d, bool gate, c
     const bool xzw = d.variant == 0;
     const uint32_t G = fast_groups(d, batch, F.sms);
     F.T.stagger_ns = getenv("MKFHE_STAGGER_NS") ? uint32_t(atoi(getenv("MKFHE_STAGGER_NS"))) : 0u;
+    // key prefetch: on in latency mode (at most one gate per SM, k <= 8), where the tile comes from HBM and nothing hides the
+    // wait: 1, 16 gates boolean-mklwe 8.88 -> 8.75, 9.02 -> 8.74 ms; boolean-mkntru 12.22 -> 11.93 ms; k = 4 36.9 -> 36.2 ms;
+    // no gain from 148 gates on and -0.7% at k = 16 (profiles/r2_s6_latency.txt).  MKFHE_PREFETCH=0/1 forces it for A/B runs
+    F.T.prefetch = (batch <= uint32_t(F.sms) && d.k <= 8) ? 1u : 0u;
+    if (const char* pf = getenv("MKFHE_PREFETCH")) F.T.prefetch = pf[0] == '1' ? 1u : 0u;
     const bool alias = G > 1 ? grouped_smem_bytes(d.k, d.n, G, false) > 227 * 1024 : fast_use_alias(d);
     const size_t smem = G > 1 ? grouped_smem_bytes(d.k, d.n, G, alias) : fast_smem_bytes(d.k, d.n, alias, xzw);
     auto launch = [&](auto kern) -> cudaError_t {
@@ -1388,7 +1421,7 @@ inline cudaError_t fast_ntt(FastState& F, const DevCtx& d, uint32_t* polys, uint
     // default: the bulk-copy ring (ntt_batch_tma); MKFHE_NTT_VARIANT=ldg selects the register-prefetch kernel it is measured against
     const char* var = getenv("MKFHE_NTT_VARIANT");
     if (!getenv("MKFHE_NTT16") && !(var && var[0] == 'l')) {
-        int ctas = 5;  // measured on B200 (profiles/r2_s3_ntt*.json)
+        int ctas = 4;  // 4, 5 and 6 resident CTAs measured equal on B200 (profiles/r2_s3_experiments.txt): the kernel is not latency-bound
         if (const char* c = getenv("MKFHE_NTT_CTAS")) ctas = std::min(6, std::max(4, atoi(c)));
         const size_t smem = ntt_tma_smem_bytes(ctas);
         const unsigned g = unsigned(std::min<uint64_t>(batch, uint64_t(F.sms) * ctas));

@@ -162,10 +162,12 @@ def replicate_key_images(ctx, device, dist=None, src: int = 0) -> int:
     return total
 
 
-def gather_results(local, total: int, dist=None, dst: int = 0):
+def gather_results(local, total: int, dist=None, dst: int = 0, out=None):
     """Rows of every rank's `local` tensor ([hi-lo, ...]) concatenated in gate order on rank `dst` (None elsewhere).
     Shards may be ragged (sizes differ by one): rows are padded to the largest shard for the collective.  A gather, not an
-    all-gather: only `dst` holds the whole table (2^20 gates at k = 4 are 9.4 GB)."""
+    all-gather: only `dst` holds the whole table (2^20 gates at k = 4 are 9.4 GB).  `out` (rank dst; optional): a tensor of
+    world * largest-shard rows to receive into, reused across calls -- with even shards the result is a view of it and the
+    call allocates and copies nothing."""
     import torch
 
     if dist is None:
@@ -176,13 +178,28 @@ def gather_results(local, total: int, dist=None, dst: int = 0):
     pad = local
     if local.shape[0] < most:
         pad = torch.cat([local, local.new_zeros((most - local.shape[0],) + tuple(local.shape[1:]))])
-    bufs = [torch.empty_like(pad) for _ in range(world)] if rank == dst else None
+    bufs = None
+    if rank == dst:
+        if out is None or out.shape[0] != world * most or out.dtype != local.dtype:
+            out = torch.empty((world * most,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+        bufs = list(out.chunk(world))
     dist.gather(pad.contiguous(), bufs, dst=dst)
     if rank != dst:
         return None
     if all(hi - lo == most for lo, hi in sizes):
-        return torch.cat(bufs)
+        return out
     return torch.cat([b[: hi - lo] for b, (lo, hi) in zip(bufs, sizes)])
+
+
+def gather_buffer(local, total: int, dist=None, dst: int = 0):
+    """The reusable receive buffer gather_results(..., out=) wants on rank `dst` (None elsewhere / single process)."""
+    import torch
+
+    if dist is None or dist.get_rank() != dst:
+        return None
+    world = dist.get_world_size()
+    most = max(hi - lo for lo, hi in (shard_range(total, world, r) for r in range(world)))
+    return torch.empty((world * most,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
 
 
 def xor_hash_np(rows: np.ndarray, first_gate: int = 0) -> int:

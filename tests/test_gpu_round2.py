@@ -189,7 +189,10 @@ def test_key_file_written_by_the_reference_bridge_serves_a_fresh_evaluator(toy, 
     assert (dec == 1 - (m0 & m1)).all()
     bits = rng.integers(0, 2, 9)
     fin, bin_, fout, bo, dec = r.batch_b200_ct_roundtrip(str(tmp_path / "cts.mkfhe"), bits)
-    assert (fin == fout).all() and (bin_ == bo).all() and (dec == bits).all()
+    assert (fin == fout).all() and (bin_ == bo).all()
+    # the loaded objects decrypt exactly as the originals do (toy sets are small enough for the reference's own Decrypt to
+    # miss the plaintext now and then, so the originals' decryptions are the yardstick, not the bits)
+    assert list(dec) == [r.decrypt(fin[g].ravel(), int(bin_[g])) for g in range(len(bits))]
     r.close()
 
 

@@ -27,6 +27,34 @@ check)  # full GPU test suite, smoke, default bench line, both transform loaders
   run ntt2048 --workload ntt --ntt-n 2048 --steps 20 --warmup 3 --ntt-variants tma,ldg,b
   run ntt1024 --workload ntt --ntt-n 1024 --steps 20 --warmup 3 --ntt-variants tma,ldg,b
   ;;
+lat)    # small batches: L2 key prefetch on / off (MKFHE_PREFETCH), then the config-4 job on one GPU
+  (time python -m pytest tests -m gpu -x -q) > gpurun_out/${TAG}_tests.log 2>&1; tail -3 gpurun_out/${TAG}_tests.log
+  q() { echo "== $*"; env "$@" python tests/dev_quick_bench.py --paramset $PS --batches $BT --check $CK --reps 5 2>&1 | grep -E "batch|MISMATCH|exact|Error|error" ; }
+  PS=STD100_MKNTRU_LWE BT=1,16,148,296 CK=1; q MKFHE_PREFETCH=0; q MKFHE_PREFETCH=1
+  PS=STD100_MKNTRU BT=1,148,296 CK=1; q MKFHE_PREFETCH=0; q MKFHE_PREFETCH=1
+  PS=STD100_MKNTRU_2 BT=1,148 CK=1; q MKFHE_PREFETCH=0; q MKFHE_PREFETCH=1
+  PS=STD100_MKNTRU_4 BT=148 CK=1; q MKFHE_PREFETCH=0; q MKFHE_PREFETCH=1
+  bash tools/gpu_r2.sh sharded $TAG 1 1048576
+  ;;
+nccl)   # transports and collective bandwidth of this box: tools/gpu_r2.sh nccl <tag> <N>
+  N=${3:-2}
+  NCCL_DEBUG=INFO python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29513 tools/nccl_probe.py > gpurun_out/${TAG}_nccl_n$N.log 2>&1
+  grep -E "^\{" gpurun_out/${TAG}_nccl_n$N.log > gpurun_out/${TAG}_nccl_n$N.json
+  grep -E "via |NVLS|P2P|SHM|Channel 00|Connected|nvlink|NVLink" gpurun_out/${TAG}_nccl_n$N.log | head -40 > gpurun_out/${TAG}_nccl_n${N}_transports.txt
+  nvidia-smi topo -m > gpurun_out/${TAG}_topo.txt 2>&1
+  cat gpurun_out/${TAG}_nccl_n$N.json; head -12 gpurun_out/${TAG}_nccl_n${N}_transports.txt; cat gpurun_out/${TAG}_topo.txt | head -14
+  ;;
+multi)  # N GPUs (gpurun --gpus N): default bench under torchrun, both arms; then the config-4 job at --total-gates $3 (default 2^17)
+  N=${3:-2}; TG=${4:-131072}
+  TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511"
+  (time timeout 1200 $TR bench.py --gpus $N --steps 5 --warmup 3) > gpurun_out/${TAG}_bench_n$N.json 2> gpurun_out/${TAG}_bench_n$N.err; cut -c1-300 gpurun_out/${TAG}_bench_n$N.json; tail -3 gpurun_out/${TAG}_bench_n$N.err
+  (time timeout 1500 $TR bench.py --gpus $N --workload sharded --paramset STD100_MKNTRU_2 --total-gates $TG --steps 1 --warmup 1 --check-oracle 16) > gpurun_out/${TAG}_sharded_n$N.json 2> gpurun_out/${TAG}_sharded_n$N.err; cut -c1-300 gpurun_out/${TAG}_sharded_n$N.json; tail -3 gpurun_out/${TAG}_sharded_n$N.err
+  ;;
+sharded)  # the config-4 job alone: tools/gpu_r2.sh sharded <tag> <N> <total gates>
+  N=${3:-1}; TG=${4:-1048576}
+  if [ "$N" = 1 ]; then TR="python"; else TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512"; fi
+  (time timeout 1700 $TR bench.py --gpus $N --workload sharded --paramset STD100_MKNTRU_2 --total-gates $TG --steps 1 --warmup 1 --check-oracle 16) > gpurun_out/${TAG}_sharded_n$N.json 2> gpurun_out/${TAG}_sharded_n$N.err; cut -c1-400 gpurun_out/${TAG}_sharded_n$N.json; tail -3 gpurun_out/${TAG}_sharded_n$N.err
+  ;;
 exp1)   # experiments: transform-kernel occupancy, CTA de-phasing, shuffle vs shared-memory exchange, 3 party-parallel groups
   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o /tmp/exchange_microbench tools/exchange_microbench.cu && /tmp/exchange_microbench > gpurun_out/${TAG}_exchange_microbench.txt 2>&1
   cat gpurun_out/${TAG}_exchange_microbench.txt
