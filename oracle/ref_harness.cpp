@@ -670,12 +670,21 @@ int ref_batch_b200_errors(void* h, int* mask) {
             probe(1, [&] { c->batch->EvalBinGateBatch(AND, std::vector<MNTRUCiphertext>{a}, std::vector<MNTRUCiphertext>{b}); });
             probe(2, [&] { c->batch->EvalBinGateBatch(NAND, std::vector<MNTRUCiphertext>{a}, std::vector<MNTRUCiphertext>{a}); });
             probe(4, [&] { c->batch->EvalBinGateBatch(NAND, std::vector<MNTRUCiphertext>{a, b}, std::vector<MNTRUCiphertext>{b}); });
+            // a circuit whose primary input (wire 1: read by the gate, written by none) holds no ciphertext
+            probe(8, [&] {
+                std::vector<MNTRUCiphertext> w{a, nullptr, nullptr};
+                c->batch->EvalCircuit(w, std::vector<BinFHEBatchB200::Gate>{{0, 1, 2}});
+            });
         }
         else {
             MKLWECiphertext a = mk_mklwe_ct(c, z.data(), 1, c->q), b = mk_mklwe_ct(c, z.data(), 1, c->q);
             probe(1, [&] { c->batch->EvalBinGateBatch(AND, std::vector<MKLWECiphertext>{a}, std::vector<MKLWECiphertext>{b}); });
             probe(2, [&] { c->batch->EvalBinGateBatch(NAND, std::vector<MKLWECiphertext>{a}, std::vector<MKLWECiphertext>{a}); });
             probe(4, [&] { c->batch->EvalBinGateBatch(NAND, std::vector<MKLWECiphertext>{a, b}, std::vector<MKLWECiphertext>{b}); });
+            probe(8, [&] {
+                std::vector<MKLWECiphertext> w{a, nullptr, nullptr};
+                c->batch->EvalCircuit(w, std::vector<BinFHEBatchB200::Gate>{{0, 1, 2}});
+            });
         }
     });
 }

@@ -195,7 +195,7 @@ def test_batched_gate_class_over_reference_objects(full):
     for g in (0, 3, 5):  # the reference takes 1-2 s a gate
         eo, eb = r.eval_gate(ct1[g].ravel(), int(b1[g]), ct2[g].ravel(), int(b2[g]))
         assert (out[g].ravel() == eo).all() and int(bout[g]) == int(eb)
-    assert r.batch_b200_errors() == 7
+    assert r.batch_b200_errors() == 15  # wrong gate | one object twice | ragged vectors | a circuit input that holds no ciphertext
     # EvalCircuit of the same class: a + b for one 2-bit adder on reference ciphertext objects
     from mkfhe_b200.netlist import ripple_carry_adders
 

@@ -24,6 +24,9 @@ CASES = [  # paramset, environment overrides, gates in the batch, gates re-compu
     ("STD100_MKNTRU_LWE", {"MKFHE_GROUPS": "1"}, 17, 16),
     ("STD100_MKNTRU", {}, 17, 16),
     ("STD100_MKNTRU", {"MKFHE_GROUPS": "1"}, 17, 16),
+    ("STD100_MKNTRU", {"MKFHE_GROUPS": "1", "MKFHE_MINB": "4"}, 5, 4),  # the 64-register XZW build (batches that fill 4-gate waves better)
+    ("STD100_MKNTRU", {"MKFHE_GROUPS": "3"}, 3, 2),
+    ("STD100_MKNTRU_LWE_2", {"MKFHE_GROUPS": "3"}, 3, 2),
     ("STD100_MKNTRU_2", {"MKFHE_GROUPS": "1"}, 17, 16),
     ("STD100_MKNTRU_2", {}, 17, 16),
     ("STD100_MKNTRU_2", {"MKFHE_GROUPS": "4"}, 3, 2),

@@ -27,6 +27,25 @@ check)  # full GPU test suite, smoke, default bench line, both transform loaders
   run ntt2048 --workload ntt --ntt-n 2048 --steps 20 --warmup 3 --ntt-variants tma,ldg,b
   run ntt1024 --workload ntt --ntt-n 1024 --steps 20 --warmup 3 --ntt-variants tma,ldg,b
   ;;
+prof2)  # final kernels: launch list of the default bench command, ncu --set full of the gate kernels on the bench's own launches
+        # (distinct gates, reference keys), the TMA transform kernel, the party-parallel kernel with the held-product schedule
+  CMD="python bench.py --steps 2 --warmup 3 --no-cpu-baseline --check-oracle 0"
+  $CMD > gpurun_out/${TAG}_bench_plain.json 2> gpurun_out/${TAG}_bench_plain.err && \
+  ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${TAG}_bench_launches.csv $CMD > gpurun_out/${TAG}_bench_launches.log 2>&1
+  prof mklwe4096  blind_rotate_fast 3 1 --steps 1 --warmup 3 --no-also --check-oracle 0
+  prof mkntru4096 blind_rotate_fast 3 1 --steps 1 --warmup 3 --no-also --check-oracle 0 --paramset STD100_MKNTRU
+  prof ntt2048tma ntt_batch_tma 4 2 --workload ntt --ntt-n 2048 --steps 1 --warmup 1 --ntt-variants tma --min-seconds 0
+  prof mklwe148   blind_rotate_grouped 3 1 --batch 148 --steps 1 --warmup 3 --synthetic-keys --no-also --check-oracle 0
+  prof k16_148    blind_rotate_grouped 1 1 --paramset STD100_MKNTRU_4 --batch 148 --steps 1 --warmup 1 --synthetic-keys --check-oracle 0
+  ;;
+exp2)   # party-parallel groups after the held-product schedule: 1 / 2 / 3 groups at k = 8, 16 (both flavours), k = 4
+  q() { echo "== $*"; env "$@" python tests/dev_quick_bench.py --paramset $PS --batches $BT --check $CK --reps 3 2>&1 | grep -E "batch|MISMATCH|exact|Error|error" ; }
+  PS=STD100_MKNTRU_3 BT=148,296,592 CK=1; q X=0; q MKFHE_GROUPS=2; q MKFHE_GROUPS=3
+  PS=STD100_MKNTRU_LWE_3 BT=148,296,592 CK=1; q X=0; q MKFHE_GROUPS=2; q MKFHE_GROUPS=3
+  PS=STD100_MKNTRU_4 BT=148,296 CK=1; q X=0; q MKFHE_GROUPS=3
+  PS=STD100_MKNTRU_2 BT=148,444 CK=1; q X=0; q MKFHE_GROUPS=3
+  PS=STD100_MKNTRU_LWE_2 BT=148,444 CK=1; q X=0; q MKFHE_GROUPS=3
+  ;;
 lat)    # small batches: L2 key prefetch on / off (MKFHE_PREFETCH), then the config-4 job on one GPU
   (time python -m pytest tests -m gpu -x -q) > gpurun_out/${TAG}_tests.log 2>&1; tail -3 gpurun_out/${TAG}_tests.log
   q() { echo "== $*"; env "$@" python tests/dev_quick_bench.py --paramset $PS --batches $BT --check $CK --reps 5 2>&1 | grep -E "batch|MISMATCH|exact|Error|error" ; }
@@ -49,6 +68,12 @@ multi)  # N GPUs (gpurun --gpus N): default bench under torchrun, both arms; the
   TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511"
   (time timeout 1200 $TR bench.py --gpus $N --steps 5 --warmup 3) > gpurun_out/${TAG}_bench_n$N.json 2> gpurun_out/${TAG}_bench_n$N.err; cut -c1-300 gpurun_out/${TAG}_bench_n$N.json; tail -3 gpurun_out/${TAG}_bench_n$N.err
   (time timeout 1500 $TR bench.py --gpus $N --workload sharded --paramset STD100_MKNTRU_2 --total-gates $TG --steps 1 --warmup 1 --check-oracle 16) > gpurun_out/${TAG}_sharded_n$N.json 2> gpurun_out/${TAG}_sharded_n$N.err; cut -c1-300 gpurun_out/${TAG}_sharded_n$N.json; tail -3 gpurun_out/${TAG}_sharded_n$N.err
+  ;;
+n8)     # 8 GPUs: the config-4 job, then both arms of the default bench under torchrun (what the driver runs at round end)
+  bash tools/gpu_r2.sh sharded $TAG 8 1048576
+  TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29514"
+  (time timeout 900 $TR bench.py --impl reference --gpus 8 --steps 2 --warmup 1) > gpurun_out/${TAG}_ref_n8.json 2> gpurun_out/${TAG}_ref_n8.err; cut -c1-300 gpurun_out/${TAG}_ref_n8.json
+  (time timeout 900 $TR bench.py --gpus 8 --steps 5 --warmup 3) > gpurun_out/${TAG}_bench_n8.json 2> gpurun_out/${TAG}_bench_n8.err; cut -c1-300 gpurun_out/${TAG}_bench_n8.json; tail -3 gpurun_out/${TAG}_bench_n8.err
   ;;
 sharded)  # the config-4 job alone: tools/gpu_r2.sh sharded <tag> <N> <total gates>
   N=${3:-1}; TG=${4:-1048576}
