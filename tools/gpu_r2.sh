@@ -37,6 +37,8 @@ prof2)  # final kernels: launch list of the default bench command, ncu --set ful
   prof ntt2048tma ntt_batch_tma 4 2 --workload ntt --ntt-n 2048 --steps 1 --warmup 1 --ntt-variants tma --min-seconds 0
   prof mklwe148   blind_rotate_grouped 3 1 --batch 148 --steps 1 --warmup 3 --synthetic-keys --no-also --check-oracle 0
   prof k16_148    blind_rotate_grouped 1 1 --paramset STD100_MKNTRU_4 --batch 148 --steps 1 --warmup 1 --synthetic-keys --check-oracle 0
+  # calibration: what the pipe counters read while the GPU does nothing but register-resident butterflies (the roofline's peak)
+  prof bflypeak   butterfly_peak 1 1 --batch 148 --steps 1 --warmup 1 --synthetic-keys --no-also --check-oracle 0
   ;;
 exp2)   # party-parallel groups after the held-product schedule: 1 / 2 / 3 groups at k = 8, 16 (both flavours), k = 4
   q() { echo "== $*"; env "$@" python tests/dev_quick_bench.py --paramset $PS --batches $BT --check $CK --reps 3 2>&1 | grep -E "batch|MISMATCH|exact|Error|error" ; }
