@@ -1360,12 +1360,10 @@ inline cudaError_t fast_blind_rotate(FastState& F, const DevCtx& d, bool gate, c
     int minb = G > 1 ? 1 : std::max(2, fast_gates_per_sm(smem));
     // XZW at 64 registers spills in the step loop; 3 gates per SM with 80 registers measured 3% faster than 4 with 64
     // (16.66k vs 16.17k gates/s, boolean-mkntru k = 2, profiles/r1_s28_xzw_quick.txt); XZW_B measured equal, stays at 4
-    // -- per full wave; a batch that ends in a thin last wave can still be faster at 4: time ~ waves(g) * g / rate(g) with
-    // rate(3) = 1.03 rate(4).  4096 gates: 10 waves of 444 (the last 22% full) against 7 waves of 592 -> 4 per SM wins by 4%.
-    if (xzw && minb > 3) {
-        const uint64_t w3 = (uint64_t(batch) + 3ull * F.sms - 1) / (3ull * F.sms), w4 = (uint64_t(batch) + 4ull * F.sms - 1) / (4ull * F.sms);
-        if (double(w3) * 3.0 / 1.03 <= double(w4) * 4.0) minb = 3;
-    }
+    // A thin last wave does not change this: 4096 gates are 10 waves of 444 at 3 per SM (the last 22% full) against 7 waves of
+    // 592 at 4, yet 3 per SM measured 242.4 ms and 4 per SM 247.6 ms (profiles/r2_s2_bench.json, r2_s11_mkntru4096.txt) -- the
+    // gates of a thin wave have their SMs to themselves and finish in half a wave time.
+    if (xzw && minb > 3) minb = 3;
     // a batch that puts fewer gates on an SM than the budget allows gets the registers of the absent ones: ms per launch at
     // 296 gates, 64 / 80 / 128 registers: 16.14 / 15.57 / 14.91 (boolean-mklwe); at 444: 22.31 / 21.56 / 22.72
     // (profiles/r1_s57_minb_midrange.txt)
