@@ -1078,8 +1078,8 @@ def main():
     ap.add_argument("--adder-bits", type=int, default=8)
     ap.add_argument("--ntt-n", type=int, default=2048)
     ap.add_argument("--ntt-batch", type=int, default=1 << 18)
-    ap.add_argument("--ntt-variants", default="tma,ldg", help="loaders to measure: tma (bulk-copy ring, the default kernel), ldg "
-                    "(register prefetch), b (tma with the Barrett-style final fold)")
+    ap.add_argument("--ntt-variants", default="tma,1,ldg", help="loaders to measure: tma (the default kernel: bulk-copy ring, two "
+                    "polynomials per slot), 1 (one polynomial per slot), b (1 with the Barrett-style final fold), ldg (register prefetch)")
     ap.add_argument("--min-seconds", type=float, default=2.5, help="ntt: minimum length of a timed region (clock sampling)")
     args = ap.parse_args()
     if args.synthetic_keys:

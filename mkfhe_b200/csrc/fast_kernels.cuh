@@ -51,6 +51,7 @@ struct FastTables {
                           // instead of IMAD.IADD (fma pipe, the saturated one: profiles/r1_fast_v2_blind_rotate.txt)
     uint32_t prefetch;    // 1: every step asks L2 for the NEXT step's key tile (prefetch.global.L2, one 128-byte line per thread, no
                           // registers): with few gates in flight the tile comes from HBM and the step would wait for it
+    uint32_t pair;        // 1: the 80- / 128-register builds take inverse transforms two at a time (fast_step PAIR); MKFHE_PAIR=0/1
     uint32_t stagger_ns;  // experiment (MKFHE_STAGGER_NS): CTA b of the gate kernel starts (b mod 4) * stagger_ns late, so that the
                           // resident gates of an SM run out of phase; 0 = off
 };
@@ -288,6 +289,100 @@ __device__ __forceinline__ void inv_ntt_regs(uint32_t (&x)[8], uint32_t* E, cons
     for (int r = 0; r < 8; ++r) x[r] = shoup_lazy(x[r], __ldg(T.scale2 + tid + 256 * r), Q);
 }
 
+// The same inverse transform on NP polynomials at once (shared twiddle loads: the stand-alone transform kernel is short of
+// LSU wavefronts, and twiddles are a quarter of them).  E: NP * FNP words.  The gate kernels keep the one-polynomial form above.
+template <int NP, bool HALF = false>
+__device__ __forceinline__ void inv_ntt_regs_np(uint32_t (&x)[NP][8], uint32_t* E, const FastTables& T, uint32_t Q, uint32_t tid) {
+    const uint32_t twoQ = 2 * Q, sixQ = 6 * Q;
+    const uint32_t lane = tid & 31, lo2 = tid & 3;
+    const ExIdx ex(tid);
+#pragma unroll
+    for (int p = 0; p < NP; ++p)
+#pragma unroll
+        for (int i = 0; i < 8; i += 2) {
+            const uint32_t u = x[p][i], v = x[p][i + 1];
+            x[p][i] = u + v;
+            x[p][i + 1] = u + sixQ - v;
+        }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        if (i & 2) continue;
+#pragma unroll
+        for (int p = 0; p < NP; ++p) MKFHE_BFLY(x[p][i], x[p][i + 2], T.itwA[2 + (i & 1)]);
+    }
+    __syncwarp();
+#pragma unroll
+    for (int p = 0; p < NP; ++p)
+#pragma unroll
+        for (int c = 0; c < 2; ++c)
+            *reinterpret_cast<uint4*>(E + p * FNP + ex.D(c)) = make_uint4(x[p][4 * c], x[p][4 * c + 1], x[p][4 * c + 2], x[p][4 * c + 3]);
+    __syncwarp();
+#pragma unroll
+    for (int p = 0; p < NP; ++p)
+#pragma unroll
+        for (int r = 0; r < 8; ++r) x[p][r] = E[p * FNP + ex.C(r)];
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+        const int h = 1 << s;
+        const uint32_t twi = 4 * h + lo2;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            if (r & h) continue;
+            const uint2 w = T.itwB[twi + 4 * (r & (h - 1))];
+#pragma unroll
+            for (int p = 0; p < NP; ++p) MKFHE_BFLY(x[p][r], x[p][r + h], w);
+        }
+    }
+#pragma unroll
+    for (int p = 0; p < NP; ++p)
+#pragma unroll
+        for (int r = 0; r < 8; ++r) E[p * FNP + ex.C(r)] = x[p][r];
+    __syncwarp();
+#pragma unroll
+    for (int p = 0; p < NP; ++p)
+#pragma unroll
+        for (int r = 0; r < 8; ++r) x[p][r] = E[p * FNP + ex.B(r)];
+#pragma unroll
+    for (int s = 0; s < 3; ++s) {
+        const int h = 1 << s;
+        const uint2* tws = T.itw2 + 32 * h + lane;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            if (r & h) continue;
+            const uint2 w = __ldg(tws + 32 * (r & (h - 1)));
+#pragma unroll
+            for (int p = 0; p < NP; ++p) MKFHE_BFLY(x[p][r], x[p][r + h], w);
+        }
+    }
+#pragma unroll
+    for (int p = 0; p < NP; ++p)
+#pragma unroll
+        for (int r = 0; r < 8; ++r) E[p * FNP + ex.B(r)] = x[p][r];
+    __syncthreads();
+#pragma unroll
+    for (int p = 0; p < NP; ++p)
+#pragma unroll
+        for (int r = 0; r < 8; ++r) x[p][r] = E[p * FNP + ex.A(r)];
+#pragma unroll
+    for (int s = 0; s < (HALF ? 2 : 3); ++s) {
+        const int h = 1 << s;
+        const uint2* tws = T.itw2 + 256 * h + tid;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            if (r & h) continue;
+            const uint2 w = __ldg(tws + 256 * (r & (h - 1)));
+#pragma unroll
+            for (int p = 0; p < NP; ++p) MKFHE_BFLY(x[p][r], x[p][r + h], w);
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        const uint2 sc = __ldg(T.scale2 + tid + 256 * r);
+#pragma unroll
+        for (int p = 0; p < NP; ++p) x[p][r] = shoup_lazy(x[p][r], sc, Q);
+    }
+}
+
 // ---- helpers of the specialised step ---------------------------------------------------------------------------------
 
 // SignedDigitDecompose of one canonical coefficient t (mk-acc.cpp:54-80), first digit dropped, two digits kept, each
@@ -439,7 +534,15 @@ __device__ __forceinline__ void key_mac4(const DevCtx& P, const uint32_t* k1p, c
 // key evs + ev1 (X^c - 1) [+ ev2 (X^-c - 1)] is assembled per slot, the accumulator itself is decomposed (no monomial) and
 // the result REPLACES it.  Runs once per gate, so it is a separate instantiation instead of selects in the hot loop.
 // Entry: a[] visible to all threads, nobody still reading E1 / E2.  Exit: as entry (ends with a block barrier).
-template <bool XZW, bool FIRST, bool ALIAS, bool PREFETCH = false>  // PREFETCH: the builds that serve small batches (MINB < 4)
+// PAIR (the builds with 80 or 128 registers): inverse transforms are taken two at a time.  A non-owner party's product X_p is
+// parked in registers until the next product is ready -- the next non-owner's, or the owner's V -- and both go back to
+// coefficients in ONE two-polynomial inverse (inv_ntt_regs_np<2>): the pair shares every twiddle load (22 of the inverse's 66
+// LSU instructions) and doubles the independent butterflies per stage, which is what the low-occupancy builds are short of
+// (stall `wait`, profiles/r2_s1_k8_296.txt).  Same exact sums, in a different order of evaluation.  The pair exchanges through
+// E1 (both halves): no barrier is needed against the forward transforms around it, because a transform's last exchange and the
+// next transform's first exchange use the same per-thread-private positions (forward ends on pattern D and the inverse begins
+// on D; the inverse ends on A and the next forward begins on A).
+template <bool XZW, bool FIRST, bool ALIAS, bool PREFETCH = false, bool PAIR = false>  // PREFETCH: the builds that serve small batches
 __device__ __forceinline__ void fast_step(const DevCtx& P, const FastTables& T, uint32_t* a, uint32_t* E1, uint32_t* E2, uint32_t* Ms,
                                           uint32_t s, uint32_t c, uint32_t tid) {
     constexpr uint32_t N = FN, M = 2 * FN;
@@ -455,6 +558,9 @@ __device__ __forceinline__ void fast_step(const DevCtx& P, const FastTables& T, 
     if (PREFETCH && T.prefetch) prefetch_step_keys<XZW>(P, s + 1, tid);
     uint32_t keep[8];  // V while parties are processed, then X of the key owner
     uint32_t y[8];
+    uint32_t hold[8];  // PAIR: a non-owner's product waiting for a partner
+    uint32_t hp = 0;
+    bool have = false;
     // XZW: Q - X^-c at this thread's 8 slots is the same in all k + 1 iterations of the step.  Gathering it from the power
     // table costs 8 scattered 4-byte loads per iteration (up to 32 L1 wavefronts each: as much LSU traffic as everything
     // else in the iteration); it is gathered once per step instead and parked in shared memory at this thread's own words
@@ -513,6 +619,43 @@ __device__ __forceinline__ void fast_step(const DevCtx& P, const FastTables& T, 
                 for (int q = 0; q < 4; ++q) y[4 * ch + q] = keep[4 * ch + q] + x4[q];  // < 6Q
             }
         }
+        if (PAIR && !FIRST && it < k) {
+            if (it + 1 < k && !have) {  // a non-owner with nothing parked: park it, no inverse yet
+#pragma unroll
+                for (int r = 0; r < 8; ++r) hold[r] = y[r];
+                hp = p;
+                have = true;
+                continue;
+            }
+            if (have) {  // parked product + this one (a non-owner's X_p, or the owner's V) in one two-polynomial inverse
+                uint32_t z[2][8];
+#pragma unroll
+                for (int r = 0; r < 8; ++r) {
+                    z[0][r] = hold[r];
+                    z[1][r] = y[r];
+                }
+                inv_ntt_regs_np<2>(z, E1, T, Q, tid);
+                uint32_t* ah = a + hp * N;
+#pragma unroll
+                for (int r = 0; r < 8; ++r) {
+                    uint32_t v = ah[tid + 256 * r] + z[0][r];  // < 3Q
+                    v = min(v, v - 2 * Q);
+                    ah[tid + 256 * r] = min(v, v - Q);
+                    y[r] = z[1][r];
+                }
+                have = false;
+                if (it + 1 < k) {
+                    uint32_t* ap = a + p * N;
+#pragma unroll
+                    for (int r = 0; r < 8; ++r) {
+                        uint32_t v = ap[tid + 256 * r] + y[r];
+                        v = min(v, v - 2 * Q);
+                        ap[tid + 256 * r] = min(v, v - Q);
+                    }
+                }
+                continue;  // (the owner's V stays in y for the next iteration)
+            }
+        }
         inv_ntt_regs(y, ALIAS ? E1 : E2, T, Q, tid);
         if (it + 1 != k) {  // a_p (+)= result (the owner's V goes on to the next iteration in registers instead)
             uint32_t* ap = a + p * N;
@@ -527,10 +670,10 @@ __device__ __forceinline__ void fast_step(const DevCtx& P, const FastTables& T, 
                 }
             }
         }
-        // ALIAS: everybody is done reading the inverse's last exchange before the next forward transform writes E1.
         // (a_p itself needs no barrier here: it was read -- at shifted positions, by other threads -- before the two
-        // barriers inside this iteration's transforms, and is read again only after the barrier that ends the step.)
-        if (ALIAS) __syncthreads();
+        // barriers inside this iteration's transforms, and is read again only after the barrier that ends the step.  Nor does
+        // ALIAS: the inverse's last exchange reads, and the next forward's first exchange writes, pattern A -- positions
+        // private to each thread; round 1 had a block barrier here that bought nothing.)
     }
     __syncthreads();  // a[] complete before the next step's shifted reads
 }
@@ -551,11 +694,12 @@ __global__ void __launch_bounds__(FT, MINB) blind_rotate_fast(const DevCtx P, co
 
     if (T.stagger_ns) __nanosleep((blockIdx.x & 3u) * T.stagger_ns);
     rotate_prologue<GATE>(P, io, blockIdx.x, a, crot);
-    fast_step<XZW, true, ALIAS, (MINB < 4)>(P, T, a, E1, E2, Ms, 0, crot[0], tid);
+    fast_step<XZW, true, ALIAS, (MINB < 4), false>(P, T, a, E1, E2, Ms, 0, crot[0], tid);
     for (uint32_t s = 1; s < k * n; ++s) {
         const uint32_t c = crot[s];
         if (c == 0) continue;  // X^0 - 1 = 0: the step leaves acc unchanged
-        fast_step<XZW, false, ALIAS, (MINB < 4)>(P, T, a, E1, E2, Ms, s, c, tid);
+        if (MINB < 4 && T.pair) fast_step<XZW, false, ALIAS, true, true>(P, T, a, E1, E2, Ms, s, c, tid);
+        else fast_step<XZW, false, ALIAS, (MINB < 4), false>(P, T, a, E1, E2, Ms, s, c, tid);
     }
     rotate_epilogue<GATE>(P, io, blockIdx.x, a, E1);
 }
@@ -880,6 +1024,88 @@ __global__ void __launch_bounds__(FT, CTAS) ntt_batch_tma(const FastTables T, co
         }
     }
     if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");  // shared memory stays valid until the stores have read it
+}
+
+// Two polynomials per ring slot and CTA iteration (16 KiB bulk copies): the transforms of a pair share every twiddle load, which
+// takes 13 (forward) / 22 (inverse) of the ~90 / ~108 LSU wavefronts per warp and polynomial off the kernel's busiest unit.
+// 3 slots of 16 KiB + two exchange buffers = 66 KiB per CTA, 3 CTAs per SM at up to 80 registers.  `pairs` counts slots; an odd
+// last polynomial is the caller's business (it goes through ntt_batch_tma).
+constexpr int NTT2_STAGES = 3;
+__host__ __device__ inline size_t ntt_tma2_smem_bytes() { return (size_t(NTT2_STAGES) * 2 * FN + 2 * FNP) * 4 + NTT2_STAGES * 8; }
+
+template <bool HALF, bool SHIFTFOLD>
+__global__ void __launch_bounds__(FT, 3) ntt_batch_tma2(const FastTables T, const uint32_t Q, const uint2 one2, uint32_t* polys,
+                                                        const uint64_t pairs, const int inverse) {
+    extern __shared__ __align__(128) uint32_t sm[];
+    uint32_t* ring = sm;
+    uint32_t* E = ring + NTT2_STAGES * 2 * FN;
+    uint64_t* full = reinterpret_cast<uint64_t*>(E + 2 * FNP);
+    const uint32_t tid = threadIdx.x;
+    constexpr uint32_t BYTES = 2 * FN * 4;
+    const uint64_t mine = blockIdx.x < pairs ? (pairs - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < NTT2_STAGES; ++s) mbar_init(full + s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        for (uint64_t i = 0; i < mine && i < NTT2_STAGES - 1; ++i) {
+            mbar_expect_tx(full + i, BYTES);
+            bulk_load(ring + i * 2 * FN, polys + (blockIdx.x + i * gridDim.x) * 2 * FN, BYTES, full + i);
+        }
+    }
+    __syncthreads();
+    for (uint64_t i = 0; i < mine; ++i) {
+        const uint32_t s = uint32_t(i % NTT2_STAGES), parity = uint32_t(i / NTT2_STAGES) & 1u;
+        uint32_t* buf = ring + s * 2 * FN;
+        mbar_wait(full + s, parity);
+        uint32_t x[2][8];
+        if (!inverse) {
+#pragma unroll
+            for (int p = 0; p < 2; ++p)
+#pragma unroll
+                for (int r = 0; r < 8; ++r) x[p][r] = buf[p * FN + tid + 256 * r];
+            fwd_ntt_regs<2, false, HALF>(x, E, T, Q, tid);
+#pragma unroll
+            for (int p = 0; p < 2; ++p)
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    uint4 v;
+                    if (SHIFTFOLD) {
+                        v.x = fold1(fold_shift27(x[p][4 * c + 0], Q), Q); v.y = fold1(fold_shift27(x[p][4 * c + 1], Q), Q);
+                        v.z = fold1(fold_shift27(x[p][4 * c + 2], Q), Q); v.w = fold1(fold_shift27(x[p][4 * c + 3], Q), Q);
+                    } else {
+                        v.x = fold1(shoup_lazy(x[p][4 * c + 0], one2, Q), Q); v.y = fold1(shoup_lazy(x[p][4 * c + 1], one2, Q), Q);
+                        v.z = fold1(shoup_lazy(x[p][4 * c + 2], one2, Q), Q); v.w = fold1(shoup_lazy(x[p][4 * c + 3], one2, Q), Q);
+                    }
+                    *reinterpret_cast<uint4*>(buf + p * FN + 8 * tid + 4 * c) = v;
+                }
+        } else {
+#pragma unroll
+            for (int p = 0; p < 2; ++p)
+#pragma unroll
+                for (int c = 0; c < 2; ++c) {
+                    const uint4 v = *reinterpret_cast<const uint4*>(buf + p * FN + 8 * tid + 4 * c);
+                    x[p][4 * c] = v.x; x[p][4 * c + 1] = v.y; x[p][4 * c + 2] = v.z; x[p][4 * c + 3] = v.w;
+                }
+            inv_ntt_regs_np<2, HALF>(x, E, T, Q, tid);
+#pragma unroll
+            for (int p = 0; p < 2; ++p)
+#pragma unroll
+                for (int r = 0; r < 8; ++r) buf[p * FN + tid + 256 * r] = fold1(x[p][r], Q);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncthreads();
+        if (tid == 0) {
+            bulk_store(polys + (blockIdx.x + i * gridDim.x) * 2 * FN, buf, BYTES);
+            const uint64_t nx = i + NTT2_STAGES - 1;
+            if (nx < mine) {
+                if (i > 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                const uint32_t ns = uint32_t(nx % NTT2_STAGES);
+                mbar_expect_tx(full + ns, BYTES);
+                bulk_load(ring + ns * 2 * FN, polys + (blockIdx.x + nx * gridDim.x) * 2 * FN, BYTES, full + ns);
+            }
+        }
+    }
+    if (tid == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
 
 // ---- butterfly micro-benchmark: the measured peak the gate kernel's roofline is quoted against -----------------------------
@@ -1312,12 +1538,19 @@ inline cudaError_t fast_load_pkey(FastState&, const DevCtx& d, uint64_t words, c
 
 // gates resident per SM: 64 registers x 256 threads allow 4; shared memory (1 KiB reserved per CTA) may allow fewer
 inline int fast_gates_per_sm(size_t smem) { return int(std::min<size_t>(4, (227 * 1024) / (smem + 1024))); }
-// Measured on B200 (k = 4, STD100_MKNTRU_2): 4 gates per SM with ALIAS run at 3783 gates/s, 3 gates per SM without at
-// 4246 gates/s -- the extra block barrier per iteration costs more than the fourth resident gate brings.  So ALIAS is only
-// the fallback for party counts whose separate buffer does not fit shared memory at all.
-inline bool fast_use_alias(const DevCtx& d) {
+// ALIAS (the inverse transform exchanges through E1[0]; no buffer of its own: 9 KiB less per gate).  Round 1 paid a block barrier
+// per iteration for it and measured it slower (k = 4: 3783 vs 4246 gates/s); the barrier was never needed (fast_step), and
+// without it the layout is free.  It is chosen when the separate buffer does not fit at all, and -- for the XZW_B flavour,
+// whose 64-register build does not spill -- when it lets one more gate share an SM and the batch has gates for it:
+// boolean-mklwe k = 4, 888 gates: 4 per SM aliased 6436 gates/s, 3 per SM with the separate buffer 6034 (6198 with paired
+// inverses); profiles/r2_s14_pair_alias.txt.  The XZW flavour at 64 registers spills and stays at 3 per SM.
+inline bool fast_use_alias(const DevCtx& d, uint32_t batch, int sms) {
     if (const char* e = getenv("MKFHE_FAST_ALIAS")) return e[0] == '1';
-    return fast_smem_bytes(d.k, d.n, false, d.variant == 0) > 227 * 1024;
+    const bool xzw = d.variant == 0;
+    const size_t plain = fast_smem_bytes(d.k, d.n, false, xzw), aliased = fast_smem_bytes(d.k, d.n, true, xzw);
+    if (plain > 227 * 1024) return true;
+    const int g0 = fast_gates_per_sm(plain), g1 = fast_gates_per_sm(aliased);
+    return !xzw && g1 > g0 && uint64_t(batch) > uint64_t(g0) * uint64_t(sms);
 }
 
 // party-parallel groups per gate, overridable for experiments with MKFHE_GROUPS.  Measured on B200, gates/s
@@ -1347,7 +1580,9 @@ inline cudaError_t fast_blind_rotate(FastState& F, const DevCtx& d, bool gate, c
     // no gain from 148 gates on and -0.7% at k = 16 (profiles/r2_s6_latency.txt).  MKFHE_PREFETCH=0/1 forces it for A/B runs
     F.T.prefetch = (batch <= uint32_t(F.sms) && d.k <= 8) ? 1u : 0u;
     if (const char* pf = getenv("MKFHE_PREFETCH")) F.T.prefetch = pf[0] == '1' ? 1u : 0u;
-    const bool alias = G > 1 ? grouped_smem_bytes(d.k, d.n, G, false) > 227 * 1024 : fast_use_alias(d);
+    F.T.pair = 1u;
+    if (const char* pr = getenv("MKFHE_PAIR")) F.T.pair = pr[0] == '1' ? 1u : 0u;
+    const bool alias = G > 1 ? grouped_smem_bytes(d.k, d.n, G, false) > 227 * 1024 : fast_use_alias(d, batch, F.sms);
     const size_t smem = G > 1 ? grouped_smem_bytes(d.k, d.n, G, alias) : fast_smem_bytes(d.k, d.n, alias, xzw);
     auto launch = [&](auto kern) -> cudaError_t {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
@@ -1421,8 +1656,33 @@ inline cudaError_t fast_ntt(FastState& F, const DevCtx& d, uint32_t* polys, uint
                             uint64_t* launches) {
     // HALF: batch counts PAIRS of size-1024 polynomials (the caller sends an odd last one through the generic kernel)
     const unsigned grid = unsigned(std::min<uint64_t>(batch, uint64_t(F.sms) * 4));
-    // default: the bulk-copy ring (ntt_batch_tma); MKFHE_NTT_VARIANT=ldg selects the register-prefetch kernel it is measured against
     const char* var = getenv("MKFHE_NTT_VARIANT");
+    // default: the bulk-copy ring with TWO polynomials per slot (ntt_batch_tma2: +2.4% / +3.6% at N = 2048 / 1024 over one per
+    // slot, profiles/r2_s13_ntt*.json); MKFHE_NTT_VARIANT = 1: one polynomial per slot (ntt_batch_tma), b: the same with the
+    // Barrett-style output fold, ldg: the register-prefetch kernel of round 1
+    if ((!var || var[0] == '2' || var[0] == 't') && !getenv("MKFHE_NTT16") && batch >= 2) {  // (HALF: a slot holds two pairs)
+        const uint64_t pairs = batch / 2;
+        const size_t smem = ntt_tma2_smem_bytes();
+        const unsigned g = unsigned(std::min<uint64_t>(pairs, uint64_t(F.sms) * 3));
+        const bool sf = fold_shift27_ok(d.mod.Q);
+        auto launch = [&](auto kern) -> cudaError_t {
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+            if (e != cudaSuccess) return e;
+            kern<<<g, FT, smem, st>>>(F.T, d.mod.Q, F.one2, polys, pairs, inverse);
+            return cudaSuccess;
+        };
+        cudaError_t e = F.half ? (sf ? launch(ntt_batch_tma2<true, true>) : launch(ntt_batch_tma2<true, false>))
+                               : (sf ? launch(ntt_batch_tma2<false, true>) : launch(ntt_batch_tma2<false, false>));
+        if (e != cudaSuccess) return e;
+        ++*launches;
+        if ((e = cudaGetLastError()) != cudaSuccess) return e;
+        if (batch & 1) {  // the odd last one: the one-polynomial kernel
+            polys += (batch - 1) * FN;
+            batch = 1;
+        } else {
+            return cudaSuccess;
+        }
+    }
     if (!getenv("MKFHE_NTT16") && !(var && var[0] == 'l')) {
         int ctas = 4;  // 4, 5 and 6 resident CTAs measured equal on B200 (profiles/r2_s3_experiments.txt): the kernel is not latency-bound
         if (const char* c = getenv("MKFHE_NTT_CTAS")) ctas = std::min(6, std::max(4, atoi(c)));

@@ -33,10 +33,11 @@ def _ntt_params(N):
                            variant=1, scheme=1)
 
 
-@pytest.mark.parametrize("variant", ["tma", "ldg", "b"])
+@pytest.mark.parametrize("variant", ["tma", "1", "ldg", "b"])
 @pytest.mark.parametrize("N", [2048, 1024])
 def test_ntt_loaders_vs_oracle(N, variant, monkeypatch):
-    """ntt_batch_tma (cp.async.bulk + mbarrier ring; 'b': its Barrett-style output fold) and ntt_batch_fast (register prefetch)
+    """ntt_batch_tma2 (the default: cp.async.bulk + mbarrier ring, two polynomials per slot, an odd last one on ntt_batch_tma),
+    ntt_batch_tma ('1': one polynomial per slot; 'b': its Barrett-style output fold) and ntt_batch_fast ('ldg': register prefetch)
     give the oracle's NativePoly::SetFormat bit for bit, for batches below, at and above the ring depth and the grid size
     (592 CTAs: 593 and 1777 polynomials give CTAs with 1, 2, 3 and 4 = NTT_STAGES polynomials; N = 1024 counts pairs)."""
     from gpu_util import ctx_from_params

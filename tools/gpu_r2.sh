@@ -1,6 +1,8 @@
 #!/bin/bash
 # Round-2 GPU sessions, one script: tools/gpu_r2.sh <session> <tag>.  Everything lands in gpurun_out/<tag>_*.
 #   prof   ncu --set full of the gate kernels at k = 4 / 8 / 16, the 128-register k = 2 build, the batched transform; per-line
+# (transform-loader names: up to session r2s13 "tma" meant one polynomial per ring slot and "2" two; since then "tma" is the
+# two-polynomial default and "1" the one-polynomial kernel)
 #          shared-memory conflict attribution of the k = 2 gate kernel; integer-pipe peaks
 S=$1; TAG=$2; mkdir -p gpurun_out
 prof() { # prof <name> <kernel regex> <skip> <count> <bench args...>
@@ -24,8 +26,8 @@ check)  # full GPU test suite, smoke, default bench line, both transform loaders
   (time python -m pytest tests -m gpu -x -q) > gpurun_out/${TAG}_tests.log 2>&1; tail -5 gpurun_out/${TAG}_tests.log
   python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${TAG}_smoke.log 2>&1; tail -2 gpurun_out/${TAG}_smoke.log
   run bench --steps 5 --warmup 3
-  run ntt2048 --workload ntt --ntt-n 2048 --steps 20 --warmup 3 --ntt-variants tma,ldg,b
-  run ntt1024 --workload ntt --ntt-n 1024 --steps 20 --warmup 3 --ntt-variants tma,ldg,b
+  run ntt2048 --workload ntt --ntt-n 2048 --steps 20 --warmup 3 --ntt-variants tma,1,ldg
+  run ntt1024 --workload ntt --ntt-n 1024 --steps 20 --warmup 3 --ntt-variants tma,1,ldg
   ;;
 prof2)  # final kernels: launch list of the default bench command, ncu --set full of the gate kernels on the bench's own launches
         # (distinct gates, reference keys), the TMA transform kernel, the party-parallel kernel with the held-product schedule
@@ -39,6 +41,20 @@ prof2)  # final kernels: launch list of the default bench command, ncu --set ful
   prof k16_148    blind_rotate_grouped 1 1 --paramset STD100_MKNTRU_4 --batch 148 --steps 1 --warmup 1 --synthetic-keys --check-oracle 0
   # calibration: what the pipe counters read while the GPU does nothing but register-resident butterflies (the roofline's peak)
   prof bflypeak   butterfly_peak 1 1 --batch 148 --steps 1 --warmup 1 --synthetic-keys --no-also --check-oracle 0
+  ;;
+ntt2)   # full GPU tests + smoke, then the transform loaders incl. the two-polynomial ring
+  (time python -m pytest tests -m gpu -q) > gpurun_out/${TAG}_tests.log 2>&1; tail -4 gpurun_out/${TAG}_tests.log
+  python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${TAG}_smoke.log 2>&1; tail -3 gpurun_out/${TAG}_smoke.log
+  run ntt2048 --workload ntt --ntt-n 2048 --steps 20 --warmup 3 --ntt-variants tma,2,ldg
+  run ntt1024 --workload ntt --ntt-n 1024 --steps 20 --warmup 3 --ntt-variants tma,2,ldg
+  ;;
+pair)   # paired inverse transforms (MKFHE_PAIR=0/1) in the 80- / 128-register builds of the sequential kernel
+  q() { echo "== $*"; env "$@" python tests/dev_quick_bench.py --paramset $PS --batches $BT --check $CK --reps 3 2>&1 | grep -E "batch|MISMATCH|exact|Error|error" ; }
+  PS=STD100_MKNTRU_3 BT=296,592 CK=2; q MKFHE_PAIR=0; q MKFHE_PAIR=1
+  PS=STD100_MKNTRU_2 BT=444,888 CK=2; q MKFHE_PAIR=0; q MKFHE_PAIR=1
+  PS=STD100_MKNTRU_LWE_2 BT=444,888 CK=2; q MKFHE_PAIR=0; q MKFHE_PAIR=1; q MKFHE_PAIR=1 MKFHE_FAST_ALIAS=1; q MKFHE_PAIR=0 MKFHE_FAST_ALIAS=1
+  PS=STD100_MKNTRU_LWE BT=296,444 CK=2; q MKFHE_PAIR=0; q MKFHE_PAIR=1
+  PS=STD100_MKNTRU BT=296,444,4096 CK=2; q MKFHE_PAIR=0; q MKFHE_PAIR=1
   ;;
 exp2)   # party-parallel groups after the held-product schedule: 1 / 2 / 3 groups at k = 8, 16 (both flavours), k = 4
   q() { echo "== $*"; env "$@" python tests/dev_quick_bench.py --paramset $PS --batches $BT --check $CK --reps 3 2>&1 | grep -E "batch|MISMATCH|exact|Error|error" ; }
