@@ -193,12 +193,12 @@ def make_workload(paramset: str, method: str, batch: int, seed: int, encrypt: bo
 
 
 # ---------------------------------------------------------------- CPU arms
-def cpu_gates_per_s(paramset: str, threads: int, gates: int, ref=None):
+def cpu_gates_per_s(paramset: str, threads: int, gates: int, ref=None, force_port: bool = False):
     """The reference's EvalBinGate(NAND) on `threads` host threads over `gates` gates.  kind = "reference" when
     oracle/_ref (the unmodified reference, compiled in place) is present, else "port" (oracle/mkfhe_oracle.c)."""
     from oracle import refapi
 
-    if ref is not None or (refapi.available() and paramset in refapi.PARAMSETS):
+    if not force_port and (ref is not None or (refapi.available() and paramset in refapi.PARAMSETS)):
         r = ref
         if r is None:
             r = refapi.Ref.from_paramset(paramset)
@@ -572,7 +572,9 @@ def measure_gate_batch(env, paramset, B, steps, warmup, check_oracle, cpu_gates_
         if world == 1 and not no_cpu_baseline:
             cores = os.cpu_count() or 1
             gates = cores * cpu_gates_per_thread  # bounded sample: ~10-20 s of host work
-            gps, kind, secs = cpu_gates_per_s(paramset, cores, gates, ref)
+            # with synthetic keys (the party sweep: the reference's keygen takes minutes at k >= 8) the CPU leg is the C port
+            # of the path on the same synthetic keys' shapes
+            gps, kind, secs = cpu_gates_per_s(paramset, cores, gates, ref, force_port=ref is None and bool(os.environ.get("MKFHE_BENCH_SYNTHETIC_KEYS")))
             res["cpu_baseline"] = {"value": gps, "unit": UNIT, "cores": cores, "kind": kind,
                                    "sample": f"{gates} EvalBinGate(NAND) on {cores} threads in {secs:.1f}s, same paramset"}
             if ref is not None:  # the reference example's own measurement: one gate, one thread (boolean-mkntru.cpp:34-38)

@@ -48,6 +48,15 @@ ntt2)   # full GPU tests + smoke, then the transform loaders incl. the two-polyn
   run ntt2048 --workload ntt --ntt-n 2048 --steps 20 --warmup 3 --ntt-variants tma,2,ldg
   run ntt1024 --workload ntt --ntt-n 1024 --steps 20 --warmup 3 --ntt-variants tma,2,ldg
   ;;
+sweep)  # configs[2]: party-count sweep at batch 16384 (synthetic keys), oracle sample 16/16/4/1, CPU leg = the C port on all cores
+  q() { echo "== $*"; env "$@" python tests/dev_quick_bench.py --paramset $PS --batches $BT --check $CK --reps 3 2>&1 | grep -E "batch|MISMATCH|exact|Error|error" ; }
+  PS=STD100_MKNTRU_LWE BT=4096 CK=1; q X=0; q MKFHE_MINB=3
+  PS=STD100_MKNTRU_LWE_2 BT=888,4096 CK=1; q X=0
+  run k2  --paramset STD100_MKNTRU   --batch 16384 --steps 2 --warmup 1 --synthetic-keys --no-also --check-oracle 16 --cpu-baseline-gates-per-thread 4
+  run k4  --paramset STD100_MKNTRU_2 --batch 16384 --steps 1 --warmup 1 --synthetic-keys --no-also --check-oracle 16 --cpu-baseline-gates-per-thread 1
+  run k8  --paramset STD100_MKNTRU_3 --batch 16384 --steps 1 --warmup 1 --synthetic-keys --no-also --check-oracle 4 --cpu-baseline-gates-per-thread 1
+  run k16 --paramset STD100_MKNTRU_4 --batch 16384 --steps 1 --warmup 1 --synthetic-keys --no-also --check-oracle 1 --cpu-baseline-gates-per-thread 1
+  ;;
 pair)   # paired inverse transforms (MKFHE_PAIR=0/1) in the 80- / 128-register builds of the sequential kernel
   q() { echo "== $*"; env "$@" python tests/dev_quick_bench.py --paramset $PS --batches $BT --check $CK --reps 3 2>&1 | grep -E "batch|MISMATCH|exact|Error|error" ; }
   PS=STD100_MKNTRU_3 BT=296,592 CK=2; q MKFHE_PAIR=0; q MKFHE_PAIR=1
