@@ -48,6 +48,14 @@ ntt2)   # full GPU tests + smoke, then the transform loaders incl. the two-polyn
   run ntt2048 --workload ntt --ntt-n 2048 --steps 20 --warmup 3 --ntt-variants tma,2,ldg
   run ntt1024 --workload ntt --ntt-n 1024 --steps 20 --warmup 3 --ntt-variants tma,2,ldg
   ;;
+final)  # what the driver runs at round end (tests, smoke, both bench arms at N = 1), after one more A/B
+  q() { echo "== $*"; env "$@" python tests/dev_quick_bench.py --paramset $PS --batches $BT --check $CK --reps 3 2>&1 | grep -E "batch|MISMATCH|exact|Error|error" ; }
+  PS=STD100_MKNTRU_LWE BT=592,4096 CK=1; q X=0; q MKFHE_FAST_ALIAS=1
+  (time python -m pytest tests -m gpu -x -q) > gpurun_out/${TAG}_tests.log 2>&1; tail -4 gpurun_out/${TAG}_tests.log
+  python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${TAG}_smoke.log 2>&1; tail -3 gpurun_out/${TAG}_smoke.log
+  run ref --impl reference --steps 3 --warmup 1
+  run bench --steps 20 --warmup 3
+  ;;
 sweep)  # configs[2]: party-count sweep at batch 16384 (synthetic keys), oracle sample 16/16/4/1, CPU leg = the C port on all cores
   q() { echo "== $*"; env "$@" python tests/dev_quick_bench.py --paramset $PS --batches $BT --check $CK --reps 3 2>&1 | grep -E "batch|MISMATCH|exact|Error|error" ; }
   PS=STD100_MKNTRU_LWE BT=4096 CK=1; q X=0; q MKFHE_MINB=3
