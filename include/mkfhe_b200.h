@@ -171,6 +171,28 @@ int mkfhe_eval_circuit_dev(mkfhe_ctx* ctx, uint32_t* d_wires, uint32_t* d_wires_
 int64_t mkfhe_circuit_levels(uint64_t n_wires, const uint32_t* in1, const uint32_t* in2, const uint32_t* out, uint64_t n_gates,
                              uint32_t* level_of_gate);
 
+/* mkfhe_eval_circuit_dev WITHOUT device allocation.  This entry point has no counterpart in the reference; it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments, same results, same stream ordering as mkfhe_eval_circuit_dev; the per-level scratch
+ * (level-sorted index arrays, gathered inputs, level outputs) lives in ONE file-scope device array of
+ * MKFHE_STATIC_SCRATCH_WORDS 32-bit words (8 MiB) that every GPU loading the library holds until the process exits, instead of
+ * the context's memory pool.  The call issues no cudaMalloc / cudaFree / pool allocation.
+ *   Limit: mkfhe_circuit_static_words(params, n_gates, widest_level) <= MKFHE_STATIC_SCRATCH_WORDS, i.e.
+ *          pad64(3 n_gates) + 3 pad64(widest k n) [+ 3 pad64(widest) for MKLWE] words (pad64 = round up to 64 words);
+ *          levels of up to 695 gates at boolean-mklwe size (k = 2, n = 500), 621 / 311 / 155 / 77 gates at boolean-mkntru size for
+ *          k = 2 / 4 / 8 / 16 (with 4 gates per widest-level gate in the netlist).  Larger circuits: MKFHE_EINVAL with the sizes in
+ *          mkfhe_last_error -- use mkfhe_eval_circuit_dev.  Needs the fused key-switch path (qKS < 2^16: every reference set).
+ *   Sharing: ALL contexts and calls on one GPU share the array and it keeps the previous call's contents (nothing in it has to
+ *          start at zero: every word a call reads was written by that call first).  Calls that overlap on the GPU -- two
+ *          contexts on different streams, or one context after mkfhe_ctx_set_stream without the wait it performs -- RACE on it;
+ *          calls on one stream are ordered and safe. */
+#define MKFHE_STATIC_SCRATCH_WORDS (2u << 20)
+int mkfhe_eval_circuit_dev_static(mkfhe_ctx* ctx, uint32_t* d_wires, uint32_t* d_wires_b, uint64_t n_wires, const uint32_t* in1,
+                                  const uint32_t* in2, const uint32_t* out, uint64_t n_gates, uint32_t* n_levels);
+/* words of the static array a circuit needs (no GPU needed) and the array's size */
+uint64_t mkfhe_circuit_static_words(const mkfhe_params* p, uint64_t n_gates, uint64_t widest_level);
+uint64_t mkfhe_static_scratch_words(void);
+
 /* MNTRUEncryptionScheme::Decrypt (mntru-pke.cpp:306-341) / MKLWEEncryptionScheme::Decrypt (mklwe-pke.cpp:66-97) for `batch`
  * ciphertexts: ct [batch][k][n] mod q, b [batch] (MKLWE; NULL for MNTRU), p = plaintext modulus (4 in both examples),
  * m [batch] receives the plaintexts.  Host pointers, synchronous; _dev: device pointers, asynchronous. */

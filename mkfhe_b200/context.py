@@ -270,6 +270,19 @@ class BinFHEContext:
                  "mkfhe_eval_circuit_dev")
         return int(lv.value)
 
+    def EvalCircuitDeviceStatic(self, wires, gates, b=None) -> int:
+        """EvalCircuitDevice without device allocation (mkfhe_eval_circuit_dev_static: the scratch of the level batches lives in
+        the library's file-scope device array; no counterpart in the reference).  Raises MkfheError (MKFHE_EINVAL) for a circuit
+        beyond the array's size; calls that overlap on one GPU race on the shared array."""
+        g = np.ascontiguousarray(gates, dtype=np.uint32).reshape(-1, 3)
+        i1, i2, o = (np.ascontiguousarray(g[:, j]) for j in range(3))
+        W = wires.numel() // (self.params.k * self.params.n)
+        lv = C.c_uint32(0)
+        dp = lambda t: None if t is None else C.c_void_p(t.data_ptr())
+        self._ck(self._L.mkfhe_eval_circuit_dev_static(self._h, dp(wires), dp(b), W, _ptr(i1)[0], _ptr(i2)[0], _ptr(o)[0], len(g),
+                                                       C.byref(lv)), "mkfhe_eval_circuit_dev_static")
+        return int(lv.value)
+
     # -- BinFHEContext::Decrypt (binfhecontext.h:318-338 -> mntru-pke.cpp:306-341 / mklwe-pke.cpp:66-97), batched
     def LoadSecretKey(self, sk):
         """sk: uint32 [k, n] -- MNTRUPrivateKey::GetF_col0() or MKLWEPrivateKey::GetElement() of the decrypting parties"""

@@ -11,6 +11,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <exception>
+#include <mutex>
 #include <new>
 #include <string>
 #include <vector>
@@ -822,6 +823,113 @@ int mkfhe_eval_circuit(mkfhe_ctx* ctx, uint32_t* wires, uint32_t* wires_b, uint6
     CU(cudaMemcpyAsync(wires, d_w, words * 4, cudaMemcpyDeviceToHost, ctx->stream));
     if (lwe) CU(cudaMemcpyAsync(wires_b, d_b, n_wires * 4, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
+    return MKFHE_OK;
+}
+
+// ---- circuits without device allocation (no counterpart in the reference) ----
+// The level batches of mkfhe_eval_circuit_dev (sorted index arrays, gathered inputs, level outputs) live in ONE file-scope
+// device array instead of the context's pool, for callers that may not allocate: CUDA graph capture, tight serving loops,
+// harnesses that forbid cudaMalloc.  Every GPU that loads the library holds the array (8 MiB) until the process exits.
+// g_static_scratch is a host-side stand-in in host code, not a device address: the kernels below are given the pointer
+// cudaGetSymbolAddress returns for the context's device (looked up once per device, with that device current).
+static __device__ __align__(256) uint32_t g_static_scratch[MKFHE_STATIC_SCRATCH_WORDS];
+
+static int static_scratch_ptr(mkfhe_ctx* ctx, uint32_t** out) {
+    constexpr int MAXDEV = 64;
+    static std::mutex mu;
+    static uint32_t* by_device[MAXDEV] = {};
+    if (ctx->device < 0 || ctx->device >= MAXDEV) return fail(ctx, MKFHE_EINVAL, "device ordinal %d out of range", ctx->device);
+    std::lock_guard<std::mutex> lk(mu);
+    if (!by_device[ctx->device]) {
+        void* p = nullptr;
+        CU(cudaSetDevice(ctx->device));
+        CU(cudaGetSymbolAddress(&p, g_static_scratch));
+        by_device[ctx->device] = static_cast<uint32_t*>(p);
+    }
+    *out = by_device[ctx->device];
+    return MKFHE_OK;
+}
+
+uint64_t mkfhe_static_scratch_words(void) { return MKFHE_STATIC_SCRATCH_WORDS; }
+
+uint64_t mkfhe_circuit_static_words(const mkfhe_params* p, uint64_t n_gates, uint64_t widest_level) {
+    if (!p) return 0;
+    auto pad = [](uint64_t w) { return (w + 63) & ~uint64_t(63); };  // every sub-buffer starts on a 256-byte boundary
+    const uint64_t kn = uint64_t(p->k) * p->n;
+    uint64_t w = pad(3 * n_gates) + 3 * pad(widest_level * kn);
+    if (p->scheme == MKFHE_SCHEME_MKLWE) w += 3 * pad(widest_level);
+    return w;
+}
+
+int mkfhe_eval_circuit_dev_static(mkfhe_ctx* ctx, uint32_t* d_wires, uint32_t* d_wires_b, uint64_t n_wires, const uint32_t* in1,
+                                  const uint32_t* in2, const uint32_t* out, uint64_t n_gates, uint32_t* n_levels) {
+    if (!ctx || !d_wires || ((!in1 || !in2 || !out) && n_gates)) return MKFHE_EINVAL;
+    const mkfhe_params& p = ctx->p;
+    const bool lwe = p.scheme == MKFHE_SCHEME_MKLWE;
+    if (lwe && !d_wires_b) return fail(ctx, MKFHE_EINVAL, "MKLWE circuits need wires_b");
+    if (!ctx->fuse_ks)
+        return fail(ctx, MKFHE_EINVAL, "mkfhe_eval_circuit_dev_static needs the fused key-switch path (qKS < 2^16); the unfused path "
+                                       "grows workspaces with cudaMalloc");
+    if (n_wires > 0xffffffffull || n_gates > 0x7fffffffull) return fail(ctx, MKFHE_EINVAL, "circuit too large");
+    std::vector<uint32_t> level;
+    const char* why = "";
+    const int64_t L = circuit_levelise(n_wires, in1, in2, out, n_gates, level, &why);
+    if (L < 0) return fail(ctx, MKFHE_EINVAL, "mkfhe_eval_circuit_dev_static: %s", why);
+    if (n_levels) *n_levels = uint32_t(L);
+    if (n_gates == 0) return MKFHE_OK;
+    std::vector<uint64_t> start(size_t(L) + 1, 0);
+    for (uint64_t g = 0; g < n_gates; ++g) start[level[g] + 1]++;
+    uint64_t widest = 0;
+    for (int64_t l = 0; l < L; ++l) {
+        widest = std::max(widest, start[l + 1]);
+        start[l + 1] += start[l];
+    }
+    const uint64_t need = mkfhe_circuit_static_words(&p, n_gates, widest);
+    if (need > MKFHE_STATIC_SCRATCH_WORDS)
+        return fail(ctx, MKFHE_EINVAL, "mkfhe_eval_circuit_dev_static: %llu gates with a widest level of %llu need %llu words of scratch, "
+                                       "the static array holds %llu (use mkfhe_eval_circuit_dev)",
+                    (unsigned long long)n_gates, (unsigned long long)widest, (unsigned long long)need,
+                    (unsigned long long)MKFHE_STATIC_SCRATCH_WORDS);
+    std::vector<uint32_t> idx(3 * n_gates);  // [in1 | in2 | out], each sorted by level (host memory only)
+    {
+        std::vector<uint64_t> at(start.begin(), start.end() - 1);
+        for (uint64_t g = 0; g < n_gates; ++g) {
+            const uint64_t pos = at[level[g]]++;
+            idx[pos] = in1[g];
+            idx[n_gates + pos] = in2[g];
+            idx[2 * n_gates + pos] = out[g];
+        }
+    }
+    CU(cudaSetDevice(ctx->device));
+    uint32_t* base = nullptr;
+    int rc = static_scratch_ptr(ctx, &base);
+    if (rc) return rc;
+    auto pad = [](uint64_t w) { return (w + 63) & ~uint64_t(63); };
+    const uint32_t kn = p.k * p.n;
+    // nothing in the array has to start at zero: the index block is overwritten by the copy below and every row a level reads
+    // from c1 / c2 / co (and b1 / b2 / bo) is written by that level's gather or gate kernel first
+    uint32_t* d_idx = base;
+    uint32_t* c1 = d_idx + pad(3 * n_gates);
+    uint32_t* c2 = c1 + pad(widest * kn);
+    uint32_t* co = c2 + pad(widest * kn);
+    uint32_t *b1 = nullptr, *b2 = nullptr, *bo = nullptr;
+    if (lwe) {
+        b1 = co + pad(widest * kn);
+        b2 = b1 + pad(widest);
+        bo = b2 + pad(widest);
+    }
+    CU(cudaMemcpyAsync(d_idx, idx.data(), idx.size() * 4, cudaMemcpyHostToDevice, ctx->stream));
+    for (int64_t l = 0; l < L; ++l) {
+        const uint64_t s = start[l], B = start[l + 1] - s;
+        circuit_gather<<<unsigned(B), 256, 0, ctx->stream>>>(d_wires, lwe ? d_wires_b : nullptr, d_idx + s, d_idx + n_gates + s, c1, c2, b1,
+                                                           b2, kn);
+        CU(cudaGetLastError());
+        rc = mkfhe_eval_nand_dev(ctx, c1, b1, c2, b2, co, bo, B);
+        if (rc) return rc;
+        circuit_scatter<<<unsigned(B), 256, 0, ctx->stream>>>(d_wires, lwe ? d_wires_b : nullptr, d_idx + 2 * n_gates + s, co, bo, kn);
+        CU(cudaGetLastError());
+        ctx->launches += 2;
+    }
     return MKFHE_OK;
 }
 

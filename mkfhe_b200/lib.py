@@ -25,7 +25,7 @@ SYMBOLS = [
     "mkfhe_load_bk", "mkfhe_load_pkey", "mkfhe_load_ksk_mntru", "mkfhe_load_ksk_mklwe", "mkfhe_load_ctnand",
     "mkfhe_key_image", "mkfhe_key_image_commit",
     "mkfhe_eval_acc", "mkfhe_eval_acc_dev", "mkfhe_eval_nand", "mkfhe_eval_nand_dev", "mkfhe_ntt", "mkfhe_ntt_dev",
-    "mkfhe_load_sk", "mkfhe_decrypt", "mkfhe_decrypt_dev", "mkfhe_eval_circuit", "mkfhe_eval_circuit_dev", "mkfhe_circuit_levels", "mkfhe_keygen_bk", "mkfhe_keygen_pkey", "mkfhe_keygen_ksk_mntru", "mkfhe_keygen_ksk_mklwe", "mkfhe_encrypt_mntru", "mkfhe_encrypt_mklwe", "mkfhe_keyfile_write", "mkfhe_keyfile_info", "mkfhe_keyfile_load", "mkfhe_ctfile_write", "mkfhe_ctfile_info", "mkfhe_ctfile_read",
+    "mkfhe_load_sk", "mkfhe_decrypt", "mkfhe_decrypt_dev", "mkfhe_eval_circuit", "mkfhe_eval_circuit_dev", "mkfhe_circuit_levels", "mkfhe_eval_circuit_dev_static", "mkfhe_circuit_static_words", "mkfhe_static_scratch_words", "mkfhe_keygen_bk", "mkfhe_keygen_pkey", "mkfhe_keygen_ksk_mntru", "mkfhe_keygen_ksk_mklwe", "mkfhe_encrypt_mntru", "mkfhe_encrypt_mklwe", "mkfhe_keyfile_write", "mkfhe_keyfile_info", "mkfhe_keyfile_load", "mkfhe_ctfile_write", "mkfhe_ctfile_info", "mkfhe_ctfile_read",
     "mkfhe_decompose", "mkfhe_last_gate_timing", "mkfhe_launch_count", "mkfhe_device_bytes", "mkfhe_version", "mkfhe_measure_int32_peak", "mkfhe_measure_butterfly_peak",
 ]
 
@@ -74,6 +74,11 @@ def load():
     L.mkfhe_eval_circuit_dev.argtypes = [vp, vp, vp, u64, vp, vp, vp, u64, vp]
     L.mkfhe_circuit_levels.argtypes = [u64, vp, vp, vp, u64, vp]
     L.mkfhe_circuit_levels.restype = C.c_int64
+    L.mkfhe_eval_circuit_dev_static.argtypes = [vp, vp, vp, u64, vp, vp, vp, u64, vp]
+    L.mkfhe_circuit_static_words.argtypes = [C.POINTER(Params), u64, u64]
+    L.mkfhe_circuit_static_words.restype = u64
+    L.mkfhe_static_scratch_words.argtypes = []
+    L.mkfhe_static_scratch_words.restype = u64
     L.mkfhe_decrypt.argtypes = [vp, vp, vp, u32, vp, u64]
     L.mkfhe_decrypt_dev.argtypes = [vp, vp, vp, u32, vp, u64]
     L.mkfhe_keygen_bk.argtypes = [vp, vp, vp, vp, vp, vp, vp, i32]

@@ -22,6 +22,11 @@ peaks() {
 run() { name=$1; shift; (time timeout 1500 python bench.py "$@") > gpurun_out/${TAG}_${name}.json 2> gpurun_out/${TAG}_${name}.err; \
         echo "== $name"; cut -c1-600 gpurun_out/${TAG}_${name}.json; tail -2 gpurun_out/${TAG}_${name}.err; }
 case $S in
+noalloc)  # the allocation-free circuit entry point: its test alone in a fresh process, then after the whole suite, then smoke
+  (time python -m pytest tests/test_zz_no_alloc.py -m gpu -x -q) > gpurun_out/${TAG}_noalloc_alone.log 2>&1; tail -4 gpurun_out/${TAG}_noalloc_alone.log
+  (time python -m pytest tests -m gpu -x -q) > gpurun_out/${TAG}_tests.log 2>&1; tail -4 gpurun_out/${TAG}_tests.log
+  python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${TAG}_smoke.log 2>&1; tail -3 gpurun_out/${TAG}_smoke.log
+  ;;
 check)  # full GPU test suite, smoke, default bench line, both transform loaders at N = 2048 / 1024
   (time python -m pytest tests -m gpu -x -q) > gpurun_out/${TAG}_tests.log 2>&1; tail -5 gpurun_out/${TAG}_tests.log
   python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${TAG}_smoke.log 2>&1; tail -2 gpurun_out/${TAG}_smoke.log
