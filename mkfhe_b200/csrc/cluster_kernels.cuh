@@ -1,0 +1,339 @@
+// cluster_kernels.cuh -- one gate on a thread-block CLUSTER of two SMs (sm_100a), for the batches that leave most of the GPU idle:
+// the single accumulator of the drop-in UniEncAccumulator::EvalAcc (mk-acc.h:67-71), one EvalBinGate, the narrow levels of a
+// circuit.
+//
+// Why: a gate's steps are sequential, and within a step the chain  party terms -> sumV -> sumV term  (mk-acc-xzw.cpp:240-289) is
+// what the clock sees.  On ONE SM (blind_rotate_grouped, two groups of 256 threads) a single boolean-mklwe gate keeps the fma-heavy
+// pipe about 55% busy -- both groups' transforms queue on the same four sub-partitions -- and takes 8.75 ms.  Here CTA r of the
+// cluster owns the parties p = r (mod 2): their accumulators live in ITS shared memory, its 8 warps have an SM's pipes to
+// themselves, and the only traffic between the SMs is the partial sum  sum_p <D_p, Pkey_p>  of the CTA that does not own the step's
+// key: 8 KiB per step, written straight into the key owner's shared memory (distributed shared memory, st.shared::cluster), followed
+// by one cluster barrier (barrier.cluster.arrive.release / wait.acquire).  The CTA that does not own the key never waits for the
+// other one's sumV term: after the barrier it transforms its last product back, updates its accumulator and starts the next step's
+// party terms, so the key owner's chain (its parties, then the sumV term) is the only critical path.
+//
+// Per step s = (u, i), CTA r, owner CTA o = u mod 2:
+//   for own parties p != u, then p = u (if r == o):  digits of (X^c - 1) a_p -> 2 forward NTTs -> X_p = <D_p, d>, V_r += <D_p, Pkey_p>
+//   r != o:  V_r -> Vs[s & 1] of CTA o (remote);  arrive;  a_p += INTT(X_p) for the last own party;  wait
+//   r == o:  arrive;  wait;  V = V_o + Vs[s & 1];  W = digits of INTT(V);  X_u += <NTT(W), f>;  a_u += INTT(X_u)
+// Vs is double-buffered by the parity of the step: CTA r's write of step s + 2 cannot pass the owner's read of step s, because r
+// must first pass the barrier of step s + 1, at which the owner arrives only after step s.
+// Same exact sums as the sequential kernel (fast_step), evaluated in a different order: results are bit-identical (the tests hold
+// this kernel to the oracle and to the compiled reference).
+#pragma once
+#include "fast_kernels.cuh"
+
+namespace mkfhe {
+
+constexpr uint32_t CL = 2;  // CTAs per cluster = SMs per gate
+
+__device__ __forceinline__ uint32_t cluster_rank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+// address of `p` (a shared-memory address of this CTA) in the shared memory of CTA `rank` of the cluster
+__device__ __forceinline__ uint32_t cluster_map(const void* p, uint32_t rank) {
+    uint32_t local = static_cast<uint32_t>(__cvta_generic_to_shared(p)), remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(rank));
+    return remote;
+}
+__device__ __forceinline__ void cluster_st4(uint32_t addr, uint4 v) {
+    asm volatile("st.shared::cluster.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ void cluster_st1(uint32_t addr, uint32_t v) {
+    asm volatile("st.shared::cluster.u32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
+}
+
+// parties of CTA r: p = r, r + CL, ...; party p lives at local row p / CL
+__host__ __device__ inline uint32_t cluster_rows(uint32_t k) { return (k + CL - 1) / CL; }
+// Shared memory of one CTA: a[rows][N] | E1[2][FNP] | E2[FNP] | Vs[2][N] | Ms[N] (XZW) | xchg[4] | crot[k*n] (u16)
+__host__ __device__ inline size_t cluster_smem_bytes(uint32_t k, uint32_t n, bool xzw) {
+    return (size_t(cluster_rows(k)) * FN + 3 * FNP + 2 * FN + (xzw ? FN : 0) + 4) * 4 + ((size_t(k) * n * 2 + 15) & ~size_t(15));
+}
+
+// One step of EvalAcc on the cluster (see the header comment).  `a`: this CTA's rows; `par`: parity of the count of executed steps
+// (the same in both CTAs: they skip the same zero rotations).  Ends with a block barrier; every thread executes exactly one
+// cluster arrive and one cluster wait.  Exchange-buffer discipline as in fast_step: forward transforms through E1, inverse ones
+// through E2, and between two uses of either buffer lies the block barrier inside a transform on the other.
+template <bool XZW, bool FIRST>
+__device__ __forceinline__ void cluster_step(const DevCtx& P, const FastTables& T, uint32_t* a, uint32_t* E1, uint32_t* E2, uint32_t* Vs,
+                                             uint32_t* Ms, uint32_t s, uint32_t c, uint32_t par, uint32_t tid, uint32_t rank) {
+    constexpr uint32_t N = FN, M = 2 * FN;
+    const uint32_t Q = P.mod.Q, k = P.k, n = P.n, g = P.gbits;
+    const uint32_t u = FIRST ? 0u : s / n, i = FIRST ? 0u : s - u * n;
+    const bool owner = (u % CL) == rank;
+    const uint32_t ju = u / CL;                          // local row of the key owner's accumulator (in the owner CTA)
+    const uint32_t rows = (k - rank + CL - 1) / CL;      // own parties
+    const uint32_t cneg = (M - c) & (M - 1);
+    const size_t per = size_t(2) * 2 * N;
+    const uint32_t* ev1 = P.bk + (size_t(u * P.S) * n + i) * per + 4 * tid;
+    const uint32_t* ev2 = XZW ? ev1 + size_t(n) * per : ev1;
+    const uint32_t* evs = P.bk + size_t(k) * P.S * n * per + 4 * tid;
+    const uint32_t brv8 = __brev(tid) >> 24;
+    const uint32_t e0n = cneg * (2 * brv8 + 1), e0p = c * (2 * brv8 + 1);
+    if (T.prefetch && rank == 0) prefetch_step_keys<XZW>(P, s + 1, tid);
+    uint32_t* Mt = Ms + 4 * tid;
+    if (XZW && !FIRST) {  // Q - X^-c at this thread's slots, once per step (see fast_step)
+#pragma unroll
+        for (int ch = 0; ch < 2; ++ch) {
+            uint32_t mq[4];
+            monomial4(P.psipow, e0n, cneg, ch, mq);
+            *reinterpret_cast<uint4*>(Mt + (N / 2) * ch) = make_uint4(Q - mq[0], Q - mq[1], Q - mq[2], Q - mq[3]);
+        }
+    }
+    uint32_t* Vp = Vs + par * N + 8 * tid;  // this thread's 8 slots of the step's partial-sum buffer
+    uint32_t keep[8];                       // V_r = sum over own parties of <D_p, Pkey_p>, < 4Q
+    uint32_t y[8];                          // the last own party's <D_p, d>, evaluation domain, < 3Q
+    uint32_t* alast = a;
+#pragma unroll 1
+    for (uint32_t j = 0; j < rows; ++j) {
+        // own parties in increasing order, the key owner's (if it is ours) last: its f-term needs the complete V
+        const uint32_t row = owner ? (j + 1 < rows ? (j < ju ? j : j + 1) : ju) : j;
+        const uint32_t p = rank + CL * row;
+        uint32_t* ap = a + row * N;
+        uint32_t D[2][8];
+#pragma unroll
+        for (int r = 0; r < 8; ++r) decompose2(FIRST ? ap[tid + 256 * r] : rot_sub(ap, c, tid + 256 * r, N, Q), Q, g, D[0][r], D[1][r]);
+        fwd_ntt_regs<2>(D, E1, T, Q, tid);
+        const uint32_t* pk = P.pkey + size_t(p) * 2 * N + 4 * tid;
+#pragma unroll
+        for (int ch = 0; ch < 2; ++ch) {
+            uint32_t x4[4];
+            key_mac4<XZW, FIRST>(P, ev1, ev2, evs, c, cneg, e0p, e0n, ch, D, x4, (XZW && !FIRST) ? Mt : nullptr);  // "d" column
+            const uint4 q0 = ldg4(pk + (N / 2) * ch), q1 = ldg4(pk + N + (N / 2) * ch);
+            const uint32_t pp0[4] = {q0.x, q0.y, q0.z, q0.w}, pp1[4] = {q1.x, q1.y, q1.z, q1.w};
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int sl = 4 * ch + q;
+                const uint32_t v = mac2(D[0][sl], pp0[q], D[1][sl], pp1[q], P.mod);  // < 3Q
+                uint32_t vs = (j == 0 ? 0u : keep[sl]) + v;                          // < 7Q
+                keep[sl] = min(vs, vs - 4 * Q);                                      // < 4Q
+                y[sl] = x4[q];
+            }
+        }
+        alast = ap;
+        if (j + 1 < rows) {  // not the last own party: back to coefficients now
+            inv_ntt_regs(y, E2, T, Q, tid);
+#pragma unroll
+            for (int r = 0; r < 8; ++r) {
+                if (FIRST) {
+                    ap[tid + 256 * r] = fold1(y[r], Q);
+                } else {
+                    uint32_t v = ap[tid + 256 * r] + y[r];  // < 3Q
+                    v = min(v, v - 2 * Q);
+                    ap[tid + 256 * r] = min(v, v - Q);
+                }
+            }
+        }
+    }
+    if (!owner) {
+        // V_r into the key owner's shared memory (the thread with the same tid there picks these 8 slots up), then the barrier
+        const uint32_t remote = cluster_map(Vp, u % CL);
+        cluster_st4(remote, make_uint4(keep[0], keep[1], keep[2], keep[3]));
+        cluster_st4(remote + 16, make_uint4(keep[4], keep[5], keep[6], keep[7]));
+        cluster_arrive();
+    } else {
+        cluster_arrive();
+        cluster_wait();
+        // ---- the sumV term (mk-acc-xzw.cpp:273-289): V = V_o + V_r, W = digits of INTT(V), X_u += <NTT(W), f> ----
+        uint32_t xu[8], D[2][8];
+        const uint4 r0 = *reinterpret_cast<const uint4*>(Vp), r1 = *reinterpret_cast<const uint4*>(Vp + 4);
+        const uint32_t rv[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+#pragma unroll
+        for (int sl = 0; sl < 8; ++sl) {
+            xu[sl] = y[sl];
+            const uint32_t v = keep[sl] + rv[sl];  // < 8Q
+            y[sl] = min(v, v - 4 * Q);             // < 4Q
+        }
+        inv_ntt_regs(y, E2, T, Q, tid);
+#pragma unroll
+        for (int r = 0; r < 8; ++r) decompose2(fold1(y[r], Q), Q, g, D[0][r], D[1][r]);
+        fwd_ntt_regs<2>(D, E1, T, Q, tid);
+#pragma unroll
+        for (int ch = 0; ch < 2; ++ch) {
+            uint32_t x4[4];
+            key_mac4<XZW, FIRST>(P, ev1 + N, ev2 + N, evs + N, c, cneg, e0p, e0n, ch, D, x4, (XZW && !FIRST) ? Mt : nullptr);  // "f" column
+#pragma unroll
+            for (int q = 0; q < 4; ++q) y[4 * ch + q] = xu[4 * ch + q] + x4[q];  // < 6Q
+        }
+    }
+    // the last own party's product (the owner's now includes the sumV term) back to coefficients
+    inv_ntt_regs(y, E2, T, Q, tid);
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        if (FIRST) {
+            alast[tid + 256 * r] = fold1(y[r], Q);
+        } else {
+            uint32_t v = alast[tid + 256 * r] + y[r];  // < 3Q
+            v = min(v, v - 2 * Q);
+            alast[tid + 256 * r] = min(v, v - Q);
+        }
+    }
+    if (!owner) cluster_wait();  // (free by now: the owner arrived before its sumV term)
+    __syncthreads();             // a[] complete before the next step's shifted reads
+}
+
+// Key switch of this CTA's parties (keyswitch_epilogue of generic_kernels.cuh restricted to the rows p = rank (mod CL)); the two
+// CTAs switch their parties side by side.  MKLWE: b needs the sum of the B column over ALL parties (mklwe-pke.cpp:277-280): CTA 1
+// leaves its share in CTA 0's xchg word before the closing cluster barrier of the kernel, CTA 0 finishes b after it.
+__device__ __noinline__ uint32_t cluster_keyswitch(const DevCtx& P, const GateIO& io, uint32_t g, const uint32_t* a, uint32_t* scratch,
+                                                   uint32_t rank) {
+    const uint32_t N = P.N, Q = P.mod.Q, k = P.k, n = P.n;
+    const uint32_t tid = threadIdx.x, T = blockDim.x;
+    uint32_t* ms = scratch;
+    uint32_t* sums = scratch + N;
+    uint32_t bsum = 0;  // thread 0: this CTA's share of the B column
+    for (uint32_t u = rank, row = 0; u < k; u += CL, ++row) {
+        const uint32_t* au = a + row * N;
+        for (uint32_t e = tid; e < N; e += T) {  // Transpose + INTT = [a0, -a_{N-1}, ..., -a_1]; RoundqQ (mntru-pke.cpp:359-374)
+            const uint32_t v = e == 0 ? au[0] : au[N - e];
+            const uint32_t ext = (e == 0 || v == 0) ? v : Q - v;
+            ms[e] = round_qQ(ext, P.qKS, Q);
+        }
+        for (uint32_t x = tid; x < P.npad; x += T) sums[x] = 0;
+        __syncthreads();
+        switch (P.dKS) {
+            case 3: keyswitch_party<3>(P, u, ms, sums); break;
+            case 4: keyswitch_party<4>(P, u, ms, sums); break;
+            default: keyswitch_party<0>(P, u, ms, sums); break;
+        }
+        __syncthreads();
+        uint32_t* o = io.out + (size_t(g) * k + u) * n;
+        for (uint32_t x = tid; x < n; x += T) {
+            const uint32_t sv = sums[x] % P.qKS;
+            o[x] = P.scheme == 1 ? (sv == 0 ? 0u : P.qKS - sv) : sv;
+        }
+        if (P.scheme == 1 && tid == 0) bsum = (bsum + sums[n] % P.qKS) % P.qKS;
+        __syncthreads();
+    }
+    return bsum;
+}
+
+template <bool GATE, bool XZW>
+__global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(FT, 1) blind_rotate_cluster(const DevCtx P, const FastTables T, const GateIO io) {
+    extern __shared__ __align__(16) uint32_t sm[];
+    const uint32_t k = P.k, n = P.n, tid = threadIdx.x, rank = cluster_rank(), g = blockIdx.x / CL;
+    constexpr uint32_t N = FN, M = 2 * FN;
+    const uint32_t rows = (k - rank + CL - 1) / CL;
+    uint32_t* a = sm;
+    uint32_t* E1 = a + cluster_rows(k) * N;
+    uint32_t* E2 = E1 + 2 * FNP;
+    uint32_t* Vs = E2 + FNP;
+    uint32_t* Ms = Vs + 2 * N;
+    uint32_t* xchg = XZW ? Ms + N : Ms;
+    uint16_t* crot = reinterpret_cast<uint16_t*>(xchg + 4);
+    const uint32_t Q = P.mod.Q;
+
+    // ---- prologue: rotation amounts (both CTAs keep all of them) and this CTA's rows of the initial accumulator ----
+    for (uint32_t s = tid; s < k * n; s += FT) crot[s] = static_cast<uint16_t>(rotation_amount<GATE>(P, io, g, s));
+    if (GATE) {
+        // initial accumulator in COEFFICIENT form: party 0 only (binfhe-base-scheme.cpp:1018-1055 MKLWE, :1086-1110 MNTRU), as
+        // rotate_prologue builds it
+        uint32_t b_hat = 0;
+        if (P.scheme == 1) {
+            const uint32_t bt = submod((5u * P.q / 8u) % P.q, addmod(io.b1[g], io.b2[g], P.q), P.q);
+            b_hat = round_qQ(bt, M, P.q);
+        }
+        const uint32_t Q2p = Q / 8 + 1, Q2pNeg = Q - Q2p;
+        for (uint32_t e = tid; e < rows * N; e += FT) {
+            uint32_t v = 0;
+            if (rank == 0 && e < N) {
+                if (P.scheme == 0) {
+                    v = e < N / 2 ? Q2pNeg : Q2p;
+                } else {
+                    const uint32_t j = (e + M - b_hat) & (N - 1);
+                    const uint32_t Rx = j < N / 2 ? Q2p : Q2pNeg;
+                    const uint32_t index = b_hat + j;
+                    v = (index >= N && index < M) ? Q - Rx : Rx;
+                }
+            }
+            a[e] = v;
+        }
+        __syncthreads();
+    } else {
+        for (uint32_t row = 0; row < rows; ++row) {
+            const uint32_t* ai = io.acc_in + (size_t(g) * k + rank + CL * row) * N;
+            for (uint32_t e = tid; e < N; e += FT) a[row * N + e] = ai[e];
+        }
+        __syncthreads();
+        ntt_inv_smem(a, rows, P);
+        for (uint32_t e = tid; e < rows * N; e += FT) a[e] = montmul(a[e], P.ninv_mont, P.mod);
+        __syncthreads();
+    }
+    // both CTAs are running (their shared memory may be written from now on)
+    cluster_arrive();
+    cluster_wait();
+
+    uint32_t par = 0;
+    cluster_step<XZW, true>(P, T, a, E1, E2, Vs, Ms, 0, crot[0], par, tid, rank);
+    for (uint32_t s = 1; s < k * n; ++s) {
+        const uint32_t c = crot[s];
+        if (c == 0) continue;  // X^0 - 1 = 0: the step leaves acc unchanged (the same decision in both CTAs)
+        par ^= 1u;
+        cluster_step<XZW, false>(P, T, a, E1, E2, Vs, Ms, s, c, par, tid, rank);
+    }
+
+    // ---- epilogue: this CTA's rows -> outputs ----
+    uint32_t bsum = 0;
+    if (GATE && P.ksk16 != nullptr) {
+        bsum = cluster_keyswitch(P, io, g, a, E1, rank);
+        if (P.scheme == 1 && rank != 0 && tid == 0) cluster_st1(cluster_map(xchg, 0), bsum);
+    } else if (GATE) {
+        for (uint32_t row = 0; row < rows; ++row) {
+            uint32_t* out = io.ms_out + (size_t(g) * k + rank + CL * row) * N;
+            const uint32_t* au = a + row * N;
+            for (uint32_t e = tid; e < N; e += FT) {
+                const uint32_t v = e == 0 ? au[0] : au[N - e];
+                const uint32_t ext = (e == 0 || v == 0) ? v : Q - v;
+                out[e] = round_qQ(ext, P.qKS, Q);
+            }
+        }
+    } else {
+        ntt_fwd_smem(a, rows, P);
+        for (uint32_t row = 0; row < rows; ++row) {
+            uint32_t* out = io.acc_out + (size_t(g) * k + rank + CL * row) * N;
+            for (uint32_t e = tid; e < N; e += FT) out[e] = a[row * N + e];
+        }
+    }
+    // closing barrier: CTA 1's share of b has landed, and no CTA exits while its shared memory may still be written
+    cluster_arrive();
+    cluster_wait();
+    if (GATE && P.ksk16 != nullptr && P.scheme == 1 && rank == 0 && tid == 0) {
+        const uint32_t all = (bsum + xchg[0]) % P.qKS;  // b = RoundqQ(Q/8 + 1) - sum B (binfhe-base-scheme.cpp:450-458)
+        io.bout[g] = submod(round_qQ((Q >> 3) + 1, P.qKS, Q), all, P.qKS);
+    }
+}
+
+// ---- host side ----
+inline bool cluster_supported(const DevCtx& d) {
+    return fast_supported(d) && d.k >= CL && cluster_smem_bytes(d.k, d.n, d.variant == 0) <= 227 * 1024;
+}
+// Batches that leave at least half of the SMs idle get two SMs per gate.  MKFHE_CLUSTER=0/1 forces the choice for A/B runs.
+inline bool cluster_wanted(const DevCtx& d, uint32_t batch, int sms) {
+    if (!cluster_supported(d)) return false;
+    if (const char* e = getenv("MKFHE_CLUSTER")) return e[0] == '1';
+    return uint64_t(batch) * CL <= uint64_t(sms);
+}
+inline cudaError_t cluster_blind_rotate(FastState& F, const DevCtx& d, bool gate, const GateIO& io, uint32_t batch, cudaStream_t st,
+                                        uint64_t* launches) {
+    const bool xzw = d.variant == 0;
+    F.T.prefetch = d.k <= 8 ? 1u : 0u;
+    if (const char* pf = getenv("MKFHE_PREFETCH")) F.T.prefetch = pf[0] == '1' ? 1u : 0u;
+    const size_t smem = cluster_smem_bytes(d.k, d.n, xzw);
+    auto launch = [&](auto kern) -> cudaError_t {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+        if (e != cudaSuccess) return e;
+        kern<<<batch * CL, FT, smem, st>>>(d, F.T, io);
+        return cudaSuccess;
+    };
+    const cudaError_t e = gate ? (xzw ? launch(blind_rotate_cluster<true, true>) : launch(blind_rotate_cluster<true, false>))
+                               : (xzw ? launch(blind_rotate_cluster<false, true>) : launch(blind_rotate_cluster<false, false>));
+    if (e != cudaSuccess) return e;
+    ++*launches;
+    return cudaGetLastError();
+}
+
+}  // namespace mkfhe

@@ -704,6 +704,44 @@ __global__ void __launch_bounds__(FT, MINB) blind_rotate_fast(const DevCtx P, co
     rotate_epilogue<GATE>(P, io, blockIdx.x, a, E1);
 }
 
+// ---- accumulators in global memory (L2) for large party counts ---------------------------------------------------------------
+// From k = 8 on the accumulator a[k][N] (8 KiB per party) decides how many gates share an SM: 2 at k = 8, 1 at k = 16, and an SM
+// with 8-16 warps is latency-bound (stall `wait`, fma-heavy pipe 57-61% busy against 71% at k = 2 with 32 warps;
+// profiles/r2_s1_k8_296.txt, r2_s11_k16_148.txt).  Here the accumulator of a gate lives in a per-CTA slice of a global workspace
+// instead: only the resident CTAs' slices are live (148 x MINB x k x 8 KiB <= 76 MiB at k = 16, inside the 126 MB L2), shared memory
+// holds the exchange buffers and rotation amounts alone, and MINB = 4 gates (32 warps) share an SM at every party count.  The step
+// function is the same code: `a` is a generic pointer, the accesses (coalesced 4-byte rows, one wavefront each as in shared memory)
+// become LDG / STG served by L2, and the block barriers that ordered them in shared memory order them in global memory as well
+// (all accesses to a slice come from the one CTA that owns it).  The CTA is persistent: gate g = blockIdx.x, + gridDim.x, ...
+// Shared memory: E1[2][FNP] | E2[FNP] | Ms[N] (XZW) | crot[k*n] (u16).
+// MEASURED (see fast_ag_wanted): bit-exact, and not faster except at k = 16 boolean-mklwe (+2%) -- kept as a selectable experiment.
+__host__ __device__ inline size_t fast_ag_smem_bytes(uint32_t k, uint32_t n, bool xzw) {
+    return (size_t(3) * FNP + (xzw ? FN : 0)) * 4 + ((size_t(k) * n * 2 + 15) & ~size_t(15));
+}
+template <bool GATE, bool XZW, int MINB>
+__global__ void __launch_bounds__(FT, MINB) blind_rotate_fast_ag(const DevCtx P, const FastTables T, const GateIO io, uint32_t* accws,
+                                                                 uint32_t batch) {
+    extern __shared__ __align__(16) uint32_t sm[];
+    const uint32_t k = P.k, n = P.n, tid = threadIdx.x;
+    constexpr uint32_t N = FN;
+    uint32_t* E1 = sm;
+    uint32_t* E2 = E1 + 2 * FNP;
+    uint32_t* Ms = E2 + FNP;
+    uint16_t* crot = reinterpret_cast<uint16_t*>(XZW ? Ms + N : Ms);
+    uint32_t* a = accws + size_t(blockIdx.x) * k * N;
+    for (uint32_t g = blockIdx.x; g < batch; g += gridDim.x) {
+        rotate_prologue<GATE>(P, io, g, a, crot);
+        fast_step<XZW, true, false, false, false>(P, T, a, E1, E2, Ms, 0, crot[0], tid);
+        for (uint32_t s = 1; s < k * n; ++s) {
+            const uint32_t c = crot[s];
+            if (c == 0) continue;
+            fast_step<XZW, false, false, false, false>(P, T, a, E1, E2, Ms, s, c, tid);
+        }
+        rotate_epilogue<GATE>(P, io, g, a, E1);
+        __syncthreads();  // the next gate's prologue rewrites crot and a
+    }
+}
+
 // ---- party-parallel variant for large party counts ----------------------------------------------------------------------
 // At k >= 8 one gate's accumulator takes 64-128 KiB of shared memory, so only 2 (k = 8) or 1 (k = 16) gates fit an SM and a
 // 256-thread CTA per gate leaves the SM with 16 or 8 warps.  Here one CTA of G x 256 threads owns one gate and the G groups
@@ -1406,8 +1444,21 @@ struct FastState {
     uint4* d_tw16{nullptr};
     uint2 one2{};
     int sms{148};
+    uint32_t* accws{nullptr};  // blind_rotate_fast_ag: [sms * 4][k][N] accumulator slices, allocated by fast_init when MKFHE_AG=1
     bool half{false};  // tables for N = 1024 (two polynomials per 2048-word pass): only the batched transform uses them
 };
+
+// accumulators in global memory (blind_rotate_fast_ag): an experiment, selected with MKFHE_AG=1 at context creation (the
+// workspace is allocated then) -- measured on B200 (profiles/r2_s18_ag.txt, gates/s, shared-memory kernels vs this one):
+//   k = 16  boolean-mklwe 436 vs 446 (+2%)   boolean-mkntru 343 vs 329 (4 per SM, 64 registers) / 303 (3 per SM, 80)
+//   k = 8   boolean-mklwe 1740 vs 1695       boolean-mkntru 1368 vs 1248
+//   k = 4   boolean-mklwe 6685 vs 6120       boolean-mkntru 4979 vs 4286         k = 2 boolean-mklwe 22.09 k vs 20.46 k
+// Four times the warps at k = 16 buy back what the L2 round trips of the accumulator rows (and the 64-bit addresses: 112-212 B of
+// spills in the step loop) cost, no more; at equal occupancy (k = 2) the global accumulator costs 8%.  Off by default.
+inline bool fast_ag_wanted(const DevCtx&) {
+    const char* e = getenv("MKFHE_AG");
+    return e != nullptr && e[0] == '1';
+}
 
 inline bool fast_supported(const DevCtx& d) {
     return d.N == FN && d.ell == 2 && d.mod.Q < (1u << 27) && d.gbits >= 2 && d.gbits <= 16 &&
@@ -1504,9 +1555,15 @@ inline cudaError_t fast_init(FastState& F, const DevCtx& d, uint32_t psi, cudaSt
     int dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&F.sms, cudaDevAttrMultiProcessorCount, dev);
+    if (!half && fast_ag_wanted(d)) {  // at set-up, so that the gate calls never allocate
+        const size_t bytes = size_t(F.sms) * 4 * d.k * FN * sizeof(uint32_t);
+        if ((e = cudaMalloc(reinterpret_cast<void**>(&F.accws), bytes)) != cudaSuccess) return e;
+        *dev_bytes += bytes;
+    }
     return cudaSuccess;
 }
 inline void fast_destroy(FastState& F) {
+    if (F.accws) cudaFree(F.accws);
     for (uint2* p : {F.d_tw2, F.d_itw2, F.d_scale2})
         if (p) cudaFree(p);
     if (F.d_tw4) cudaFree(F.d_tw4);
@@ -1573,6 +1630,31 @@ inline uint32_t fast_groups(const DevCtx& d, uint32_t batch, int sms) {
 inline cudaError_t fast_blind_rotate(FastState& F, const DevCtx& d, bool gate, const GateIO& io, uint32_t batch, cudaStream_t st,
                                      uint64_t* launches) {
     const bool xzw = d.variant == 0;
+    // large party counts, more gates than SMs: the accumulators move to L2 and four (XZW: three, as at k = 2) gates share an SM
+    if (F.accws != nullptr && fast_ag_wanted(d) && batch > uint32_t(F.sms)) {
+        F.T.prefetch = 0u;
+        F.T.pair = 0u;
+        int minb = xzw ? 3 : 4;
+        if (const char* ev = getenv("MKFHE_MINB")) minb = std::min(4, std::max(3, atoi(ev)));
+        const size_t smem = fast_ag_smem_bytes(d.k, d.n, xzw);
+        const uint32_t grid = std::min<uint32_t>(batch, uint32_t(F.sms) * uint32_t(minb));
+        auto launch = [&](auto kern) -> cudaError_t {
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+            if (e != cudaSuccess) return e;
+            kern<<<grid, FT, smem, st>>>(d, F.T, io, F.accws, batch);
+            return cudaSuccess;
+        };
+        cudaError_t e;
+        if (minb >= 4)
+            e = gate ? (xzw ? launch(blind_rotate_fast_ag<true, true, 4>) : launch(blind_rotate_fast_ag<true, false, 4>))
+                     : (xzw ? launch(blind_rotate_fast_ag<false, true, 4>) : launch(blind_rotate_fast_ag<false, false, 4>));
+        else
+            e = gate ? (xzw ? launch(blind_rotate_fast_ag<true, true, 3>) : launch(blind_rotate_fast_ag<true, false, 3>))
+                     : (xzw ? launch(blind_rotate_fast_ag<false, true, 3>) : launch(blind_rotate_fast_ag<false, false, 3>));
+        if (e != cudaSuccess) return e;
+        ++*launches;
+        return cudaGetLastError();
+    }
     const uint32_t G = fast_groups(d, batch, F.sms);
     F.T.stagger_ns = getenv("MKFHE_STAGGER_NS") ? uint32_t(atoi(getenv("MKFHE_STAGGER_NS"))) : 0u;
     // key prefetch: on in latency mode (at most one gate per SM, k <= 8), where the tile comes from HBM and nothing hides the

@@ -18,6 +18,7 @@
 
 #include "../../include/mkfhe_b200.h"
 #include "fast_kernels.cuh"
+#include "cluster_kernels.cuh"
 #include "generic_kernels.cuh"
 #include "keyfile.h"
 
@@ -598,6 +599,11 @@ static int launch_rotate(mkfhe_ctx* ctx, bool gate, const GateIO& io, uint64_t b
     if (!ctx->bk || !ctx->pkey) return fail(ctx, MKFHE_ENOKEY, "bootstrapping key / Pkey not loaded");
     if (batch == 0) return MKFHE_OK;
     if (batch > 0x7fffffffull) return fail(ctx, MKFHE_EINVAL, "batch too large");
+    if (ctx->use_fast && cluster_wanted(ctx->d, uint32_t(batch), ctx->fast.sms)) {  // few gates: two SMs per gate
+        cudaError_t e = cluster_blind_rotate(ctx->fast, ctx->d, gate, io, uint32_t(batch), ctx->stream, &ctx->launches);
+        if (e != cudaSuccess) return fail(ctx, MKFHE_ECUDA, "cluster_blind_rotate: %s", cudaGetErrorString(e));
+        return MKFHE_OK;
+    }
     if (ctx->use_fast) {
         cudaError_t e = fast_blind_rotate(ctx->fast, ctx->d, gate, io, uint32_t(batch), ctx->stream, &ctx->launches);
         if (e != cudaSuccess) return fail(ctx, MKFHE_ECUDA, "fast_blind_rotate: %s", cudaGetErrorString(e));

@@ -36,6 +36,9 @@ CASES = [  # paramset, environment overrides, gates in the batch, gates re-compu
     ("STD100_MKNTRU_3", {"MKFHE_GROUPS": "1"}, 5, 4),
     ("STD100_MKNTRU_3", {}, 5, 4),
     ("STD100_MKNTRU_4", {}, 2, 1),
+    # accumulators in global memory (blind_rotate_fast_ag, an experiment behind MKFHE_AG=1; batches above the SM count only)
+    ("STD100_MKNTRU_LWE", {"MKFHE_AG": "1"}, 150, 2),
+    ("STD100_MKNTRU_2", {"MKFHE_AG": "1", "MKFHE_MINB": "4"}, 150, 2),
     ("STD100_MKNTRU_4", {"MKFHE_GROUPS": "1"}, 2, 1),
 ]
 

@@ -22,6 +22,25 @@ peaks() {
 run() { name=$1; shift; (time timeout 1500 python bench.py "$@") > gpurun_out/${TAG}_${name}.json 2> gpurun_out/${TAG}_${name}.err; \
         echo "== $name"; cut -c1-600 gpurun_out/${TAG}_${name}.json; tail -2 gpurun_out/${TAG}_${name}.err; }
 case $S in
+cl)     # two SMs per gate (blind_rotate_cluster) against the party-parallel kernel on one SM, small batches
+  q() { echo "== $*"; env "$@" timeout 300 python tests/dev_quick_bench.py --paramset $PS --batches $BT --check $CK --reps 3 2>&1 | grep -E "batch|MISMATCH|exact|Error|error|rror" ; }
+  PS=STD100_MKNTRU_LWE BT=1,16,74 CK=2; q MKFHE_CLUSTER=0; q MKFHE_CLUSTER=1
+  PS=STD100_MKNTRU BT=1,16,74 CK=2; q MKFHE_CLUSTER=0; q MKFHE_CLUSTER=1
+  PS=STD100_MKNTRU_2 BT=1,74 CK=2; q MKFHE_CLUSTER=0; q MKFHE_CLUSTER=1
+  PS=STD100_MKNTRU_LWE_2 BT=1,74 CK=2; q MKFHE_CLUSTER=0; q MKFHE_CLUSTER=1
+  PS=STD100_MKNTRU_3 BT=74 CK=1; q MKFHE_CLUSTER=0; q MKFHE_CLUSTER=1
+  PS=STD100_MKNTRU_4 BT=74 CK=1; q MKFHE_CLUSTER=0; q MKFHE_CLUSTER=1
+  ;;
+ag)     # accumulators in global memory (blind_rotate_fast_ag) against the shared-memory kernels, k = 4 / 8 / 16, both flavours
+  q() { echo "== $*"; env "$@" python tests/dev_quick_bench.py --paramset $PS --batches $BT --check $CK --reps 2 2>&1 | grep -E "batch|MISMATCH|exact|Error|error" ; }
+  PS=STD100_MKNTRU_4 BT=592,1184 CK=1; q MKFHE_AG=0; q MKFHE_AG=1; q MKFHE_AG=1 MKFHE_MINB=4
+  PS=STD100_MKNTRU_LWE_4 BT=592,1184 CK=1; q MKFHE_AG=0; q MKFHE_AG=1; q MKFHE_AG=1 MKFHE_MINB=3
+  PS=STD100_MKNTRU_3 BT=592,1184 CK=1; q MKFHE_AG=0; q MKFHE_AG=1; q MKFHE_AG=1 MKFHE_MINB=4
+  PS=STD100_MKNTRU_LWE_3 BT=592,1184 CK=1; q MKFHE_AG=0; q MKFHE_AG=1
+  PS=STD100_MKNTRU_2 BT=888,1776 CK=1; q MKFHE_AG=0; q MKFHE_AG=1
+  PS=STD100_MKNTRU_LWE_2 BT=888,1776 CK=1; q MKFHE_AG=0; q MKFHE_AG=1
+  PS=STD100_MKNTRU_LWE BT=1184 CK=1; q MKFHE_AG=0; q MKFHE_AG=1
+  ;;
 noalloc)  # the allocation-free circuit entry point: its test alone in a fresh process, then after the whole suite, then smoke
   (time python -m pytest tests/test_zz_no_alloc.py -m gpu -x -q) > gpurun_out/${TAG}_noalloc_alone.log 2>&1; tail -4 gpurun_out/${TAG}_noalloc_alone.log
   (time python -m pytest tests -m gpu -x -q) > gpurun_out/${TAG}_tests.log 2>&1; tail -4 gpurun_out/${TAG}_tests.log
