@@ -581,6 +581,24 @@ def measure_gate_batch(env, paramset, B, steps, warmup, check_oracle, cpu_gates_
                 ms = sorted(ref.time_gate(5))
                 res["cpu_baseline"]["single_thread_ms"] = ms[len(ms) // 2]
                 res["cpu_baseline"]["single_thread_sample"] = "median of 5 single EvalBinGate(NAND) calls, steady_clock, 1 thread"
+    if rank == 0:
+        # BASELINE.json configs[0] / the reference examples' own measurement: ONE gate per call (the drop-in accumulator's case).
+        # Device-resident kernel time and the host-buffer C-ABI call, median of 5 after 2 warm-up calls; small batches run on a
+        # thread-block cluster of `sms_per_gate` SMs (mkfhe_b200/csrc/cluster_kernels.cuh)
+        one = [t[:1] for t in (d_ct1, d_ct2, d_out, d_b1, d_b2, d_bout)]
+        lat, lat_host = [], []
+        for _ in range(7):
+            ctx.EvalBinGateDevice(one[0], one[1], one[2], one[3] if lwe else None, one[4] if lwe else None, one[5] if lwe else None)
+            a, b = ctx.last_gate_timing()
+            lat.append(a + b)
+        sms_per_gate = ctx.last_gate_sms()
+        for _ in range(7):
+            t0 = time.perf_counter()
+            ctx._ck(ctx._L.mkfhe_eval_nand(ctx._h, hp(h_ct1), hp(h_b1) if lwe else None, hp(h_ct2), hp(h_b2) if lwe else None,
+                                           hp(h_out), hp(h_bout) if lwe else None, 1), "mkfhe_eval_nand")
+            lat_host.append((time.perf_counter() - t0) * 1e3)
+        res["single_gate"] = {"ms": sorted(lat[2:])[2], "e2e_ms": sorted(lat_host[2:])[2], "sms_per_gate": sms_per_gate,
+                              "what": "one EvalBinGate(NAND) per call: kernel time (CUDA events) and the synchronous host-buffer call"}
     ctx.close()
     del ctx
     torch.cuda.empty_cache()

@@ -211,6 +211,9 @@ int mkfhe_decompose(mkfhe_ctx* ctx, const uint32_t* polys, uint32_t* out, uint64
 /* ---- introspection ---- */
 /* number of kernel launches this context has issued since creation (bench.py's gpu_launches claim) */
 uint64_t mkfhe_launch_count(const mkfhe_ctx* ctx);
+/* SMs per gate of the last blind-rotation launch (mkfhe_eval_acc* / mkfhe_eval_nand* / circuits): 1, or the size of the thread-block
+ * cluster (2, 4, 8) that small batches run on -- the reference has no counterpart (one thread per EvalAcc, mk-acc-xzw.cpp:89-130) */
+uint32_t mkfhe_last_gate_sms(const mkfhe_ctx* ctx);
 /* device time (CUDA events on the context's stream) of the last mkfhe_eval_nand[_dev] batch, split into the blind-rotation
  * kernel and the key-switch kernels; waits for that batch to finish.  bench.py's roofline numerators come from here. */
 int mkfhe_last_gate_timing(mkfhe_ctx* ctx, float* rotate_ms, float* keyswitch_ms);

@@ -369,6 +369,10 @@ class BinFHEContext:
         self._ck(self._L.mkfhe_last_gate_timing(self._h, C.byref(a), C.byref(b)), "mkfhe_last_gate_timing")
         return float(a.value), float(b.value)
 
+    def last_gate_sms(self) -> int:
+        """SMs per gate of the last blind-rotation launch: 1, or the thread-block cluster size (2 / 4 / 8) of a small batch"""
+        return int(self._L.mkfhe_last_gate_sms(self._h))
+
     def launch_count(self) -> int:
         return int(self._L.mkfhe_launch_count(self._h))
 

@@ -25,7 +25,7 @@
 
 namespace mkfhe {
 
-constexpr uint32_t CL = 2;  // CTAs per cluster = SMs per gate
+// CL (template parameter below): CTAs per cluster = SMs per gate: 2, 4 or 8 (the portable maximum), at most the party count
 
 __device__ __forceinline__ uint32_t cluster_rank() {
     uint32_t r;
@@ -33,6 +33,9 @@ __device__ __forceinline__ uint32_t cluster_rank() {
     return r;
 }
 __device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+// arrival of a CTA that has written nothing the others will read (the key owner): no release fence (ncu showed the fence of
+// arrive.release as 5% of the owner's samples, profiles/r2_s21_cluster74.txt)
+__device__ __forceinline__ void cluster_arrive_relaxed() { asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory"); }
 __device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
 // address of `p` (a shared-memory address of this CTA) in the shared memory of CTA `rank` of the cluster
 __device__ __forceinline__ uint32_t cluster_map(const void* p, uint32_t rank) {
@@ -48,17 +51,17 @@ __device__ __forceinline__ void cluster_st1(uint32_t addr, uint32_t v) {
 }
 
 // parties of CTA r: p = r, r + CL, ...; party p lives at local row p / CL
-__host__ __device__ inline uint32_t cluster_rows(uint32_t k) { return (k + CL - 1) / CL; }
-// Shared memory of one CTA: a[rows][N] | E1[2][FNP] | E2[FNP] | Vs[2][N] | Ms[N] (XZW) | xchg[4] | crot[k*n] (u16)
-__host__ __device__ inline size_t cluster_smem_bytes(uint32_t k, uint32_t n, bool xzw) {
-    return (size_t(cluster_rows(k)) * FN + 3 * FNP + 2 * FN + (xzw ? FN : 0) + 4) * 4 + ((size_t(k) * n * 2 + 15) & ~size_t(15));
+__host__ __device__ inline uint32_t cluster_rows(uint32_t k, uint32_t CL) { return (k + CL - 1) / CL; }
+// Shared memory of one CTA: a[rows][N] | E1[2][FNP] | E2[FNP] | Vs[2][CL - 1][N] | Ms[N] (XZW) | xchg[8] | crot[k*n] (u16)
+__host__ __device__ inline size_t cluster_smem_bytes(uint32_t k, uint32_t n, bool xzw, uint32_t CL) {
+    return (size_t(cluster_rows(k, CL)) * FN + 3 * FNP + 2 * (CL - 1) * FN + (xzw ? FN : 0) + 8) * 4 + ((size_t(k) * n * 2 + 15) & ~size_t(15));
 }
 
 // One step of EvalAcc on the cluster (see the header comment).  `a`: this CTA's rows; `par`: parity of the count of executed steps
 // (the same in both CTAs: they skip the same zero rotations).  Ends with a block barrier; every thread executes exactly one
 // cluster arrive and one cluster wait.  Exchange-buffer discipline as in fast_step: forward transforms through E1, inverse ones
 // through E2, and between two uses of either buffer lies the block barrier inside a transform on the other.
-template <bool XZW, bool FIRST>
+template <bool XZW, bool FIRST, int CL>
 __device__ __forceinline__ void cluster_step(const DevCtx& P, const FastTables& T, uint32_t* a, uint32_t* E1, uint32_t* E2, uint32_t* Vs,
                                              uint32_t* Ms, uint32_t s, uint32_t c, uint32_t par, uint32_t tid, uint32_t rank) {
     constexpr uint32_t N = FN, M = 2 * FN;
@@ -84,7 +87,7 @@ __device__ __forceinline__ void cluster_step(const DevCtx& P, const FastTables& 
             *reinterpret_cast<uint4*>(Mt + (N / 2) * ch) = make_uint4(Q - mq[0], Q - mq[1], Q - mq[2], Q - mq[3]);
         }
     }
-    uint32_t* Vp = Vs + par * N + 8 * tid;  // this thread's 8 slots of the step's partial-sum buffer
+    uint32_t* Vp = Vs + par * (CL - 1) * N + 8 * tid;  // this thread's 8 slots of the step's partial-sum buffers (one per other CTA)
     uint32_t keep[8];                       // V_r = sum over own parties of <D_p, Pkey_p>, < 4Q
     uint32_t y[8];                          // the last own party's <D_p, d>, evaluation domain, < 3Q
     uint32_t* alast = a;
@@ -131,22 +134,30 @@ __device__ __forceinline__ void cluster_step(const DevCtx& P, const FastTables& 
     }
     if (!owner) {
         // V_r into the key owner's shared memory (the thread with the same tid there picks these 8 slots up), then the barrier
-        const uint32_t remote = cluster_map(Vp, u % CL);
+        const uint32_t slot = (rank + CL - 1 - u % CL) % CL;  // 0 .. CL - 2: this CTA's buffer in the owner's shared memory
+        const uint32_t remote = cluster_map(Vp + slot * N, u % CL);
         cluster_st4(remote, make_uint4(keep[0], keep[1], keep[2], keep[3]));
         cluster_st4(remote + 16, make_uint4(keep[4], keep[5], keep[6], keep[7]));
         cluster_arrive();
     } else {
-        cluster_arrive();
+        cluster_arrive_relaxed();
         cluster_wait();
         // ---- the sumV term (mk-acc-xzw.cpp:273-289): V = V_o + V_r, W = digits of INTT(V), X_u += <NTT(W), f> ----
         uint32_t xu[8], D[2][8];
-        const uint4 r0 = *reinterpret_cast<const uint4*>(Vp), r1 = *reinterpret_cast<const uint4*>(Vp + 4);
-        const uint32_t rv[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
 #pragma unroll
         for (int sl = 0; sl < 8; ++sl) {
             xu[sl] = y[sl];
-            const uint32_t v = keep[sl] + rv[sl];  // < 8Q
-            y[sl] = min(v, v - 4 * Q);             // < 4Q
+            y[sl] = keep[sl];
+        }
+#pragma unroll
+        for (int o = 0; o < CL - 1; ++o) {
+            const uint4 r0 = *reinterpret_cast<const uint4*>(Vp + o * N), r1 = *reinterpret_cast<const uint4*>(Vp + o * N + 4);
+            const uint32_t rv[8] = {r0.x, r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+#pragma unroll
+            for (int sl = 0; sl < 8; ++sl) {
+                const uint32_t v = y[sl] + rv[sl];  // < 8Q
+                y[sl] = min(v, v - 4 * Q);          // < 4Q
+            }
         }
         inv_ntt_regs(y, E2, T, Q, tid);
 #pragma unroll
@@ -177,10 +188,10 @@ __device__ __forceinline__ void cluster_step(const DevCtx& P, const FastTables& 
 }
 
 // Key switch of this CTA's parties (keyswitch_epilogue of generic_kernels.cuh restricted to the rows p = rank (mod CL)); the two
-// CTAs switch their parties side by side.  MKLWE: b needs the sum of the B column over ALL parties (mklwe-pke.cpp:277-280): CTA 1
-// leaves its share in CTA 0's xchg word before the closing cluster barrier of the kernel, CTA 0 finishes b after it.
+// CTAs switch their parties side by side.  MKLWE: b needs the sum of the B column over ALL parties (mklwe-pke.cpp:277-280): CTA r > 0
+// leaves its share in CTA 0's xchg[r] before the closing cluster barrier of the kernel, CTA 0 finishes b after it.
 __device__ __noinline__ uint32_t cluster_keyswitch(const DevCtx& P, const GateIO& io, uint32_t g, const uint32_t* a, uint32_t* scratch,
-                                                   uint32_t rank) {
+                                                   uint32_t rank, uint32_t CL) {
     const uint32_t N = P.N, Q = P.mod.Q, k = P.k, n = P.n;
     const uint32_t tid = threadIdx.x, T = blockDim.x;
     uint32_t* ms = scratch;
@@ -212,19 +223,19 @@ __device__ __noinline__ uint32_t cluster_keyswitch(const DevCtx& P, const GateIO
     return bsum;
 }
 
-template <bool GATE, bool XZW>
-__global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(FT, 1) blind_rotate_cluster(const DevCtx P, const FastTables T, const GateIO io) {
+template <bool GATE, bool XZW, int CL>  // launched with the cluster-dimension attribute (CL, 1, 1)
+__global__ void __launch_bounds__(FT, 1) blind_rotate_cluster(const DevCtx P, const FastTables T, const GateIO io) {
     extern __shared__ __align__(16) uint32_t sm[];
     const uint32_t k = P.k, n = P.n, tid = threadIdx.x, rank = cluster_rank(), g = blockIdx.x / CL;
     constexpr uint32_t N = FN, M = 2 * FN;
     const uint32_t rows = (k - rank + CL - 1) / CL;
     uint32_t* a = sm;
-    uint32_t* E1 = a + cluster_rows(k) * N;
+    uint32_t* E1 = a + cluster_rows(k, CL) * N;
     uint32_t* E2 = E1 + 2 * FNP;
     uint32_t* Vs = E2 + FNP;
-    uint32_t* Ms = Vs + 2 * N;
+    uint32_t* Ms = Vs + 2 * (CL - 1) * N;
     uint32_t* xchg = XZW ? Ms + N : Ms;
-    uint16_t* crot = reinterpret_cast<uint16_t*>(xchg + 4);
+    uint16_t* crot = reinterpret_cast<uint16_t*>(xchg + 8);
     const uint32_t Q = P.mod.Q;
 
     // ---- prologue: rotation amounts (both CTAs keep all of them) and this CTA's rows of the initial accumulator ----
@@ -268,19 +279,19 @@ __global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(FT, 1) blind_rotate
     cluster_wait();
 
     uint32_t par = 0;
-    cluster_step<XZW, true>(P, T, a, E1, E2, Vs, Ms, 0, crot[0], par, tid, rank);
+    cluster_step<XZW, true, CL>(P, T, a, E1, E2, Vs, Ms, 0, crot[0], par, tid, rank);
     for (uint32_t s = 1; s < k * n; ++s) {
         const uint32_t c = crot[s];
         if (c == 0) continue;  // X^0 - 1 = 0: the step leaves acc unchanged (the same decision in both CTAs)
         par ^= 1u;
-        cluster_step<XZW, false>(P, T, a, E1, E2, Vs, Ms, s, c, par, tid, rank);
+        cluster_step<XZW, false, CL>(P, T, a, E1, E2, Vs, Ms, s, c, par, tid, rank);
     }
 
     // ---- epilogue: this CTA's rows -> outputs ----
     uint32_t bsum = 0;
     if (GATE && P.ksk16 != nullptr) {
-        bsum = cluster_keyswitch(P, io, g, a, E1, rank);
-        if (P.scheme == 1 && rank != 0 && tid == 0) cluster_st1(cluster_map(xchg, 0), bsum);
+        bsum = cluster_keyswitch(P, io, g, a, E1, rank, CL);
+        if (P.scheme == 1 && rank != 0 && tid == 0) cluster_st1(cluster_map(xchg + rank, 0), bsum);
     } else if (GATE) {
         for (uint32_t row = 0; row < rows; ++row) {
             uint32_t* out = io.ms_out + (size_t(g) * k + rank + CL * row) * N;
@@ -302,35 +313,81 @@ __global__ void __cluster_dims__(CL, 1, 1) __launch_bounds__(FT, 1) blind_rotate
     cluster_arrive();
     cluster_wait();
     if (GATE && P.ksk16 != nullptr && P.scheme == 1 && rank == 0 && tid == 0) {
-        const uint32_t all = (bsum + xchg[0]) % P.qKS;  // b = RoundqQ(Q/8 + 1) - sum B (binfhe-base-scheme.cpp:450-458)
+        uint32_t all = bsum;  // b = RoundqQ(Q/8 + 1) - sum B (binfhe-base-scheme.cpp:450-458)
+        for (uint32_t r = 1; r < CL; ++r) all = (all + xchg[r]) % P.qKS;
         io.bout[g] = submod(round_qQ((Q >> 3) + 1, P.qKS, Q), all, P.qKS);
     }
 }
 
 // ---- host side ----
-inline bool cluster_supported(const DevCtx& d) {
-    return fast_supported(d) && d.k >= CL && cluster_smem_bytes(d.k, d.n, d.variant == 0) <= 227 * 1024;
+inline bool cluster_supported(const DevCtx& d, uint32_t CL) {
+    return fast_supported(d) && d.k >= CL && cluster_smem_bytes(d.k, d.n, d.variant == 0, CL) <= 227 * 1024;
 }
-// Batches that leave at least half of the SMs idle get two SMs per gate.  MKFHE_CLUSTER=0/1 forces the choice for A/B runs.
-inline bool cluster_wanted(const DevCtx& d, uint32_t batch, int sms) {
-    if (!cluster_supported(d)) return false;
-    if (const char* e = getenv("MKFHE_CLUSTER")) return e[0] == '1';
-    return uint64_t(batch) * CL <= uint64_t(sms);
+template <class K>
+inline cudaError_t cluster_launch(K kern, uint32_t CL, uint32_t batch, size_t smem, cudaStream_t st, const DevCtx& d, const FastTables& T,
+                                  const GateIO& io, int* max_clusters) {
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
+    if (e != cudaSuccess) return e;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(batch * CL, 1, 1);
+    cfg.blockDim = dim3(FT, 1, 1);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CL;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    if (max_clusters != nullptr) return cudaOccupancyMaxActiveClusters(max_clusters, kern, &cfg);
+    return cudaLaunchKernelEx(&cfg, kern, d, T, io);
 }
-inline cudaError_t cluster_blind_rotate(FastState& F, const DevCtx& d, bool gate, const GateIO& io, uint32_t batch, cudaStream_t st,
-                                        uint64_t* launches) {
+// kernel of (gate, xzw, CL); max_clusters != null: only ask how many clusters of this shape the GPU holds at once
+inline cudaError_t cluster_dispatch(FastState& F, const DevCtx& d, bool gate, uint32_t CL, const GateIO& io, uint32_t batch, cudaStream_t st,
+                                    int* max_clusters) {
     const bool xzw = d.variant == 0;
+    const size_t smem = cluster_smem_bytes(d.k, d.n, xzw, CL);
+#define MKFHE_CL(G_, X_)                                                                                                  \
+    (CL == 2 ? cluster_launch(blind_rotate_cluster<G_, X_, 2>, 2, batch, smem, st, d, F.T, io, max_clusters)               \
+             : CL == 4 ? cluster_launch(blind_rotate_cluster<G_, X_, 4>, 4, batch, smem, st, d, F.T, io, max_clusters)     \
+                       : cluster_launch(blind_rotate_cluster<G_, X_, 8>, 8, batch, smem, st, d, F.T, io, max_clusters))
+    return gate ? (xzw ? MKFHE_CL(true, true) : MKFHE_CL(true, false)) : (xzw ? MKFHE_CL(false, true) : MKFHE_CL(false, false));
+#undef MKFHE_CL
+}
+// SMs per gate for a batch: the largest cluster (8, 4, 2 CTAs, at most one per party) of which the GPU holds `batch` at once -- a
+// second wave would double the latency the cluster is there to cut; 0 = no cluster (the one-SM kernels).
+// MKFHE_CLUSTER = 0: never; 2 / 4 / 8: that size whenever the parameter set supports it (A/B runs, tests).
+inline uint32_t cluster_size_for(FastState& F, const DevCtx& d, bool gate, uint32_t batch) {
+    uint32_t forced = 0;
+    if (const char* e = getenv("MKFHE_CLUSTER")) {
+        forced = uint32_t(atoi(e));
+        if (forced != 2 && forced != 4 && forced != 8) return 0;
+        return cluster_supported(d, forced) ? forced : 0;
+    }
+    // a run that selects a one-SM kernel variant by hand (experiments, the variant tests) keeps it
+    if (getenv("MKFHE_GROUPS") || getenv("MKFHE_MINB") || getenv("MKFHE_FAST_ALIAS") || getenv("MKFHE_AG")) return 0;
+    for (uint32_t CL = 8; CL >= 2; CL >>= 1) {
+        if (!cluster_supported(d, CL) || uint64_t(batch) * CL > uint64_t(F.sms)) continue;
+        int& cached = F.max_clusters[gate ? 1 : 0][CL == 8 ? 2 : CL == 4 ? 1 : 0];
+        if (cached < 0) {
+            int m = 0;
+            GateIO none{};
+            if (cluster_dispatch(F, d, gate, CL, none, 1, nullptr, &m) != cudaSuccess) {
+                cudaGetLastError();
+                m = 0;
+            }
+            cached = m;
+        }
+        if (int64_t(batch) <= int64_t(cached)) return CL;
+    }
+    return 0;
+}
+inline cudaError_t cluster_blind_rotate(FastState& F, const DevCtx& d, bool gate, uint32_t CL, const GateIO& io, uint32_t batch,
+                                        cudaStream_t st, uint64_t* launches) {
     F.T.prefetch = d.k <= 8 ? 1u : 0u;
     if (const char* pf = getenv("MKFHE_PREFETCH")) F.T.prefetch = pf[0] == '1' ? 1u : 0u;
-    const size_t smem = cluster_smem_bytes(d.k, d.n, xzw);
-    auto launch = [&](auto kern) -> cudaError_t {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
-        if (e != cudaSuccess) return e;
-        kern<<<batch * CL, FT, smem, st>>>(d, F.T, io);
-        return cudaSuccess;
-    };
-    const cudaError_t e = gate ? (xzw ? launch(blind_rotate_cluster<true, true>) : launch(blind_rotate_cluster<true, false>))
-                               : (xzw ? launch(blind_rotate_cluster<false, true>) : launch(blind_rotate_cluster<false, false>));
+    const cudaError_t e = cluster_dispatch(F, d, gate, CL, io, batch, st, nullptr);
     if (e != cudaSuccess) return e;
     ++*launches;
     return cudaGetLastError();

@@ -1444,6 +1444,7 @@ struct FastState {
     uint4* d_tw16{nullptr};
     uint2 one2{};
     int sms{148};
+    int max_clusters[2][3] = {{-1, -1, -1}, {-1, -1, -1}};  // cluster_kernels.cuh: co-resident clusters of 2 / 4 / 8 CTAs, [gate][size]
     uint32_t* accws{nullptr};  // blind_rotate_fast_ag: [sms * 4][k][N] accumulator slices, allocated by fast_init when MKFHE_AG=1
     bool half{false};  // tables for N = 1024 (two polynomials per 2048-word pass): only the batched transform uses them
 };

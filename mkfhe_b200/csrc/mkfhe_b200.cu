@@ -34,6 +34,7 @@ struct mkfhe_ctx {
     cudaStream_t own_stream{nullptr};
     std::string err;
     uint64_t launches{0};
+    uint32_t last_sms_per_gate{1};  // SMs per gate of the last blind-rotation launch (cluster size, else 1)
     uint64_t dev_bytes{0};
     // tables
     uint32_t *tw{nullptr}, *twi{nullptr}, *psipow{nullptr};
@@ -429,6 +430,7 @@ int mkfhe_ctx_synchronize(mkfhe_ctx* ctx) {
     CU(cudaStreamSynchronize(ctx->stream));
     return MKFHE_OK;
 }
+uint32_t mkfhe_last_gate_sms(const mkfhe_ctx* ctx) { return ctx ? ctx->last_sms_per_gate : 0u; }
 uint64_t mkfhe_launch_count(const mkfhe_ctx* ctx) { return ctx ? ctx->launches : 0; }
 uint64_t mkfhe_device_bytes(const mkfhe_ctx* ctx) { return ctx ? ctx->dev_bytes : 0; }
 
@@ -599,8 +601,10 @@ static int launch_rotate(mkfhe_ctx* ctx, bool gate, const GateIO& io, uint64_t b
     if (!ctx->bk || !ctx->pkey) return fail(ctx, MKFHE_ENOKEY, "bootstrapping key / Pkey not loaded");
     if (batch == 0) return MKFHE_OK;
     if (batch > 0x7fffffffull) return fail(ctx, MKFHE_EINVAL, "batch too large");
-    if (ctx->use_fast && cluster_wanted(ctx->d, uint32_t(batch), ctx->fast.sms)) {  // few gates: two SMs per gate
-        cudaError_t e = cluster_blind_rotate(ctx->fast, ctx->d, gate, io, uint32_t(batch), ctx->stream, &ctx->launches);
+    const uint32_t CL = ctx->use_fast ? cluster_size_for(ctx->fast, ctx->d, gate, uint32_t(batch)) : 0u;
+    ctx->last_sms_per_gate = CL ? CL : 1u;
+    if (CL) {  // few gates: 2, 4 or 8 SMs per gate
+        cudaError_t e = cluster_blind_rotate(ctx->fast, ctx->d, gate, CL, io, uint32_t(batch), ctx->stream, &ctx->launches);
         if (e != cudaSuccess) return fail(ctx, MKFHE_ECUDA, "cluster_blind_rotate: %s", cudaGetErrorString(e));
         return MKFHE_OK;
     }

@@ -26,7 +26,7 @@ SYMBOLS = [
     "mkfhe_key_image", "mkfhe_key_image_commit",
     "mkfhe_eval_acc", "mkfhe_eval_acc_dev", "mkfhe_eval_nand", "mkfhe_eval_nand_dev", "mkfhe_ntt", "mkfhe_ntt_dev",
     "mkfhe_load_sk", "mkfhe_decrypt", "mkfhe_decrypt_dev", "mkfhe_eval_circuit", "mkfhe_eval_circuit_dev", "mkfhe_circuit_levels", "mkfhe_eval_circuit_dev_static", "mkfhe_circuit_static_words", "mkfhe_static_scratch_words", "mkfhe_keygen_bk", "mkfhe_keygen_pkey", "mkfhe_keygen_ksk_mntru", "mkfhe_keygen_ksk_mklwe", "mkfhe_encrypt_mntru", "mkfhe_encrypt_mklwe", "mkfhe_keyfile_write", "mkfhe_keyfile_info", "mkfhe_keyfile_load", "mkfhe_ctfile_write", "mkfhe_ctfile_info", "mkfhe_ctfile_read",
-    "mkfhe_decompose", "mkfhe_last_gate_timing", "mkfhe_launch_count", "mkfhe_device_bytes", "mkfhe_version", "mkfhe_measure_int32_peak", "mkfhe_measure_butterfly_peak",
+    "mkfhe_decompose", "mkfhe_last_gate_timing", "mkfhe_last_gate_sms", "mkfhe_launch_count", "mkfhe_device_bytes", "mkfhe_version", "mkfhe_measure_int32_peak", "mkfhe_measure_butterfly_peak",
 ]
 
 
@@ -97,6 +97,8 @@ def load():
     L.mkfhe_ntt_dev.argtypes = [vp, vp, u64, i32]
     L.mkfhe_decompose.argtypes = [vp, vp, vp, u64]
     L.mkfhe_last_gate_timing.argtypes = [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    L.mkfhe_last_gate_sms.argtypes = [vp]
+    L.mkfhe_last_gate_sms.restype = C.c_uint32
     L.mkfhe_launch_count.argtypes = [vp]
     L.mkfhe_launch_count.restype = u64
     L.mkfhe_device_bytes.argtypes = [vp]

@@ -36,6 +36,20 @@ CASES = [  # paramset, environment overrides, gates in the batch, gates re-compu
     ("STD100_MKNTRU_3", {"MKFHE_GROUPS": "1"}, 5, 4),
     ("STD100_MKNTRU_3", {}, 5, 4),
     ("STD100_MKNTRU_4", {}, 2, 1),
+    # thread-block clusters (blind_rotate_cluster): 2 / 4 / 8 SMs per gate, forced; batches of at most SMs / size gates pick the
+    # largest size that fits by default (the 17-, 5- and 2-gate default cases above), MKFHE_CLUSTER=0 keeps them on one SM
+    ("STD100_MKNTRU_LWE", {"MKFHE_CLUSTER": "2"}, 5, 4),
+    ("STD100_MKNTRU", {"MKFHE_CLUSTER": "2"}, 5, 4),
+    ("STD100_MKNTRU_LWE", {"MKFHE_CLUSTER": "0"}, 17, 4),
+    ("STD100_MKNTRU", {"MKFHE_CLUSTER": "0"}, 17, 4),
+    ("STD100_MKNTRU_2", {"MKFHE_CLUSTER": "2"}, 3, 2),
+    ("STD100_MKNTRU_2", {"MKFHE_CLUSTER": "4"}, 3, 2),
+    ("STD100_MKNTRU_LWE_2", {"MKFHE_CLUSTER": "4"}, 3, 2),
+    ("STD100_MKNTRU_2", {"MKFHE_CLUSTER": "0"}, 3, 2),
+    ("STD100_MKNTRU_3", {"MKFHE_CLUSTER": "8"}, 2, 1),
+    ("STD100_MKNTRU_LWE_3", {"MKFHE_CLUSTER": "4"}, 2, 1),
+    ("STD100_MKNTRU_4", {"MKFHE_CLUSTER": "8"}, 2, 1),
+    ("STD100_MKNTRU_4", {"MKFHE_CLUSTER": "0"}, 2, 1),
     # accumulators in global memory (blind_rotate_fast_ag, an experiment behind MKFHE_AG=1; batches above the SM count only)
     ("STD100_MKNTRU_LWE", {"MKFHE_AG": "1"}, 150, 2),
     ("STD100_MKNTRU_2", {"MKFHE_AG": "1", "MKFHE_MINB": "4"}, 150, 2),
@@ -119,3 +133,35 @@ def test_k4_full_size_against_the_compiled_reference():
     assert r.decrypt(eo, 0) == 1
     ctx.close()
     r.close()
+
+
+@pytest.mark.parametrize("k,cl", [(3, "2"), (5, "4"), (6, "4")])
+def test_cluster_kernel_party_counts_that_do_not_divide(k, cl, monkeypatch):
+    """blind_rotate_cluster with a party count that is not a multiple of the cluster size (CTAs own different numbers of parties;
+    the reference's tables stop at powers of two, its code does not): one gate and one EvalAcc against the C oracle, and against
+    the one-SM kernels."""
+    P = mk.derive_params(mk.PARAMSETS["STD100_MKNTRU"], mk.MKNTRU)
+    P.k = k
+    rng = np.random.default_rng(100 + k)
+    ell, S = P.digitsG - 1, 2
+    bk = rng.integers(0, P.Q, size=(P.k * S * P.n + 1) * ell * 2 * P.N, dtype=np.uint32)
+    pkey = rng.integers(0, P.Q, size=P.k * ell * P.N, dtype=np.uint32)
+    ksk = rng.integers(0, P.qKS, size=P.k * P.N * P.dKS * P.n, dtype=np.uint32)
+    ctnand = rng.integers(0, P.q, size=P.k * P.n, dtype=np.uint32)
+    ct1 = rng.integers(0, P.q, size=(2, P.k, P.n), dtype=np.uint32)
+    ct2 = rng.integers(0, P.q, size=(2, P.k, P.n), dtype=np.uint32)
+    acc = rng.integers(0, P.Q, size=(1, P.k, P.N), dtype=np.uint32)
+    rot = rng.integers(0, P.q, size=(1, P.k, P.n), dtype=np.uint32)
+    res = {}
+    for mode in (cl, "0"):
+        monkeypatch.setenv("MKFHE_CLUSTER", mode)
+        ctx = mk.BinFHEContext().GenerateFromParams(P)
+        ctx.LoadKeys(bk, pkey, ksk=ksk, ctnand=ctnand)
+        res[mode] = (np.asarray(ctx.EvalBinGate("NAND", ct1, ct2)), np.asarray(ctx.EvalAcc(acc, rot, P.q)))
+        ctx.close()
+    assert (res[cl][0] == res["0"][0]).all() and (res[cl][1] == res["0"][1]).all()
+    o = make_oracle(P)
+    eo, _ = o.eval_nand(bk, pkey, ksk, None, ctnand, ct1[1].ravel(), 0, ct2[1].ravel(), 0)
+    assert (res[cl][0][1].ravel() == eo).all()
+    ea = o.eval_acc(bk, pkey, acc[0].ravel(), rot[0].ravel(), P.q)
+    assert (res[cl][1][0].ravel() == np.asarray(ea).ravel()).all()

@@ -22,6 +22,32 @@ peaks() {
 run() { name=$1; shift; (time timeout 1500 python bench.py "$@") > gpurun_out/${TAG}_${name}.json 2> gpurun_out/${TAG}_${name}.err; \
         echo "== $name"; cut -c1-600 gpurun_out/${TAG}_${name}.json; tail -2 gpurun_out/${TAG}_${name}.err; }
 case $S in
+cl4)    # cluster kernel after the relaxed owner arrival; then the whole GPU suite and smoke with clusters as the small-batch default
+  q() { echo "== $*"; env "$@" timeout 300 python tests/dev_quick_bench.py --paramset $PS --batches $BT --check $CK --reps 3 2>&1 | grep -E "batch|MISMATCH|exact|rror" ; }
+  PS=STD100_MKNTRU_LWE BT=1,74 CK=1; q X=0
+  PS=STD100_MKNTRU BT=1,74 CK=1; q X=0
+  PS=STD100_MKNTRU_2 BT=1,37 CK=1; q X=0
+  (time timeout 1500 python -m pytest tests -m gpu -x -q) > gpurun_out/${TAG}_tests.log 2>&1; tail -5 gpurun_out/${TAG}_tests.log
+  python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${TAG}_smoke.log 2>&1; tail -3 gpurun_out/${TAG}_smoke.log
+  ;;
+cl3)    # cluster kernel: L1 key prefetch on / off (MKFHE_PREFETCH), ncu of the kernel, default bench line with the single-gate block
+  q() { echo "== $*"; env "$@" timeout 300 python tests/dev_quick_bench.py --paramset $PS --batches $BT --check $CK --reps 3 2>&1 | grep -E "batch|MISMATCH|exact|rror" ; }
+  PS=STD100_MKNTRU_LWE BT=1,74 CK=1; q MKFHE_PREFETCH=0; q X=0
+  PS=STD100_MKNTRU BT=1,74 CK=1; q MKFHE_PREFETCH=0; q X=0
+  PS=STD100_MKNTRU_2 BT=1 CK=1; q MKFHE_PREFETCH=0; q X=0
+  prof cluster74 blind_rotate_cluster 2 1 --batch 74 --steps 1 --warmup 2 --synthetic-keys --no-also --check-oracle 0
+  python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${TAG}_smoke.log 2>&1; tail -3 gpurun_out/${TAG}_smoke.log
+  run bench --steps 5 --warmup 3
+  ;;
+cl2)    # cluster sizes 2 / 4 / 8 at k = 4 / 8 / 16 (single gate and the largest batch that still fits), then the kernel-variant tests
+  q() { echo "== $*"; env "$@" timeout 300 python tests/dev_quick_bench.py --paramset $PS --batches $BT --check $CK --reps 3 2>&1 | grep -E "batch|MISMATCH|exact|rror" ; }
+  PS=STD100_MKNTRU_2 BT=1,16 CK=1; q MKFHE_CLUSTER=2; q MKFHE_CLUSTER=4; q X=0
+  PS=STD100_MKNTRU_LWE_2 BT=1,16 CK=1; q MKFHE_CLUSTER=4
+  PS=STD100_MKNTRU_3 BT=1,16 CK=1; q MKFHE_CLUSTER=2; q MKFHE_CLUSTER=4; q MKFHE_CLUSTER=8; q X=0
+  PS=STD100_MKNTRU_4 BT=1,16 CK=1; q MKFHE_CLUSTER=2; q MKFHE_CLUSTER=4; q MKFHE_CLUSTER=8; q X=0
+  PS=STD100_MKNTRU_LWE BT=1,37,74,75,148,149 CK=1; q X=0
+  (time timeout 900 python -m pytest tests/test_gpu_partysweep.py -m gpu -x -q) > gpurun_out/${TAG}_partysweep.log 2>&1; tail -5 gpurun_out/${TAG}_partysweep.log
+  ;;
 cl)     # two SMs per gate (blind_rotate_cluster) against the party-parallel kernel on one SM, small batches
   q() { echo "== $*"; env "$@" timeout 300 python tests/dev_quick_bench.py --paramset $PS --batches $BT --check $CK --reps 3 2>&1 | grep -E "batch|MISMATCH|exact|Error|error|rror" ; }
   PS=STD100_MKNTRU_LWE BT=1,16,74 CK=2; q MKFHE_CLUSTER=0; q MKFHE_CLUSTER=1
