@@ -41,7 +41,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not stale():
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc, *NVCC_FLAGS, "-o", LIB, *sources()]
+    cmd = [nvcc, *NVCC_FLAGS, *os.environ.get("MKFHE_NVCC_EXTRA", "").split(), "-o", LIB, *sources()]  # e.g. -DMKFHE_CLUSTER_TIMING
     proc = subprocess.run(cmd, capture_output=True, text=True)
     log = proc.stdout + proc.stderr
     with open(os.path.join(HERE, "build.log"), "w") as f:

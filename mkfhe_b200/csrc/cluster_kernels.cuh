@@ -57,13 +57,76 @@ __host__ __device__ inline size_t cluster_smem_bytes(uint32_t k, uint32_t n, boo
     return (size_t(cluster_rows(k, CL)) * FN + 3 * FNP + 2 * (CL - 1) * FN + (xzw ? FN : 0) + 8) * 4 + ((size_t(k) * n * 2 + 15) & ~size_t(15));
 }
 
+// ---- key words in registers ahead of their use -----------------------------------------------------------------------------------
+// With two warps per sub-partition nothing hides a global load between a transform and the multiply-accumulate that follows it
+// (phase timing, profiles/r2_s23_cluster_timing.txt: 1.5 k cycles per <D, key> against 2.4 k for the two forward transforms before
+// it; boolean-mkntru: 2.5 k more at the top of every step for the 8 scattered words of Q - X^-c).  This kernel has the register
+// file of an SM for 256 threads, so the loads are issued BEFORE the forward transforms and land while they run.
+template <bool XZW>
+struct KeyRegs {
+    uint4 a[2][2];                 // ev1, [digit][chunk of 4 slots]
+    uint4 b[XZW ? 2 : 1][2];       // ev2 (XZW)
+};
+template <bool XZW>
+__device__ __forceinline__ void key_load(KeyRegs<XZW>& K, const uint32_t* k1p, const uint32_t* k2p) {
+    constexpr uint32_t N = FN, KCH = FN / 2;
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+#pragma unroll
+        for (int ch = 0; ch < 2; ++ch) {
+            K.a[j][ch] = ldg4_stream(k1p + 2 * j * N + KCH * ch);
+            if (XZW) K.b[j][ch] = ldg4_stream(k2p + 2 * j * N + KCH * ch);
+        }
+}
+// key_mac4's two steady-state branches (XZW_B: ev1; XZW: ev1 - ev2 X^-c as two 64-bit sums) on preloaded words; mq = Q - X^-c at this
+// thread's 8 slots (XZW)
+template <bool XZW>
+__device__ __forceinline__ void key_mac_regs(const DevCtx& P, const KeyRegs<XZW>& K, const uint32_t (&mq)[8], int ch, const uint32_t (&D)[2][8],
+                                             uint32_t (&x4)[4]) {
+    const uint32_t Q = P.mod.Q;
+    const uint32_t a0v[4] = {K.a[0][ch].x, K.a[0][ch].y, K.a[0][ch].z, K.a[0][ch].w};
+    const uint32_t a1v[4] = {K.a[1][ch].x, K.a[1][ch].y, K.a[1][ch].z, K.a[1][ch].w};
+    if (XZW) {
+        const uint32_t b0v[4] = {K.b[0][ch].x, K.b[0][ch].y, K.b[0][ch].z, K.b[0][ch].w};
+        const uint32_t b1v[4] = {K.b[XZW ? 1 : 0][ch].x, K.b[XZW ? 1 : 0][ch].y, K.b[XZW ? 1 : 0][ch].z, K.b[XZW ? 1 : 0][ch].w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const uint32_t d0 = D[0][4 * ch + q], d1 = D[1][4 * ch + q];  // < 24Q
+            const uint64_t s2 = static_cast<uint64_t>(d0) * b0v[q] + static_cast<uint64_t>(d1) * b1v[q];
+            const uint32_t q2 = static_cast<uint32_t>(s2) * P.mod.qinv_neg;
+            const uint32_t r2 = static_cast<uint32_t>((s2 + static_cast<uint64_t>(q2) * Q) >> 32);  // < 3Q
+            const uint64_t s1 = static_cast<uint64_t>(d0) * a0v[q] + static_cast<uint64_t>(d1) * a1v[q] +
+                                static_cast<uint64_t>(r2) * mq[4 * ch + q];  // < 51 Q^2 < 2^60
+            const uint32_t q1 = static_cast<uint32_t>(s1) * P.mod.qinv_neg;
+            x4[q] = static_cast<uint32_t>((s1 + static_cast<uint64_t>(q1) * Q) >> 32);  // < 3Q
+        }
+    } else {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) x4[q] = mac2(D[0][4 * ch + q], a0v[q], D[1][4 * ch + q], a1v[q], P.mod);
+    }
+}
+
+// Phase timing of the key owner's chain (development aid: nvcc -DMKFHE_CLUSTER_TIMING; thread 0 of every CTA prints its totals)
+#ifdef MKFHE_CLUSTER_TIMING
+#define MKFHE_TICK(i_) { const uint32_t now_ = uint32_t(clock64()); tk[i_] += now_ - tlast; tlast = now_; }
+#else
+#define MKFHE_TICK(i_)
+#endif
+
 // One step of EvalAcc on the cluster (see the header comment).  `a`: this CTA's rows; `par`: parity of the count of executed steps
 // (the same in both CTAs: they skip the same zero rotations).  Ends with a block barrier; every thread executes exactly one
 // cluster arrive and one cluster wait.  Exchange-buffer discipline as in fast_step: forward transforms through E1, inverse ones
 // through E2, and between two uses of either buffer lies the block barrier inside a transform on the other.
 template <bool XZW, bool FIRST, int CL>
 __device__ __forceinline__ void cluster_step(const DevCtx& P, const FastTables& T, uint32_t* a, uint32_t* E1, uint32_t* E2, uint32_t* Vs,
-                                             uint32_t* Ms, uint32_t s, uint32_t c, uint32_t par, uint32_t tid, uint32_t rank) {
+                                             uint32_t* Ms, uint32_t s, uint32_t c, uint32_t par, uint32_t tid, uint32_t rank
+#ifdef MKFHE_CLUSTER_TIMING
+                                             , uint32_t (&tk)[16]
+#endif
+                                             ) {
+#ifdef MKFHE_CLUSTER_TIMING
+    uint32_t tlast = uint32_t(clock64());
+#endif
     constexpr uint32_t N = FN, M = 2 * FN;
     const uint32_t Q = P.mod.Q, k = P.k, n = P.n, g = P.gbits;
     const uint32_t u = FIRST ? 0u : s / n, i = FIRST ? 0u : s - u * n;
@@ -78,13 +141,16 @@ __device__ __forceinline__ void cluster_step(const DevCtx& P, const FastTables& 
     const uint32_t brv8 = __brev(tid) >> 24;
     const uint32_t e0n = cneg * (2 * brv8 + 1), e0p = c * (2 * brv8 + 1);
     if (T.prefetch && rank == 0) prefetch_step_keys<XZW>(P, s + 1, tid);
-    uint32_t* Mt = Ms + 4 * tid;
-    if (XZW && !FIRST) {  // Q - X^-c at this thread's slots, once per step (see fast_step)
+    (void)Ms;
+    uint32_t mq[8] = {};  // XZW: Q - X^-c at this thread's 8 slots, the same for every multiply-accumulate of the step: loaded once,
+                          // into registers (the one-SM kernels park it in shared memory), first used after the forward transforms
+    if (XZW && !FIRST) {
 #pragma unroll
         for (int ch = 0; ch < 2; ++ch) {
-            uint32_t mq[4];
-            monomial4(P.psipow, e0n, cneg, ch, mq);
-            *reinterpret_cast<uint4*>(Mt + (N / 2) * ch) = make_uint4(Q - mq[0], Q - mq[1], Q - mq[2], Q - mq[3]);
+            uint32_t m4[4];
+            monomial4(P.psipow, e0n, cneg, ch, m4);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) mq[4 * ch + q] = Q - m4[q];
         }
     }
     uint32_t* Vp = Vs + par * (CL - 1) * N + 8 * tid;  // this thread's 8 slots of the step's partial-sum buffers (one per other CTA)
@@ -100,13 +166,24 @@ __device__ __forceinline__ void cluster_step(const DevCtx& P, const FastTables& 
         uint32_t D[2][8];
 #pragma unroll
         for (int r = 0; r < 8; ++r) decompose2(FIRST ? ap[tid + 256 * r] : rot_sub(ap, c, tid + 256 * r, N, Q), Q, g, D[0][r], D[1][r]);
-        fwd_ntt_regs<2>(D, E1, T, Q, tid);
+        MKFHE_TICK(0)
         const uint32_t* pk = P.pkey + size_t(p) * 2 * N + 4 * tid;
+        KeyRegs<XZW> K;
+        uint4 pq[2][2];  // Pkey_p, [digit][chunk]
+        if (!FIRST) key_load<XZW>(K, ev1, ev2);  // "d" column: in flight during the transforms
+#pragma unroll
+        for (int ch = 0; ch < 2; ++ch) {
+            pq[0][ch] = ldg4(pk + (N / 2) * ch);
+            pq[1][ch] = ldg4(pk + N + (N / 2) * ch);
+        }
+        fwd_ntt_regs<2>(D, E1, T, Q, tid);
+        MKFHE_TICK(1)
 #pragma unroll
         for (int ch = 0; ch < 2; ++ch) {
             uint32_t x4[4];
-            key_mac4<XZW, FIRST>(P, ev1, ev2, evs, c, cneg, e0p, e0n, ch, D, x4, (XZW && !FIRST) ? Mt : nullptr);  // "d" column
-            const uint4 q0 = ldg4(pk + (N / 2) * ch), q1 = ldg4(pk + N + (N / 2) * ch);
+            if (FIRST) key_mac4<XZW, FIRST>(P, ev1, ev2, evs, c, cneg, e0p, e0n, ch, D, x4, nullptr);  // "d" column (KDM key, once per gate)
+            else key_mac_regs<XZW>(P, K, mq, ch, D, x4);
+            const uint4 q0 = pq[0][ch], q1 = pq[1][ch];
             const uint32_t pp0[4] = {q0.x, q0.y, q0.z, q0.w}, pp1[4] = {q1.x, q1.y, q1.z, q1.w};
 #pragma unroll
             for (int q = 0; q < 4; ++q) {
@@ -118,6 +195,7 @@ __device__ __forceinline__ void cluster_step(const DevCtx& P, const FastTables& 
             }
         }
         alast = ap;
+        MKFHE_TICK(2)
         if (j + 1 < rows) {  // not the last own party: back to coefficients now
             inv_ntt_regs(y, E2, T, Q, tid);
 #pragma unroll
@@ -139,9 +217,11 @@ __device__ __forceinline__ void cluster_step(const DevCtx& P, const FastTables& 
         cluster_st4(remote, make_uint4(keep[0], keep[1], keep[2], keep[3]));
         cluster_st4(remote + 16, make_uint4(keep[4], keep[5], keep[6], keep[7]));
         cluster_arrive();
+        MKFHE_TICK(3)
     } else {
         cluster_arrive_relaxed();
         cluster_wait();
+        MKFHE_TICK(4)
         // ---- the sumV term (mk-acc-xzw.cpp:273-289): V = V_o + V_r, W = digits of INTT(V), X_u += <NTT(W), f> ----
         uint32_t xu[8], D[2][8];
 #pragma unroll
@@ -160,19 +240,27 @@ __device__ __forceinline__ void cluster_step(const DevCtx& P, const FastTables& 
             }
         }
         inv_ntt_regs(y, E2, T, Q, tid);
+        MKFHE_TICK(5)
 #pragma unroll
         for (int r = 0; r < 8; ++r) decompose2(fold1(y[r], Q), Q, g, D[0][r], D[1][r]);
+        MKFHE_TICK(6)
+        KeyRegs<XZW> K;
+        if (!FIRST) key_load<XZW>(K, ev1 + N, ev2 + N);  // "f" column
         fwd_ntt_regs<2>(D, E1, T, Q, tid);
+        MKFHE_TICK(7)
 #pragma unroll
         for (int ch = 0; ch < 2; ++ch) {
             uint32_t x4[4];
-            key_mac4<XZW, FIRST>(P, ev1 + N, ev2 + N, evs + N, c, cneg, e0p, e0n, ch, D, x4, (XZW && !FIRST) ? Mt : nullptr);  // "f" column
+            if (FIRST) key_mac4<XZW, FIRST>(P, ev1 + N, ev2 + N, evs + N, c, cneg, e0p, e0n, ch, D, x4, nullptr);  // "f" column
+            else key_mac_regs<XZW>(P, K, mq, ch, D, x4);
 #pragma unroll
             for (int q = 0; q < 4; ++q) y[4 * ch + q] = xu[4 * ch + q] + x4[q];  // < 6Q
         }
     }
     // the last own party's product (the owner's now includes the sumV term) back to coefficients
+    MKFHE_TICK(8)
     inv_ntt_regs(y, E2, T, Q, tid);
+    MKFHE_TICK(9)
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
         if (FIRST) {
@@ -183,8 +271,11 @@ __device__ __forceinline__ void cluster_step(const DevCtx& P, const FastTables& 
             alast[tid + 256 * r] = min(v, v - Q);
         }
     }
+    MKFHE_TICK(10)
     if (!owner) cluster_wait();  // (free by now: the owner arrived before its sumV term)
+    MKFHE_TICK(11)
     __syncthreads();             // a[] complete before the next step's shifted reads
+    MKFHE_TICK(12)
 }
 
 // Key switch of this CTA's parties (keyswitch_epilogue of generic_kernels.cuh restricted to the rows p = rank (mod CL)); the two
@@ -279,13 +370,27 @@ __global__ void __launch_bounds__(FT, 1) blind_rotate_cluster(const DevCtx P, co
     cluster_wait();
 
     uint32_t par = 0;
-    cluster_step<XZW, true, CL>(P, T, a, E1, E2, Vs, Ms, 0, crot[0], par, tid, rank);
+#ifdef MKFHE_CLUSTER_TIMING
+    uint32_t tk[16] = {};
+    const uint32_t tstart = uint32_t(clock64());
+#define MKFHE_TK , tk
+#else
+#define MKFHE_TK
+#endif
+    cluster_step<XZW, true, CL>(P, T, a, E1, E2, Vs, Ms, 0, crot[0], par, tid, rank MKFHE_TK);
     for (uint32_t s = 1; s < k * n; ++s) {
         const uint32_t c = crot[s];
         if (c == 0) continue;  // X^0 - 1 = 0: the step leaves acc unchanged (the same decision in both CTAs)
         par ^= 1u;
-        cluster_step<XZW, false, CL>(P, T, a, E1, E2, Vs, Ms, s, c, par, tid, rank);
+        cluster_step<XZW, false, CL>(P, T, a, E1, E2, Vs, Ms, s, c, par, tid, rank MKFHE_TK);
     }
+#undef MKFHE_TK
+#ifdef MKFHE_CLUSTER_TIMING
+    if (tid == 0 && g == 0)
+        printf("cluster timing rank %u: total %u | decomp %u fwd2 %u mac %u | nonowner: stV+arrive %u | owner: arrive+wait %u invV %u decomp %u fwd2 %u "
+               "macf %u | inv %u update %u wait %u sync %u\n", rank, uint32_t(clock64()) - tstart, tk[0], tk[1], tk[2], tk[3], tk[4], tk[5], tk[6],
+               tk[7], tk[8], tk[9], tk[10], tk[11], tk[12]);
+#endif
 
     // ---- epilogue: this CTA's rows -> outputs ----
     uint32_t bsum = 0;
@@ -357,16 +462,17 @@ inline cudaError_t cluster_dispatch(FastState& F, const DevCtx& d, bool gate, ui
 }
 // SMs per gate for a batch: the largest cluster (8, 4, 2 CTAs, at most one per party) of which the GPU holds `batch` at once -- a
 // second wave would double the latency the cluster is there to cut; 0 = no cluster (the one-SM kernels).
-// MKFHE_CLUSTER = 0: never; 2 / 4 / 8: that size whenever the parameter set supports it (A/B runs, tests).
+// MKFHE_CLUSTER = 0: never; 2 / 4 / 8: that size whenever the parameter set supports it (A/B runs, tests); 1: this policy.
 inline uint32_t cluster_size_for(FastState& F, const DevCtx& d, bool gate, uint32_t batch) {
     uint32_t forced = 0;
     if (const char* e = getenv("MKFHE_CLUSTER")) {
         forced = uint32_t(atoi(e));
-        if (forced != 2 && forced != 4 && forced != 8) return 0;
-        return cluster_supported(d, forced) ? forced : 0;
+        if (forced == 0) return 0;
+        if (forced == 2 || forced == 4 || forced == 8) return cluster_supported(d, forced) ? forced : 0;
+        forced = 1;  // any other value: the default policy below, also next to hand-picked one-SM variants
     }
     // a run that selects a one-SM kernel variant by hand (experiments, the variant tests) keeps it
-    if (getenv("MKFHE_GROUPS") || getenv("MKFHE_MINB") || getenv("MKFHE_FAST_ALIAS") || getenv("MKFHE_AG")) return 0;
+    if (!forced && (getenv("MKFHE_GROUPS") || getenv("MKFHE_MINB") || getenv("MKFHE_FAST_ALIAS") || getenv("MKFHE_AG"))) return 0;
     for (uint32_t CL = 8; CL >= 2; CL >>= 1) {
         if (!cluster_supported(d, CL) || uint64_t(batch) * CL > uint64_t(F.sms)) continue;
         int& cached = F.max_clusters[gate ? 1 : 0][CL == 8 ? 2 : CL == 4 ? 1 : 0];

@@ -22,6 +22,15 @@ peaks() {
 run() { name=$1; shift; (time timeout 1500 python bench.py "$@") > gpurun_out/${TAG}_${name}.json 2> gpurun_out/${TAG}_${name}.err; \
         echo "== $name"; cut -c1-600 gpurun_out/${TAG}_${name}.json; tail -2 gpurun_out/${TAG}_${name}.err; }
 case $S in
+cl5)    # cluster kernel with the key words preloaded into registers: latency at k = 2 / 4 / 8 / 16
+  q() { echo "== $*"; env "$@" timeout 300 python tests/dev_quick_bench.py --paramset $PS --batches $BT --check $CK --reps 3 2>&1 | grep -E "batch|MISMATCH|exact|rror" ; }
+  PS=STD100_MKNTRU_LWE BT=1,74 CK=2; q X=0
+  PS=STD100_MKNTRU BT=1,74 CK=2; q X=0
+  PS=STD100_MKNTRU_2 BT=1,37 CK=1; q X=0
+  PS=STD100_MKNTRU_LWE_2 BT=1 CK=1; q X=0
+  PS=STD100_MKNTRU_3 BT=1 CK=1; q X=0
+  PS=STD100_MKNTRU_4 BT=1 CK=1; q X=0
+  ;;
 cl4)    # cluster kernel after the relaxed owner arrival; then the whole GPU suite and smoke with clusters as the small-batch default
   q() { echo "== $*"; env "$@" timeout 300 python tests/dev_quick_bench.py --paramset $PS --batches $BT --check $CK --reps 3 2>&1 | grep -E "batch|MISMATCH|exact|rror" ; }
   PS=STD100_MKNTRU_LWE BT=1,74 CK=1; q X=0
