@@ -34,7 +34,10 @@ __device__ __forceinline__ uint32_t cluster_rank() {
 }
 __device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
 // arrival of a CTA that has written nothing the others will read (the key owner): no release fence (ncu showed the fence of
-// arrive.release as 5% of the owner's samples, profiles/r2_s21_cluster74.txt)
+// arrive.release as 5% of the owner's samples, profiles/r2_s21_cluster74.txt).  What the owner's arrival of step e + 1 orders is a
+// write-after-read: the other CTAs may overwrite Vs[e & 1] only after the owner has read it in step e.  Those reads are shared-memory
+// loads whose values were consumed by the sumV term of step e, thousands of instructions and at least three block barriers (bar.sync
+// orders the CTA's prior shared-memory accesses) before this arrival, so no fence is needed for them.
 __device__ __forceinline__ void cluster_arrive_relaxed() { asm volatile("barrier.cluster.arrive.relaxed.aligned;" ::: "memory"); }
 __device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
 // address of `p` (a shared-memory address of this CTA) in the shared memory of CTA `rank` of the cluster

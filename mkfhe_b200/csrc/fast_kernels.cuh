@@ -681,7 +681,10 @@ __device__ __forceinline__ void fast_step(const DevCtx& P, const FastTables& T, 
 // MINB: gates the launch bounds promise per SM = the register budget (4: 64 registers, 3: 80, 2: 128).  The host picks the
 // largest MINB shared memory allows anyway, so party counts that fit fewer gates per SM get the registers the absent gates
 // would have used (no spills, longer load-to-use distances).
-template <bool GATE, bool XZW, bool ALIAS, int MINB>
+// PAIR: inverse transforms two at a time (fast_step), a build of its own: as a run-time switch inside one kernel the paired step's
+// 240 B of spills in the 80-register XZW build slowed the UNPAIRED path of the same kernel too (boolean-mkntru, 4096 gates:
+// 242.4 -> 249.8 ms with either setting, profiles/r2_s14_pair_alias.txt, r2_s27_pair_noprefetch.txt).
+template <bool GATE, bool XZW, bool ALIAS, int MINB, bool PAIR = false>
 __global__ void __launch_bounds__(FT, MINB) blind_rotate_fast(const DevCtx P, const FastTables T, const GateIO io) {
     extern __shared__ __align__(16) uint32_t sm[];
     const uint32_t k = P.k, n = P.n, tid = threadIdx.x;
@@ -694,12 +697,15 @@ __global__ void __launch_bounds__(FT, MINB) blind_rotate_fast(const DevCtx P, co
 
     if (T.stagger_ns) __nanosleep((blockIdx.x & 3u) * T.stagger_ns);
     rotate_prologue<GATE>(P, io, blockIdx.x, a, crot);
-    fast_step<XZW, true, ALIAS, (MINB < 4), false>(P, T, a, E1, E2, Ms, 0, crot[0], tid);
+    // (no key prefetch in this kernel: batches of at most one gate per SM, the only ones it pays for, run on the cluster and
+    // party-parallel kernels; carrying the code here cost the 80-register XZW build 240 B of spills and 3% at 4096 gates)
+    // (inlined on purpose: as a __noinline__ function the first step takes the kernel parameters by address, which moves them to
+    // local memory for the whole kernel: 178.6 -> 189.6 ms at 4096 gates, profiles/r2_s29_first_noinline.txt)
+    fast_step<XZW, true, ALIAS, false, false>(P, T, a, E1, E2, Ms, 0, crot[0], tid);
     for (uint32_t s = 1; s < k * n; ++s) {
         const uint32_t c = crot[s];
         if (c == 0) continue;  // X^0 - 1 = 0: the step leaves acc unchanged
-        if (MINB < 4 && T.pair) fast_step<XZW, false, ALIAS, true, true>(P, T, a, E1, E2, Ms, s, c, tid);
-        else fast_step<XZW, false, ALIAS, (MINB < 4), false>(P, T, a, E1, E2, Ms, s, c, tid);
+        fast_step<XZW, false, ALIAS, false, PAIR>(P, T, a, E1, E2, Ms, s, c, tid);
     }
     rotate_epilogue<GATE>(P, io, blockIdx.x, a, E1);
 }
@@ -1663,8 +1669,8 @@ inline cudaError_t fast_blind_rotate(FastState& F, const DevCtx& d, bool gate, c
     // no gain from 148 gates on and -0.7% at k = 16 (profiles/r2_s6_latency.txt).  MKFHE_PREFETCH=0/1 forces it for A/B runs
     F.T.prefetch = (batch <= uint32_t(F.sms) && d.k <= 8) ? 1u : 0u;
     if (const char* pf = getenv("MKFHE_PREFETCH")) F.T.prefetch = pf[0] == '1' ? 1u : 0u;
-    F.T.pair = 1u;
-    if (const char* pr = getenv("MKFHE_PAIR")) F.T.pair = pr[0] == '1' ? 1u : 0u;
+    F.T.pair = 1u;  // (resolved below, once the register budget is known)
+    const char* pair_env = getenv("MKFHE_PAIR");
     const bool alias = G > 1 ? grouped_smem_bytes(d.k, d.n, G, false) > 227 * 1024 : fast_use_alias(d, batch, F.sms);
     const size_t smem = G > 1 ? grouped_smem_bytes(d.k, d.n, G, alias) : fast_smem_bytes(d.k, d.n, alias, xzw);
     auto launch = [&](auto kern) -> cudaError_t {
@@ -1711,9 +1717,17 @@ inline cudaError_t fast_blind_rotate(FastState& F, const DevCtx& d, bool gate, c
             default: e = launch(blind_rotate_fast<true, true, true, 4>); break;
         }
     } else {
-#define MKFHE_LAUNCH_MINB(G_, X_)                                                      \
-    (minb >= 4 ? launch(blind_rotate_fast<G_, X_, false, 4>)                           \
-               : minb == 3 ? launch(blind_rotate_fast<G_, X_, false, 3>) : launch(blind_rotate_fast<G_, X_, false, 2>))
+        // paired inverses: as kernels of their own they pay at k >= 8 only (128 registers, two gates per SM: boolean-mkntru k = 8
+        // 1357 -> 1396 gates/s); unpaired is ahead everywhere else (ms per launch, unpaired / paired: boolean-mkntru 4096 gates
+        // 241.8 / 248.5, k = 4 888 gates 176.7 / 179.5; boolean-mklwe 296 gates 14.97 / 15.33, 444 gates 21.71 / 22.13, k = 4 444
+        // gates 71.9 / 72.8; profiles/r2_s28_pair_split.txt)
+        bool pair = minb == 2 && d.k >= 8;
+        if (pair_env) pair = pair_env[0] == '1' && minb < 4;
+        F.T.pair = pair ? 1u : 0u;
+#define MKFHE_LAUNCH_MINB(G_, X_)                                                                                                   \
+    (minb >= 4 ? launch(blind_rotate_fast<G_, X_, false, 4>)                                                                        \
+               : minb == 3 ? (pair ? launch(blind_rotate_fast<G_, X_, false, 3, true>) : launch(blind_rotate_fast<G_, X_, false, 3>)) \
+                           : (pair ? launch(blind_rotate_fast<G_, X_, false, 2, true>) : launch(blind_rotate_fast<G_, X_, false, 2>)))
         switch (sel >> 1) {
             case 0: e = MKFHE_LAUNCH_MINB(false, false); break;
             case 1: e = MKFHE_LAUNCH_MINB(false, true); break;

@@ -22,6 +22,20 @@ peaks() {
 run() { name=$1; shift; (time timeout 1500 python bench.py "$@") > gpurun_out/${TAG}_${name}.json 2> gpurun_out/${TAG}_${name}.err; \
         echo "== $name"; cut -c1-600 gpurun_out/${TAG}_${name}.json; tail -2 gpurun_out/${TAG}_${name}.err; }
 case $S in
+pair2)  # the 80-register XZW build without the dead prefetch code: paired inverses on / off at k = 2 / 4 / 8
+  q() { echo "== $*"; env "$@" timeout 300 python tests/dev_quick_bench.py --paramset $PS --batches $BT --check $CK --reps 3 2>&1 | grep -E "batch|MISMATCH|exact|rror" ; }
+  PS=STD100_MKNTRU BT=444,4096 CK=1; q MKFHE_PAIR=0; q MKFHE_PAIR=1
+  PS=STD100_MKNTRU_2 BT=888 CK=1; q MKFHE_PAIR=0; q MKFHE_PAIR=1
+  PS=STD100_MKNTRU_3 BT=592 CK=1; q MKFHE_PAIR=0; q MKFHE_PAIR=1
+  PS=STD100_MKNTRU_LWE_2 BT=444 CK=1; q MKFHE_PAIR=0; q MKFHE_PAIR=1
+  PS=STD100_MKNTRU_LWE BT=296,444 CK=1; q MKFHE_PAIR=0; q MKFHE_PAIR=1
+  ;;
+final2) # what the driver runs at round end: GPU tests, smoke, both bench arms at N = 1 with the driver's flags
+  (time python -m pytest tests -m gpu -x -q) > gpurun_out/${TAG}_tests.log 2>&1; tail -4 gpurun_out/${TAG}_tests.log
+  python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${TAG}_smoke.log 2>&1; tail -3 gpurun_out/${TAG}_smoke.log
+  run ref --impl reference --steps 3 --warmup 1
+  run bench --steps 20 --warmup 3
+  ;;
 cl5)    # cluster kernel with the key words preloaded into registers: latency at k = 2 / 4 / 8 / 16
   q() { echo "== $*"; env "$@" timeout 300 python tests/dev_quick_bench.py --paramset $PS --batches $BT --check $CK --reps 3 2>&1 | grep -E "batch|MISMATCH|exact|rror" ; }
   PS=STD100_MKNTRU_LWE BT=1,74 CK=2; q X=0
