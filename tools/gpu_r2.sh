@@ -22,6 +22,17 @@ peaks() {
 run() { name=$1; shift; (time timeout 1500 python bench.py "$@") > gpurun_out/${TAG}_${name}.json 2> gpurun_out/${TAG}_${name}.err; \
         echo "== $name"; cut -c1-600 gpurun_out/${TAG}_${name}.json; tail -2 gpurun_out/${TAG}_${name}.err; }
 case $S in
+final3) # after the un-mixing of the paired step: XZW register budget re-check, party sweep k = 2 / 4 / 8 at batch 16384, then what the driver runs
+  q() { echo "== $*"; env "$@" timeout 300 python tests/dev_quick_bench.py --paramset $PS --batches $BT --check $CK --reps 3 2>&1 | grep -E "batch|MISMATCH|exact|rror" ; }
+  PS=STD100_MKNTRU BT=4096 CK=1; q X=0; q MKFHE_MINB=4
+  run k2  --paramset STD100_MKNTRU   --batch 16384 --steps 2 --warmup 1 --synthetic-keys --no-also --check-oracle 16 --no-cpu-baseline
+  run k4  --paramset STD100_MKNTRU_2 --batch 16384 --steps 1 --warmup 1 --synthetic-keys --no-also --check-oracle 16 --no-cpu-baseline
+  run k8  --paramset STD100_MKNTRU_3 --batch 16384 --steps 1 --warmup 1 --synthetic-keys --no-also --check-oracle 4 --no-cpu-baseline
+  (time python -m pytest tests -m gpu -x -q) > gpurun_out/${TAG}_tests.log 2>&1; tail -4 gpurun_out/${TAG}_tests.log
+  python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/${TAG}_smoke.log 2>&1; tail -3 gpurun_out/${TAG}_smoke.log
+  run ref --impl reference --steps 3 --warmup 1
+  run bench --steps 20 --warmup 3
+  ;;
 pair2)  # the 80-register XZW build without the dead prefetch code: paired inverses on / off at k = 2 / 4 / 8
   q() { echo "== $*"; env "$@" timeout 300 python tests/dev_quick_bench.py --paramset $PS --batches $BT --check $CK --reps 3 2>&1 | grep -E "batch|MISMATCH|exact|rror" ; }
   PS=STD100_MKNTRU BT=444,4096 CK=1; q MKFHE_PAIR=0; q MKFHE_PAIR=1
