@@ -1077,9 +1077,12 @@ __global__ void __launch_bounds__(FT, CTAS) ntt_batch_tma(const FastTables T, co
 constexpr int NTT2_STAGES = 3;
 __host__ __device__ inline size_t ntt_tma2_smem_bytes() { return (size_t(NTT2_STAGES) * 2 * FN + 2 * FNP) * 4 + NTT2_STAGES * 8; }
 
-template <bool HALF, bool SHIFTFOLD>
+// INV is a template parameter, not a kernel argument: one direction per kernel (a run-time switch between two inlined transform
+// bodies is what slowed the gate kernel's paired step, see blind_rotate_fast)
+template <bool HALF, bool SHIFTFOLD, bool INV>
 __global__ void __launch_bounds__(FT, 3) ntt_batch_tma2(const FastTables T, const uint32_t Q, const uint2 one2, uint32_t* polys,
-                                                        const uint64_t pairs, const int inverse) {
+                                                        const uint64_t pairs) {
+    constexpr bool inverse = INV;
     extern __shared__ __align__(128) uint32_t sm[];
     uint32_t* ring = sm;
     uint32_t* E = ring + NTT2_STAGES * 2 * FN;
@@ -1765,11 +1768,12 @@ inline cudaError_t fast_ntt(FastState& F, const DevCtx& d, uint32_t* polys, uint
         auto launch = [&](auto kern) -> cudaError_t {
             cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
             if (e != cudaSuccess) return e;
-            kern<<<g, FT, smem, st>>>(F.T, d.mod.Q, F.one2, polys, pairs, inverse);
+            kern<<<g, FT, smem, st>>>(F.T, d.mod.Q, F.one2, polys, pairs);
             return cudaSuccess;
         };
-        cudaError_t e = F.half ? (sf ? launch(ntt_batch_tma2<true, true>) : launch(ntt_batch_tma2<true, false>))
-                               : (sf ? launch(ntt_batch_tma2<false, true>) : launch(ntt_batch_tma2<false, false>));
+#define MKFHE_TMA2(H_, S_) (inverse ? launch(ntt_batch_tma2<H_, S_, true>) : launch(ntt_batch_tma2<H_, S_, false>))
+        cudaError_t e = F.half ? (sf ? MKFHE_TMA2(true, true) : MKFHE_TMA2(true, false)) : (sf ? MKFHE_TMA2(false, true) : MKFHE_TMA2(false, false));
+#undef MKFHE_TMA2
         if (e != cudaSuccess) return e;
         ++*launches;
         if ((e = cudaGetLastError()) != cudaSuccess) return e;
