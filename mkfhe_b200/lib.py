@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libmkfhe_b200.so")
+LIB_PATH = os.environ.get("MKFHE_B200_LIB") or os.path.join(HERE, "libmkfhe_b200.so")  # (override: experimental builds, tools/gpu_r2.sh)
 
 U32P = C.POINTER(C.c_uint32)
 

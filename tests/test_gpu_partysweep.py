@@ -165,3 +165,43 @@ def test_cluster_kernel_party_counts_that_do_not_divide(k, cl, monkeypatch):
     assert (res[cl][0][1].ravel() == eo).all()
     ea = o.eval_acc(bk, pkey, acc[0].ravel(), rot[0].ravel(), P.q)
     assert (res[cl][1][0].ravel() == np.asarray(ea).ravel()).all()
+
+
+def test_cluster_policy_reports_sms_per_gate(monkeypatch):
+    """mkfhe_last_gate_sms: batches of which the GPU holds one cluster per gate at once run on 2 (k = 2) or 4 (k = 4) SMs per gate,
+    larger ones on one SM; MKFHE_CLUSTER=0 turns the clusters off.  Outputs do not depend on the choice."""
+    import torch
+
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    for paramset, want in (("STD100_MKNTRU_LWE", 2), ("STD100_MKNTRU_2", 4)):
+        monkeypatch.delenv("MKFHE_CLUSTER", raising=False)
+        method = mk.MKNTRU_LWE if "LWE" in paramset else mk.MKNTRU
+        P = mk.derive_params(mk.PARAMSETS[paramset], method)
+        P.n = 16  # a short blind rotation: the policy does not depend on n
+        rng = np.random.default_rng(9)
+        ell, S, lwe = P.digitsG - 1, (2 if P.variant == 0 else 1), P.scheme == 1
+        bk = rng.integers(0, P.Q, size=(P.k * S * P.n + 1) * ell * 2 * P.N, dtype=np.uint32)
+        pkey = rng.integers(0, P.Q, size=P.k * ell * P.N, dtype=np.uint32)
+        ctx = mk.BinFHEContext().GenerateFromParams(P)
+        if lwe:
+            rows = P.k * P.N * P.baseKS * P.dKS
+            ctx.LoadKeys(bk, pkey, kskA=rng.integers(0, P.qKS, size=rows * P.n, dtype=np.uint32),
+                         kskB=rng.integers(0, P.qKS, size=rows, dtype=np.uint32))
+        else:
+            ctx.LoadKeys(bk, pkey, ksk=rng.integers(0, P.qKS, size=P.k * P.N * P.dKS * P.n, dtype=np.uint32),
+                         ctnand=rng.integers(0, P.q, size=P.k * P.n, dtype=np.uint32))
+        B = sms + 1
+        ct1 = rng.integers(0, P.q, size=(B, P.k, P.n), dtype=np.uint32)
+        ct2 = rng.integers(0, P.q, size=(B, P.k, P.n), dtype=np.uint32)
+        b1 = rng.integers(0, P.q, size=B, dtype=np.uint32)
+        b2 = rng.integers(0, P.q, size=B, dtype=np.uint32)
+        run = (lambda m: ctx.EvalBinGate("NAND", ct1[:m], ct2[:m], b1[:m], b2[:m])[0]) if lwe else (lambda m: ctx.EvalBinGate("NAND", ct1[:m], ct2[:m]))
+        big = np.asarray(run(B))
+        assert ctx.last_gate_sms() == 1
+        small = np.asarray(run(3))
+        assert ctx.last_gate_sms() == want
+        assert (small == big[:3]).all()
+        monkeypatch.setenv("MKFHE_CLUSTER", "0")
+        off = np.asarray(run(3))
+        assert ctx.last_gate_sms() == 1 and (off == small).all()
+        ctx.close()
