@@ -15,7 +15,8 @@ host buffers (H2D + D2H inside the timed region; N > 1: + the result gather); `r
 of the blind-rotation kernel (SURVEY.md section 8d count) against the lazy-butterfly rate measured on this GPU in this run,
 and against the analytic 8-cycle floor; `roofline_hbm` = key-stream bytes against MEASURED_PEAKS.json; `cpu_baseline` = the
 reference's own code (oracle/_ref, compiled unmodified) on all host cores over a bounded sample, plus the single-thread
-single-gate latency the reference's examples print.  The default workload adds `also.boolean_mkntru`: the same measurement
+single-gate latency the reference's examples print; `single_gate` = the same one-gate call on the GPU (BASELINE.json configs[0]:
+kernel ms, host-buffer call ms, SMs per gate of the thread-block cluster it runs on).  The default workload adds `also.boolean_mkntru`: the same measurement
 for STD100_MKNTRU (the XZW accumulator of mk-acc-xzw.cpp), k = 2, same batch.  Parity inside the run (outside the timed
 regions): every output decrypted = NAND, 64 gates bit-exact against the CPU oracle.
 """

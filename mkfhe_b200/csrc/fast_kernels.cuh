@@ -701,9 +701,9 @@ __global__ void __launch_bounds__(FT, MINB) blind_rotate_fast(const DevCtx P, co
     // party-parallel kernels; carrying the code here cost the 80-register XZW build 240 B of spills and 3% at 4096 gates)
     // (inlined on purpose: as a __noinline__ function the first step takes the kernel parameters by address, which moves them to
     // local memory for the whole kernel: 178.6 -> 189.6 ms at 4096 gates, profiles/r2_s29_first_noinline.txt)
-#ifndef MKFHE_EXP_NOFIRST  // (experiment: what the inlined first step costs the step loop; results are wrong without it)
+    // (nor does its presence cost the step loop anything: a build without the first step runs the loop at the same speed,
+    // 178.80 vs 178.75 ms, profiles/r2_s34_nofirst.txt)
     fast_step<XZW, true, ALIAS, false, false>(P, T, a, E1, E2, Ms, 0, crot[0], tid);
-#endif
     for (uint32_t s = 1; s < k * n; ++s) {
         const uint32_t c = crot[s];
         if (c == 0) continue;  // X^0 - 1 = 0: the step leaves acc unchanged
