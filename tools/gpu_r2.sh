@@ -22,6 +22,11 @@ peaks() {
 run() { name=$1; shift; (time timeout 1500 python bench.py "$@") > gpurun_out/${TAG}_${name}.json 2> gpurun_out/${TAG}_${name}.err; \
         echo "== $name"; cut -c1-600 gpurun_out/${TAG}_${name}.json; tail -2 gpurun_out/${TAG}_${name}.err; }
 case $S in
+prof3)  # ncu of the last kernels of round 2: the one-direction transform kernel, the un-mixed XZW gate kernel
+  prof ntt2048fwd ntt_batch_tma2 2 1 --workload ntt --ntt-n 2048 --steps 1 --warmup 1 --ntt-variants tma --min-seconds 0
+  prof ntt2048inv ntt_batch_tma2 3 1 --workload ntt --ntt-n 2048 --steps 1 --warmup 1 --ntt-variants tma --min-seconds 0
+  prof mkntru4096 blind_rotate_fast 3 1 --steps 1 --warmup 3 --no-also --check-oracle 0 --paramset STD100_MKNTRU
+  ;;
 final3) # after the un-mixing of the paired step: XZW register budget re-check, party sweep k = 2 / 4 / 8 at batch 16384, then what the driver runs
   q() { echo "== $*"; env "$@" timeout 300 python tests/dev_quick_bench.py --paramset $PS --batches $BT --check $CK --reps 3 2>&1 | grep -E "batch|MISMATCH|exact|rror" ; }
   PS=STD100_MKNTRU BT=4096 CK=1; q X=0; q MKFHE_MINB=4
