@@ -22,6 +22,9 @@ peaks() {
 run() { name=$1; shift; (time timeout 1500 python bench.py "$@") > gpurun_out/${TAG}_${name}.json 2> gpurun_out/${TAG}_${name}.err; \
         echo "== $name"; cut -c1-600 gpurun_out/${TAG}_${name}.json; tail -2 gpurun_out/${TAG}_${name}.err; }
 case $S in
+prof4)  # ncu of the one-direction transform kernels: every launch of the short run (the summary keeps the full-batch ones)
+  prof ntt2048split ntt_batch_tma2 0 8 --workload ntt --ntt-n 2048 --steps 1 --warmup 1 --ntt-variants tma --min-seconds 0
+  ;;
 prof3)  # ncu of the last kernels of round 2: the one-direction transform kernel, the un-mixed XZW gate kernel
   prof ntt2048fwd ntt_batch_tma2 2 1 --workload ntt --ntt-n 2048 --steps 1 --warmup 1 --ntt-variants tma --min-seconds 0
   prof ntt2048inv ntt_batch_tma2 3 1 --workload ntt --ntt-n 2048 --steps 1 --warmup 1 --ntt-variants tma --min-seconds 0
