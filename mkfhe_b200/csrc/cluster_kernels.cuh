@@ -1,25 +1,27 @@
-// cluster_kernels.cuh -- one gate on a thread-block CLUSTER of two SMs (sm_100a), for the batches that leave most of the GPU idle:
-// the single accumulator of the drop-in UniEncAccumulator::EvalAcc (mk-acc.h:67-71), one EvalBinGate, the narrow levels of a
-// circuit.
+// cluster_kernels.cuh -- one gate on a thread-block CLUSTER of CL = 2, 4 or 8 SMs (sm_100a), for the batches that leave most of the
+// GPU idle: the single accumulator of the drop-in UniEncAccumulator::EvalAcc (mk-acc.h:67-71), one EvalBinGate, the narrow levels
+// of a circuit.
 //
 // Why: a gate's steps are sequential, and within a step the chain  party terms -> sumV -> sumV term  (mk-acc-xzw.cpp:240-289) is
 // what the clock sees.  On ONE SM (blind_rotate_grouped, two groups of 256 threads) a single boolean-mklwe gate keeps the fma-heavy
-// pipe about 55% busy -- both groups' transforms queue on the same four sub-partitions -- and takes 8.75 ms.  Here CTA r of the
-// cluster owns the parties p = r (mod 2): their accumulators live in ITS shared memory, its 8 warps have an SM's pipes to
-// themselves, and the only traffic between the SMs is the partial sum  sum_p <D_p, Pkey_p>  of the CTA that does not own the step's
-// key: 8 KiB per step, written straight into the key owner's shared memory (distributed shared memory, st.shared::cluster), followed
-// by one cluster barrier (barrier.cluster.arrive.release / wait.acquire).  The CTA that does not own the key never waits for the
-// other one's sumV term: after the barrier it transforms its last product back, updates its accumulator and starts the next step's
-// party terms, so the key owner's chain (its parties, then the sumV term) is the only critical path.
+// pipe about 55% busy -- both groups' transforms queue on the same four sub-partitions -- and takes 8.7 ms.  Here CTA r of the
+// cluster owns the parties p = r (mod CL): their accumulators live in ITS shared memory, its 8 warps have an SM's pipes to
+// themselves, and the only traffic between the SMs is the partial sum  sum_p <D_p, Pkey_p>  of each CTA that does not own the
+// step's key: 8 KiB per CTA and step, written straight into the key owner's shared memory (distributed shared memory,
+// st.shared::cluster on a mapa address), followed by one cluster barrier (barrier.cluster.arrive / wait.acquire).  A CTA that does
+// not own the key never waits for the owner's sumV term: after the barrier it transforms its last product back, updates its
+// accumulator and starts the next step's party terms, so the key owner's chain (its parties, then the sumV term) is the only
+// critical path.  Measured: 6.0 ms (k = 2, 2 SMs), 16.0 ms (k = 4, 4 SMs; one SM: 36.0), 92.8 ms (k = 16, 8 SMs; one SM: 428).
 //
-// Per step s = (u, i), CTA r, owner CTA o = u mod 2:
+// Per executed step e (s = (u, i), rotation != 0), CTA r, owner CTA o = u mod CL:
 //   for own parties p != u, then p = u (if r == o):  digits of (X^c - 1) a_p -> 2 forward NTTs -> X_p = <D_p, d>, V_r += <D_p, Pkey_p>
-//   r != o:  V_r -> Vs[s & 1] of CTA o (remote);  arrive;  a_p += INTT(X_p) for the last own party;  wait
-//   r == o:  arrive;  wait;  V = V_o + Vs[s & 1];  W = digits of INTT(V);  X_u += <NTT(W), f>;  a_u += INTT(X_u)
-// Vs is double-buffered by the parity of the step: CTA r's write of step s + 2 cannot pass the owner's read of step s, because r
-// must first pass the barrier of step s + 1, at which the owner arrives only after step s.
+//   r != o:  V_r -> slot (r - o - 1 mod CL) of Vs[e & 1] in CTA o (remote);  arrive.release;  a_p += INTT(X_p) for the last own party;  wait
+//   r == o:  arrive.relaxed;  wait;  V = V_o + sum of the slots of Vs[e & 1];  W = digits of INTT(V);  X_u += <NTT(W), f>;  a_u += INTT(X_u)
+// Vs is double-buffered by the parity of the count of EXECUTED steps (steps with rotation 0 are skipped, identically in every CTA):
+// CTA r's write of step e + 2 cannot pass the owner's read of step e, because r must first pass the barrier of step e + 1, at which
+// the owner of step e arrives only after step e.
 // Same exact sums as the sequential kernel (fast_step), evaluated in a different order: results are bit-identical (the tests hold
-// this kernel to the oracle and to the compiled reference).
+// this kernel to the oracle and to the compiled reference, for every cluster size and for party counts that do not divide it).
 #pragma once
 #include "fast_kernels.cuh"
 
