@@ -98,3 +98,29 @@ def test_circuit_levelisation_needs_no_gpu():
                 [(0, 1, 0)]):             # a gate overwriting its own input
         with pytest.raises(mk.config_error):
             mk.CircuitLevels(6, bad)
+
+
+def test_header_is_plain_c(tmp_path):
+    """include/mkfhe_b200.h is the drop-in boundary: it must compile as C (no C++ types, no torch types) and as C++."""
+    import subprocess
+
+    src = tmp_path / "use.c"
+    src.write_text('#include "mkfhe_b200.h"\nint main(void) { mkfhe_params p; (void)p; return (int)(MKFHE_STATIC_SCRATCH_WORDS == 0); }\n')
+    inc = os.path.join(ROOT, "include")
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Werror", "-pedantic", "-fsyntax-only", "-I", inc, str(src)])
+    subprocess.check_call(["g++", "-std=c++17", "-Wall", "-Werror", "-fsyntax-only", "-x", "c++", "-I", inc, str(src)])
+
+
+def test_static_scratch_sizing_needs_no_gpu():
+    """mkfhe_circuit_static_words / mkfhe_static_scratch_words (the allocation-free circuit entry point): host arithmetic only"""
+    L = mklib.load()
+    cap = L.mkfhe_static_scratch_words()
+    assert cap == 2 << 20
+    P = mk.derive_params(mk.PARAMSETS["STD100_MKNTRU_LWE"], mk.MKNTRU_LWE)
+    pad = lambda w: (w + 63) & ~63
+    for gates, widest in ((1, 1), (100, 7), (3000, 600)):
+        want = pad(3 * gates) + 3 * pad(widest * P.k * P.n) + 3 * pad(widest)
+        assert L.mkfhe_circuit_static_words(ctypes.byref(P), gates, widest) == want
+    Pn = mk.derive_params(mk.PARAMSETS["STD100_MKNTRU_4"], mk.MKNTRU)  # MNTRU: no b column
+    assert L.mkfhe_circuit_static_words(ctypes.byref(Pn), 10, 10) == pad(30) + 3 * pad(10 * Pn.k * Pn.n)
+    assert L.mkfhe_circuit_static_words(ctypes.byref(P), 4 * 695, 695) <= cap < L.mkfhe_circuit_static_words(ctypes.byref(P), 4 * 696, 696)
