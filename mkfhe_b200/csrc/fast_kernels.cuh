@@ -907,9 +907,11 @@ __global__ void __launch_bounds__(MAXT, 1) blind_rotate_grouped(const DevCtx P, 
 // ---- standalone batched transform (config 5, mkfhe_ntt): one polynomial per CTA-iteration, persistent grid -----------
 // HBM-bound at large batch (16 KiB moved per 11 264 butterflies), so the next polynomial's coefficients are fetched into
 // registers before the current one is transformed: loads of iteration i+1 overlap the arithmetic of iteration i.
-template <bool HALF>  // HALF: N = 1024, one CTA-iteration transforms the polynomials 2b and 2b + 1 (batch counts pairs)
+template <bool HALF, bool INV>  // HALF: N = 1024, one CTA-iteration transforms the polynomials 2b and 2b + 1 (batch counts pairs);
+                                // INV: one direction per kernel, as in ntt_batch_tma2 (the A/B twins are built the way the default is)
 __global__ void __launch_bounds__(FT, 4) ntt_batch_fast(const FastTables T, const uint32_t Q, const uint2 one2, uint32_t* polys,
-                                                        const uint64_t batch, const int inverse) {
+                                                        const uint64_t batch) {
+    constexpr bool inverse = INV;
     __shared__ __align__(16) uint32_t E[FNP];
     const uint32_t tid = threadIdx.x;
     uint32_t nx[8];
@@ -1003,9 +1005,10 @@ __device__ __forceinline__ void bulk_store(void* gmem_dst, const void* smem_src,
 __device__ __forceinline__ uint32_t fold_shift27(uint32_t x, uint32_t Q) { return x - (x >> 27) * Q; }
 __host__ __device__ inline bool fold_shift27_ok(uint32_t Q) { return Q < (1u << 27) && Q > (1u << 26) && 33ull * ((1u << 27) - Q) <= Q; }
 
-template <bool HALF, bool SHIFTFOLD, int CTAS>
+template <bool HALF, bool SHIFTFOLD, int CTAS, bool INV>
 __global__ void __launch_bounds__(FT, CTAS) ntt_batch_tma(const FastTables T, const uint32_t Q, const uint2 one2, uint32_t* polys,
-                                                       const uint64_t batch, const int inverse) {
+                                                       const uint64_t batch) {
+    constexpr bool inverse = INV;
     extern __shared__ __align__(128) uint32_t sm[];
     constexpr int NTT_STAGES = ntt_stages(CTAS);
     uint32_t* ring = sm;
@@ -1795,13 +1798,15 @@ inline cudaError_t fast_ntt(FastState& F, const DevCtx& d, uint32_t* polys, uint
         auto launch = [&](auto kern) -> cudaError_t {
             cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, int(smem));
             if (e != cudaSuccess) return e;
-            kern<<<g, FT, smem, st>>>(F.T, d.mod.Q, F.one2, polys, batch, inverse);
+            kern<<<g, FT, smem, st>>>(F.T, d.mod.Q, F.one2, polys, batch);
             return cudaSuccess;
         };
-#define MKFHE_NTT_TMA(H_, S_) (ctas == 4 ? launch(ntt_batch_tma<H_, S_, 4>) : ctas == 5 ? launch(ntt_batch_tma<H_, S_, 5>) : launch(ntt_batch_tma<H_, S_, 6>))
+#define MKFHE_NTT_TMA_D(H_, S_, I_) (ctas == 4 ? launch(ntt_batch_tma<H_, S_, 4, I_>) : ctas == 5 ? launch(ntt_batch_tma<H_, S_, 5, I_>) : launch(ntt_batch_tma<H_, S_, 6, I_>))
+#define MKFHE_NTT_TMA(H_, S_) (inverse ? MKFHE_NTT_TMA_D(H_, S_, true) : MKFHE_NTT_TMA_D(H_, S_, false))
         cudaError_t e = F.half ? (sf ? MKFHE_NTT_TMA(true, true) : MKFHE_NTT_TMA(true, false))
                                : (sf ? MKFHE_NTT_TMA(false, true) : MKFHE_NTT_TMA(false, false));
 #undef MKFHE_NTT_TMA
+#undef MKFHE_NTT_TMA_D
         if (e != cudaSuccess) return e;
         ++*launches;
         return cudaGetLastError();
@@ -1809,8 +1814,13 @@ inline cudaError_t fast_ntt(FastState& F, const DevCtx& d, uint32_t* polys, uint
     if (!F.half && getenv("MKFHE_NTT16")) {  // experimental: 16 coefficients per thread, two exchanges
         const unsigned g16 = unsigned(std::min<uint64_t>(batch, uint64_t(F.sms) * 8));
         ntt_batch_fast16<<<g16, FT16, 0, st>>>(F.T, d.mod.Q, F.one2, polys, batch, inverse);
-    } else if (F.half) ntt_batch_fast<true><<<grid, FT, 0, st>>>(F.T, d.mod.Q, F.one2, polys, batch, inverse);
-    else ntt_batch_fast<false><<<grid, FT, 0, st>>>(F.T, d.mod.Q, F.one2, polys, batch, inverse);
+    } else if (F.half) {
+        if (inverse) ntt_batch_fast<true, true><<<grid, FT, 0, st>>>(F.T, d.mod.Q, F.one2, polys, batch);
+        else ntt_batch_fast<true, false><<<grid, FT, 0, st>>>(F.T, d.mod.Q, F.one2, polys, batch);
+    } else {
+        if (inverse) ntt_batch_fast<false, true><<<grid, FT, 0, st>>>(F.T, d.mod.Q, F.one2, polys, batch);
+        else ntt_batch_fast<false, false><<<grid, FT, 0, st>>>(F.T, d.mod.Q, F.one2, polys, batch);
+    }
     ++*launches;
     return cudaGetLastError();
 }
